@@ -1,0 +1,59 @@
+// kernels.h — host-side launch interface of the CUDA kernels (internal to libfctc_b200.so).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace fctc {
+
+struct ViterbiParams {
+    const float* post;  // [N, T, C] contiguous, device
+    int64_t N, T;
+    int C;
+    int qstring;
+    float qscale, qbias;
+    int collapse;
+    uint8_t* labels;  // result pool
+    void* quals;      // uint8_t* or uint32_t* (qual_bytes)
+    int qual_bytes;
+    int32_t* path;
+    int64_t pool_cap;
+    int64_t* offsets;  // [N]
+    int32_t* lens;     // [N]
+    int32_t* status;   // [N]
+    unsigned long long* cursor;
+};
+
+// Chooses the streaming (bulk-async staged) kernel when the shape allows it, else the generic
+// one; returns cudaSuccess or the launch error.  `which` (optional) receives 0 = streaming,
+// 1 = generic.
+cudaError_t launch_viterbi(const ViterbiParams& p, int sm_count, cudaStream_t stream, int* which);
+
+struct BeamParams {
+    const float* post;  // [N, T, C]
+    int64_t N, T;
+    int C;
+    int beam_size;
+    float threshold;
+    int collapse;
+    uint8_t* labels;
+    int32_t* path;
+    int64_t pool_cap;
+    int64_t* offsets;
+    int32_t* lens;
+    int32_t* status;
+    unsigned long long* cursor;
+    void* scratch;          // trie pools, one slot per resident warp
+    int64_t scratch_bytes;
+    int64_t nodes_per_slot;  // node capacity of one slot
+    int n_slots;             // slots available in scratch
+    unsigned long long* ticket;  // read counter for dynamic scheduling (inside scratch)
+};
+
+int64_t beam_scratch_bytes(int sm_count, int64_t N, int64_t T, int C, int beam_size, int nodes_per_row,
+                           int64_t* nodes_per_slot, int* n_slots);
+cudaError_t launch_beam(const BeamParams& p, int sm_count, cudaStream_t stream);
+
+cudaError_t launch_synth(float* post, int64_t N, int64_t T, int C, int kind, uint64_t seed, int64_t first_read,
+                         cudaStream_t stream);
+
+}  // namespace fctc

@@ -1,0 +1,78 @@
+// synth.cu — synthetic posterior generator (bench + tests input).  Not part of the
+// decode path.  Counter-based: every row is a pure function of (seed, read, row), so any shard
+// of any size regenerates the same bytes.
+#include "kernels.h"
+
+namespace fctc {
+
+__device__ __forceinline__ uint64_t mix64(uint64_t z) {  // splitmix64 finaliser
+    z += 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+__device__ __forceinline__ float u24(uint64_t w, int half) {  // uniform in [0,1), 24 bits
+    uint32_t bits = half ? uint32_t(w >> 40) : uint32_t(w >> 8) & 0xFFFFFFu;
+    return float(bits) * (1.0f / 16777216.0f);
+}
+
+__global__ void __launch_bounds__(256) synth_kernel(float* post, long long N, long long T, int C, int kind,
+                                                    uint64_t seed, long long first_read) {
+    const long long rows = N * T;
+    for (long long g = blockIdx.x * (long long)blockDim.x + threadIdx.x; g < rows;
+         g += (long long)gridDim.x * blockDim.x) {
+        const long long n = g / T, t = g - n * T;
+        const uint64_t key = mix64(seed ^ mix64(uint64_t(first_read + n) * 0x100000001B3ull + 0x51ull)) + uint64_t(t) * 0xD1342543DE82EF95ull;
+        float* row = post + g * C;
+        if (kind == 0) {
+            // softmax(3 * (2u - 1)) in f32
+            float mx = -1e30f;
+            for (int c = 0; c < C; ++c) {
+                const uint64_t w = mix64(key + uint64_t(c >> 1) * 0x632BE59BD9B4E019ull);
+                const float z = 3.0f * (2.0f * u24(w, c & 1) - 1.0f);
+                row[c] = z;
+                mx = fmaxf(mx, z);
+            }
+            float sum = 0.0f;
+            for (int c = 0; c < C; ++c) {
+                const float e = expf(row[c] - mx);
+                row[c] = e;
+                sum += e;
+            }
+            const float inv = 1.0f / sum;
+            for (int c = 0; c < C; ++c) row[c] *= inv;
+        } else {
+            // peaked, nanopore-like: the dominant label is shared by row pairs (so repeats occur),
+            // blank with probability 0.65, everything else 0.05*u^2
+            const uint64_t pair_key = mix64(seed ^ mix64(uint64_t(first_read + n) * 0x100000001B3ull + 0x51ull)) +
+                                      uint64_t(t >> 1) * 0xD1342543DE82EF95ull + 0xABCDull;
+            const uint64_t wd = mix64(pair_key);
+            int dom = 0;
+            if (u24(wd, 0) >= 0.65f && C > 1) {
+                dom = 1 + int(u24(wd, 1) * float(C - 1));
+                if (dom > C - 1) dom = C - 1;
+            }
+            float sum = 0.0f;
+            for (int c = 0; c < C; ++c) {
+                const uint64_t w = mix64(key + uint64_t(c >> 1) * 0x632BE59BD9B4E019ull);
+                const float u = u24(w, c & 1);
+                const float v = (c == dom) ? 1.0f : 0.05f * u * u;
+                row[c] = v;
+                sum += v;
+            }
+            for (int c = 0; c < C; ++c) row[c] = row[c] / sum;
+        }
+    }
+}
+
+cudaError_t launch_synth(float* post, int64_t N, int64_t T, int C, int kind, uint64_t seed, int64_t first_read,
+                         cudaStream_t stream) {
+    const long long rows = N * T;
+    if (rows <= 0) return cudaSuccess;
+    long long blocks = (rows + 255) / 256;
+    if (blocks > 148 * 32) blocks = 148 * 32;
+    synth_kernel<<<dim3((unsigned)blocks), 256, 0, stream>>>(post, N, T, C, kind, seed, first_read);
+    return cudaGetLastError();
+}
+
+}  // namespace fctc

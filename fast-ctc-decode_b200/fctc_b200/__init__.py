@@ -1,0 +1,230 @@
+"""fctc_b200 — thin ctypes binding of the C ABI in include/fctc.h (libfctc_b200.so).
+
+This module only marshals pointers; every decode runs in the CUDA library.  It raises if the
+library is missing or no B200 is present — there is no CPU fallback.
+Device-resident entry points take raw device pointers (e.g. ``tensor.data_ptr()``) so that any
+allocator (torch, cuda-python, the caller's own) can own the memory.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(os.path.dirname(_HERE), "libfctc_b200.so")
+
+OK, RAN_OUT_OF_BEAM, INCOMPARABLE_VALUES, INVALID_ENVELOPE, NODE_POOL_OVERFLOW, OUTPUT_OVERFLOW, INVALID_QUALITY_CHAR = range(7)
+E_CUDA, E_ARGUMENT, E_NOMEM, E_UNSUPPORTED, E_CAPACITY = -1, -2, -3, -4, -5
+
+_lib = None
+
+_i64, _i32, _f32, _vp, _u64 = C.c_int64, C.c_int32, C.c_float, C.c_void_p, C.c_uint64
+
+_SIGNATURES = {
+    "fctc_version": (C.c_int, []),
+    "fctc_device_count": (C.c_int, []),
+    "fctc_create": (C.c_int, [C.c_int, C.POINTER(_vp)]),
+    "fctc_destroy": (None, [_vp]),
+    "fctc_last_error": (C.c_char_p, [_vp]),
+    "fctc_status_message": (C.c_char_p, [C.c_int]),
+    "fctc_device_sm_count": (C.c_int, [_vp]),
+    "fctc_viterbi_batch_device": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _i32, _f32, _f32, _i32, _vp, _vp, _i32, _vp,
+                                            _i64, _vp, _vp, _vp, _vp, _vp]),
+    "fctc_viterbi_batch": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _i32, _f32, _f32, _i32, _vp, _vp, _i32, _vp, _i64,
+                                     _vp, _vp, _vp, _vp]),
+    "fctc_viterbi_search": (C.c_int, [_vp, _vp, _i64, _i32, _i64, _i64, _i32, _f32, _f32, _i32, _vp, _vp, _vp, _i64,
+                                      _vp]),
+    "fctc_beam_scratch_bytes": (_i64, [_vp, _i64, _i64, _i32, _i32, _i32]),
+    "fctc_beam_search_batch_device": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _i32, _f32, _i32, _vp, _vp, _i64, _vp,
+                                                _vp, _vp, _vp, _vp, _i64, _i32, _vp]),
+    "fctc_beam_search_batch": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _i32, _f32, _i32, _vp, _vp, _i64, _vp, _vp, _vp,
+                                         _vp]),
+    "fctc_beam_search": (C.c_int, [_vp, _vp, _i64, _i32, _i64, _i64, _i32, _f32, _i32, _vp, _vp, _i64, _vp]),
+    "fctc_synth_posteriors_device": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _i32, _u64, _i64, _vp]),
+    "fctc_host_phred": (C.c_uint32, [_f32, _f32, _f32]),
+    "fctc_host_log10f": (None, [_vp, _vp, _i64]),
+}
+
+
+class FctcError(RuntimeError):
+    def __init__(self, code, message):
+        super().__init__(f"libfctc_b200 error {code}: {message}")
+        self.code = code
+
+
+def lib():
+    """Load libfctc_b200.so (built by build.py).  Raises if it is missing: no fallback."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(f"{LIB_PATH} not built; run `python fast-ctc-decode_b200/build.py`")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGNATURES.items():
+            fn = getattr(L, name)  # AttributeError if the library lacks a declared symbol
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def declared_symbols():
+    return sorted(_SIGNATURES)
+
+
+def _np_ptr(a):
+    return None if a is None else a.ctypes.data
+
+
+def round_up32(v):
+    return (int(v) + 31) & ~31
+
+
+class Decoder:
+    """One handle = one device + its streams and staging buffers (include/fctc.h: fctc_create)."""
+
+    def __init__(self, device=0):
+        self._L = lib()
+        h = _vp()
+        rc = self._L.fctc_create(int(device), C.byref(h))
+        if rc != 0:
+            raise FctcError(rc, (self._L.fctc_last_error(None) or b"").decode())
+        self._h = h
+        self.device = int(device)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.fctc_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc < 0:
+            raise FctcError(rc, (self._L.fctc_last_error(self._h) or b"").decode())
+        return rc
+
+    @property
+    def sm_count(self):
+        return int(self._L.fctc_device_sm_count(self._h))
+
+    # ---- device-resident API (raw pointers) ---------------------------------------------------
+    def synth_posteriors_device(self, post_ptr, n_reads, n_rows, n_labels, kind=0, seed=0, first_read=0, stream=0):
+        self._check(self._L.fctc_synth_posteriors_device(self._h, post_ptr, n_reads, n_rows, n_labels, kind, seed,
+                                                         first_read, stream or None))
+
+    def viterbi_batch_device(self, post_ptr, n_reads, n_rows, n_labels, qstring, qscale, qbias, collapse_repeats,
+                             labels_ptr, quals_ptr, qual_bytes, path_ptr, pool_capacity, offsets_ptr, lens_ptr,
+                             status_ptr, pool_used_ptr, stream=0):
+        self._check(self._L.fctc_viterbi_batch_device(self._h, post_ptr, n_reads, n_rows, n_labels, int(qstring),
+                                                      qscale, qbias, int(collapse_repeats), labels_ptr,
+                                                      quals_ptr or None, qual_bytes, path_ptr, pool_capacity,
+                                                      offsets_ptr, lens_ptr, status_ptr, pool_used_ptr,
+                                                      stream or None))
+
+    def beam_scratch_bytes(self, n_reads, n_rows, n_labels, beam_size, nodes_per_row=0):
+        return int(self._L.fctc_beam_scratch_bytes(self._h, n_reads, n_rows, n_labels, beam_size, nodes_per_row))
+
+    def beam_search_batch_device(self, post_ptr, n_reads, n_rows, n_labels, beam_size, beam_cut_threshold,
+                                 collapse_repeats, labels_ptr, path_ptr, pool_capacity, offsets_ptr, lens_ptr,
+                                 status_ptr, pool_used_ptr, scratch_ptr, scratch_bytes, nodes_per_row=0, stream=0):
+        self._check(self._L.fctc_beam_search_batch_device(self._h, post_ptr, n_reads, n_rows, n_labels, beam_size,
+                                                          beam_cut_threshold, int(collapse_repeats), labels_ptr,
+                                                          path_ptr, pool_capacity, offsets_ptr, lens_ptr, status_ptr,
+                                                          pool_used_ptr, scratch_ptr, scratch_bytes, nodes_per_row,
+                                                          stream or None))
+
+    # ---- host-memory batch API ------------------------------------------------------------------
+    def viterbi_batch(self, post, qstring=False, qscale=1.0, qbias=0.0, collapse_repeats=True, qual_bytes=1,
+                      out=None):
+        """post: C-contiguous float32 [N, T, C] (numpy; pinned memory gives full copy overlap).
+        Returns dict(labels, quals, path, offsets, lens, status, used)."""
+        post = _as_f32_3d(post)
+        N, T, Cn = post.shape
+        cap = N * round_up32(T)
+        o = out or {}
+        labels = o.get("labels", None)
+        labels = np.empty(cap, np.uint8) if labels is None else labels
+        quals = o.get("quals", None)
+        if qstring and quals is None:
+            quals = np.empty(cap, np.uint8 if qual_bytes == 1 else np.uint32)
+        path = o.get("path", None)
+        path = np.empty(cap, np.int32) if path is None else path
+        offsets = o.get("offsets", None)
+        offsets = np.empty(N, np.int64) if offsets is None else offsets
+        lens = o.get("lens", None)
+        lens = np.empty(N, np.int32) if lens is None else lens
+        status = o.get("status", None)
+        status = np.empty(N, np.int32) if status is None else status
+        used = _i64(0)
+        self._check(self._L.fctc_viterbi_batch(self._h, post.ctypes.data, N, T, Cn, int(qstring), qscale, qbias,
+                                               int(collapse_repeats), labels.ctypes.data,
+                                               _np_ptr(quals) if qstring else None, qual_bytes, path.ctypes.data,
+                                               labels.size, offsets.ctypes.data, lens.ctypes.data,
+                                               status.ctypes.data, C.byref(used)))
+        return dict(labels=labels, quals=quals if qstring else None, path=path, offsets=offsets, lens=lens,
+                    status=status, used=used.value)
+
+    def beam_search_batch(self, post, beam_size=5, beam_cut_threshold=0.0, collapse_repeats=True, out=None):
+        post = _as_f32_3d(post)
+        N, T, Cn = post.shape
+        cap = N * round_up32(T)
+        o = out or {}
+        labels = o.get("labels", None)
+        labels = np.empty(cap, np.uint8) if labels is None else labels
+        path = o.get("path", None)
+        path = np.empty(cap, np.int32) if path is None else path
+        offsets = np.empty(N, np.int64)
+        lens = np.empty(N, np.int32)
+        status = np.empty(N, np.int32)
+        used = _i64(0)
+        self._check(self._L.fctc_beam_search_batch(self._h, post.ctypes.data, N, T, Cn, beam_size, beam_cut_threshold,
+                                                   int(collapse_repeats), labels.ctypes.data, path.ctypes.data,
+                                                   labels.size, offsets.ctypes.data, lens.ctypes.data,
+                                                   status.ctypes.data, C.byref(used)))
+        return dict(labels=labels, path=path, offsets=offsets, lens=lens, status=status, used=used.value)
+
+    # ---- single-read API (shape of the pyo3 functions; any strides) --------------------------------
+    def viterbi_search(self, post, qstring=False, qscale=1.0, qbias=0.0, collapse_repeats=True):
+        post = _as_f32_2d(post)
+        T, Cn = post.shape
+        st, sc = (s // 4 for s in post.strides)
+        cap = max(T, 1)
+        labels = np.empty(cap, np.uint8)
+        quals = np.empty(cap, np.uint32)
+        path = np.empty(cap, np.int64)
+        n = _i64(0)
+        status = self._check(self._L.fctc_viterbi_search(self._h, post.ctypes.data, T, Cn, st, sc, int(qstring),
+                                                         qscale, qbias, int(collapse_repeats), labels.ctypes.data,
+                                                         quals.ctypes.data, path.ctypes.data, cap, C.byref(n)))
+        k = n.value
+        return status, labels[:k].copy(), (quals[:k].copy() if qstring else None), path[:k].copy()
+
+    def beam_search(self, post, beam_size=5, beam_cut_threshold=0.0, collapse_repeats=True):
+        post = _as_f32_2d(post)
+        T, Cn = post.shape
+        st, sc = (s // 4 for s in post.strides)
+        cap = max(T, 1)
+        labels = np.empty(cap, np.uint8)
+        path = np.empty(cap, np.int64)
+        n = _i64(0)
+        status = self._check(self._L.fctc_beam_search(self._h, post.ctypes.data, T, Cn, st, sc, beam_size,
+                                                      beam_cut_threshold, int(collapse_repeats), labels.ctypes.data,
+                                                      path.ctypes.data, cap, C.byref(n)))
+        k = n.value
+        return status, labels[:k].copy(), path[:k].copy()
+
+
+def _as_f32_3d(a):
+    if not isinstance(a, np.ndarray) or a.dtype != np.float32 or a.ndim != 3 or not a.flags.c_contiguous:
+        raise TypeError("expected a C-contiguous float32 numpy array of shape [N, T, C]")
+    return a
+
+
+def _as_f32_2d(a):
+    if not isinstance(a, np.ndarray) or a.dtype != np.float32 or a.ndim != 2:
+        raise TypeError("expected a float32 numpy array of shape [T, C]")
+    return a

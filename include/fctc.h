@@ -1,0 +1,152 @@
+/* fctc.h — C ABI of libfctc_b200.so, the B200 (sm_100a) batched CTC decoder.
+ *
+ * This is the drop-in boundary for the decode path of nanoporetech/fast-ctc-decode v0.3.7: each
+ * entry point below is what the reference's `src/lib.rs` would bind over `extern "C"` in place of
+ * its calls into `src/search.rs` / `src/duplex.rs`.  The signatures use plain pointers and sizes
+ * only (no C++/torch types), so they are bindable from Rust (`extern "C"` + build.rs linking the
+ * library), Python (ctypes / the bundled `fast_ctc_decode` extension) or C.
+ * Reference citations are file:line relative to the reference checkout.
+ *
+ * Conventions
+ *   - Posteriors are float32, label axis innermost, blank label first (src/lib.rs:604-616).
+ *   - Decoders return *alphabet indices* (1..n_labels-1, blank never appears); the caller maps
+ *     them to label strings exactly as src/search.rs:291,358 do (labels may be multi-character).
+ *   - Batch results are a pool in "unordered CSR" form: read n owns entries
+ *     [offsets[n], offsets[n]+lens[n]) of `labels` / `quals` / `path`.  Slots are handed out with one
+ *     atomic add per read (rounded up to 32 entries), so the *placement* of a read inside the pool
+ *     depends on scheduling; the *content* per read is deterministic.
+ *   - `path` entries are row indices into the read (int32 on the device, the reference's
+ *     Vec<usize>): emission row for Viterbi, first-proposal row for beam search.
+ *   - Return value: >= 0 is a per-call decode status for single-read calls (FCTC_OK or one of the
+ *     reference's SearchError values); < 0 is a call-level failure, text in fctc_last_error().
+ *   - Every call that takes a handle must be issued from one host thread at a time per handle
+ *     (one handle per device / per host thread; src/lib.rs:199 releases the GIL the same way).
+ *   - There is no CPU fallback: without a usable CUDA device fctc_create fails.
+ */
+#ifndef FCTC_H
+#define FCTC_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Per-read decode status — mirrors enum SearchError, src/lib.rs:36-58. */
+#define FCTC_OK 0
+#define FCTC_RAN_OUT_OF_BEAM 1      /* "Ran out of search space (beam_cut_threshold too high)" */
+#define FCTC_INCOMPARABLE_VALUES 2  /* "Failed to compare values (NaNs in input?)" */
+#define FCTC_INVALID_ENVELOPE 3     /* "Invalid envelope values" */
+#define FCTC_NODE_POOL_OVERFLOW 4   /* device trie pool too small for this read (batch-device API only;
+                                       the host entry points retry with a larger pool) */
+#define FCTC_OUTPUT_OVERFLOW 5      /* result pool (pool_capacity) too small for this read */
+#define FCTC_INVALID_QUALITY_CHAR 6 /* phred code is not a Unicode scalar: the reference's
+                                       char::from_u32(..).unwrap() (src/search.rs:35) would abort */
+
+/* Call-level failures. */
+#define FCTC_E_CUDA (-1)
+#define FCTC_E_ARGUMENT (-2)
+#define FCTC_E_NOMEM (-3)
+#define FCTC_E_UNSUPPORTED (-4)
+#define FCTC_E_CAPACITY (-5)
+
+typedef struct fctc_handle fctc_handle;
+
+/* Library / device management (no reference counterpart: the reference is a stateless CPU
+ * library; the handle owns the CUDA stream, pinned staging and device scratch of one device). */
+int fctc_version(void);                      /* 10000*major + 100*minor + patch */
+int fctc_device_count(void);                 /* 0 if no usable CUDA device */
+int fctc_create(int device, fctc_handle** out);
+void fctc_destroy(fctc_handle* h);
+const char* fctc_last_error(const fctc_handle* h); /* h may be NULL: last fctc_create error */
+/* SearchError Display text, src/lib.rs:43-56 (NULL for statuses that have no reference text). */
+const char* fctc_status_message(int status);
+int fctc_device_sm_count(const fctc_handle* h);
+
+/* ------------------------------------------------------------------------------------------
+ * Viterbi (greedy) decode — replaces search::viterbi_search, src/search.rs:320-383 (+ find_max
+ * :303-318, phred :31-36) as called from src/lib.rs:200-207.
+ *
+ * fctc_viterbi_batch_device: posteriors already in HBM, C-contiguous [n_reads, n_rows, n_labels];
+ *   results stay in HBM (pool form, see above).  Asynchronous on `stream` (a cudaStream_t, may be
+ *   NULL for the handle's stream).  qual_bytes selects the quality element type: 1 = uint8
+ *   (enough whenever 40*|qscale|+|qbias|+33 < 256), 4 = uint32 (any Unicode scalar, as the
+ *   reference's `char`); 1 is refused (FCTC_E_ARGUMENT) when a code could exceed 255.  quals_dev
+ *   may be NULL when qstring == 0.  *pool_used_dev is the pool
+ *   cursor (entries handed out so far): the caller zeroes it before the first call and may keep
+ *   appending batches to one pool.
+ * ------------------------------------------------------------------------------------------ */
+int fctc_viterbi_batch_device(fctc_handle* h, const float* post_dev, int64_t n_reads, int64_t n_rows,
+                              int32_t n_labels, int32_t qstring, float qscale, float qbias,
+                              int32_t collapse_repeats, uint8_t* labels_dev, void* quals_dev, int32_t qual_bytes,
+                              int32_t* path_dev, int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev,
+                              int32_t* status_dev, unsigned long long* pool_used_dev, void* stream);
+
+/* fctc_viterbi_batch: the same over HOST memory (new batched entry point of the north star):
+ *   post_host is C-contiguous [n_reads, n_rows, n_labels]; outputs are host arrays in pool form
+ *   (quals: qual_bytes 1 = uint8, 4 = uint32 Unicode scalars; path is int32).  Reads are streamed
+ *   through the device in chunks, host<->device copies overlapped with decoding; synchronous.
+ *   Pinned (page-locked) host buffers give full copy overlap; pageable ones work, slower.
+ *   pool_capacity >= n_reads * round_up(n_rows, 32) always suffices; *pool_used receives the
+ *   entries used.  If the pool is too small the call returns FCTC_E_CAPACITY.  qual_bytes == 1 is
+ *   refused (FCTC_E_ARGUMENT) when a quality code could exceed 255 for the given qscale/qbias. */
+int fctc_viterbi_batch(fctc_handle* h, const float* post_host, int64_t n_reads, int64_t n_rows, int32_t n_labels,
+                       int32_t qstring, float qscale, float qbias, int32_t collapse_repeats, uint8_t* labels,
+                       void* quals, int32_t qual_bytes, int32_t* path, int64_t pool_capacity, int64_t* offsets,
+                       int32_t* lens, int32_t* status, int64_t* pool_used);
+
+/* fctc_viterbi_search: one read, any strides (in elements) — the shape of the pyo3 entry point
+ *   src/lib.rs:171-212.  labels/quals/path hold `capacity` entries (n_rows always suffices).
+ *   Returns the decode status; n_rows == 0 or n_labels == 0 gives FCTC_E_ARGUMENT (the reference
+ *   aborts on its asserts, src/search.rs:328-331). */
+int fctc_viterbi_search(fctc_handle* h, const float* post_host, int64_t n_rows, int32_t n_labels,
+                        int64_t stride_row, int64_t stride_label, int32_t qstring, float qscale, float qbias,
+                        int32_t collapse_repeats, uint8_t* labels, uint32_t* quals, int64_t* path, int64_t capacity,
+                        int64_t* out_len);
+
+/* ------------------------------------------------------------------------------------------
+ * 1-D CTC prefix beam search — replaces search::beam_search, src/search.rs:159-301, and its
+ * support types SearchPoint (:7-28), tree::SuffixTree (src/tree.rs:17-194) and vec2d::Vec2D
+ * (src/vec2d.rs:5-41), as called from src/lib.rs:354-360.  Argument validation (beam_size >= 1,
+ * 0 <= threshold < 1/n_labels; src/lib.rs:333-349) is the caller's, as in the reference, but is
+ * re-checked here and reported as FCTC_E_ARGUMENT.
+ *
+ * The device API needs trie scratch: fctc_beam_scratch_bytes() bytes at scratch_dev (256-byte
+ * aligned), sized for nodes_per_row proposals per posterior row per read in flight (the hard
+ * bound is (n_labels-1)*beam_size; 0 selects a default that the host entry points grow on
+ * FCTC_NODE_POOL_OVERFLOW).
+ * ------------------------------------------------------------------------------------------ */
+int64_t fctc_beam_scratch_bytes(const fctc_handle* h, int64_t n_reads, int64_t n_rows, int32_t n_labels,
+                                int32_t beam_size, int32_t nodes_per_row);
+int fctc_beam_search_batch_device(fctc_handle* h, const float* post_dev, int64_t n_reads, int64_t n_rows,
+                                  int32_t n_labels, int32_t beam_size, float beam_cut_threshold,
+                                  int32_t collapse_repeats, uint8_t* labels_dev, int32_t* path_dev,
+                                  int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev, int32_t* status_dev,
+                                  unsigned long long* pool_used_dev, void* scratch_dev, int64_t scratch_bytes,
+                                  int32_t nodes_per_row, void* stream);
+int fctc_beam_search_batch(fctc_handle* h, const float* post_host, int64_t n_reads, int64_t n_rows, int32_t n_labels,
+                           int32_t beam_size, float beam_cut_threshold, int32_t collapse_repeats, uint8_t* labels,
+                           int32_t* path, int64_t pool_capacity, int64_t* offsets, int32_t* lens, int32_t* status,
+                           int64_t* pool_used);
+int fctc_beam_search(fctc_handle* h, const float* post_host, int64_t n_rows, int32_t n_labels, int64_t stride_row,
+                     int64_t stride_label, int32_t beam_size, float beam_cut_threshold, int32_t collapse_repeats,
+                     uint8_t* labels, int64_t* path, int64_t capacity, int64_t* out_len);
+
+/* ------------------------------------------------------------------------------------------
+ * Synthetic posterior generator used by bench.py and the tests (no reference counterpart; it
+ * implements SURVEY.md §8d's input definition): fills post_dev[n_reads, n_rows, n_labels] with
+ * kind 0: softmax(3*(2u-1)) rows, kind 1: peaked rows (dominant label, blank w.p. 0.65),
+ * u from a counter-based generator keyed (seed, first_read + read, row).  Asynchronous on stream.
+ * ------------------------------------------------------------------------------------------ */
+int fctc_synth_posteriors_device(fctc_handle* h, float* post_dev, int64_t n_reads, int64_t n_rows, int32_t n_labels,
+                                 int32_t kind, uint64_t seed, int64_t first_read, void* stream);
+
+/* Host instantiation of the device phred()/log10f code (same source, compiled for the host), so
+ * that CPU tests can compare it with glibc without a GPU.  Replaces nothing; test hook. */
+uint32_t fctc_host_phred(float prob, float qscale, float qbias);
+void fctc_host_log10f(const float* x, float* y, int64_t n);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FCTC_H */
