@@ -28,7 +28,7 @@ struct Slot {  // one in-flight chunk of the host-memory pipeline
     cudaEvent_t done = nullptr;
     DevBuf post, labels, quals, path, offsets, lens, status, cursor, scratch;
     unsigned long long* cursor_host = nullptr;  // pinned
-    int64_t first = 0, count = 0;               // reads of the chunk in flight
+    int64_t dst_first = 0, count = 0;           // result rows of the chunk in flight
     bool busy = false;
 };
 
@@ -102,7 +102,7 @@ bool quality_fits_u8(float qscale, float qbias) {
 
 int check_common(fctc_handle* h, int64_t n_reads, int64_t n_rows, int32_t n_labels) {
     if (!h) return FCTC_E_ARGUMENT;
-    if (n_reads < 0 || n_rows <= 0) return fail(h, FCTC_E_ARGUMENT, "n_reads must be >= 0 and n_rows >= 1");
+    if (n_reads < 0 || n_rows < 0) return fail(h, FCTC_E_ARGUMENT, "n_reads and n_rows must be >= 0");
     if (n_labels <= 0) return fail(h, FCTC_E_ARGUMENT, "Empty alphabet given");  // src/lib.rs:191
     if (n_labels > 256) return fail(h, FCTC_E_UNSUPPORTED, "alphabets above 256 labels are not supported (labels are uint8)");
     if (n_rows > (int64_t(1) << 30)) return fail(h, FCTC_E_UNSUPPORTED, "reads above 2^30 rows are not supported");
@@ -113,7 +113,7 @@ int roundup32(int64_t v) { return int((v + 31) & ~int64_t(31)); }
 
 }  // namespace
 
-extern "C" {
+// All fctc_* definitions below take C linkage from their declarations in include/fctc.h.
 
 int fctc_version(void) { return 100; }
 
@@ -198,27 +198,27 @@ int fctc_viterbi_batch_device(fctc_handle* h, const float* post_dev, int64_t n_r
                               int32_t n_labels, int32_t qstring, float qscale, float qbias,
                               int32_t collapse_repeats, uint8_t* labels_dev, void* quals_dev, int32_t qual_bytes,
                               int32_t* path_dev, int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev,
-                              int32_t* status_dev, unsigned long long* pool_used_dev, void* stream) {
+                              int32_t* status_dev, void* stream) {
     if (int rc = check_common(h, n_reads, n_rows, n_labels)) return rc;
-    if (!post_dev || !labels_dev || !path_dev || !offsets_dev || !lens_dev || !status_dev || !pool_used_dev)
+    if (n_rows == 0) return fail(h, FCTC_E_ARGUMENT, "n_rows must be >= 1 (the reference asserts a non-empty matrix)");
+    if (!post_dev || !labels_dev || !path_dev || !offsets_dev || !lens_dev || !status_dev)
         return fail(h, FCTC_E_ARGUMENT, "null device pointer");
     if (qstring && !quals_dev) return fail(h, FCTC_E_ARGUMENT, "qstring requested but quals_dev is NULL");
     if (qual_bytes != 1 && qual_bytes != 4) return fail(h, FCTC_E_ARGUMENT, "qual_bytes must be 1 or 4");
     if (qstring && qual_bytes == 1 && !quality_fits_u8(qscale, qbias))
         return fail(h, FCTC_E_ARGUMENT, "qual_bytes=1 cannot hold the quality codes of qscale=%g qbias=%g; use 4", qscale,
                     qbias);
-    if ((reinterpret_cast<uintptr_t>(labels_dev) | reinterpret_cast<uintptr_t>(path_dev) |
-         reinterpret_cast<uintptr_t>(quals_dev)) & 15u)
-        return fail(h, FCTC_E_ARGUMENT, "result pool arrays must be 16-byte aligned");
+    const int64_t stride = roundup32(n_rows);
+    if (pool_capacity < n_reads * stride)
+        return fail(h, FCTC_E_CAPACITY, "result pool too small: %lld entries given, n_reads*round_up(n_rows,32) = %lld needed",
+                    (long long)pool_capacity, (long long)(n_reads * stride));
     FCTC_CUDA(h, cudaSetDevice(h->device));
     fctc::ViterbiParams p{};
     p.post = post_dev; p.N = n_reads; p.T = n_rows; p.C = n_labels;
     p.qstring = qstring; p.qscale = qscale; p.qbias = qbias; p.collapse = collapse_repeats;
     p.labels = labels_dev; p.quals = quals_dev; p.qual_bytes = qual_bytes; p.path = path_dev;
-    p.pool_cap = pool_capacity; p.offsets = offsets_dev; p.lens = lens_dev; p.status = status_dev;
-    p.cursor = pool_used_dev;
-    cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : h->stream;
-    FCTC_CUDA(h, fctc::launch_viterbi(p, h->sm_count, st, nullptr));
+    p.slot_stride = stride; p.offset_base = 0; p.offsets = offsets_dev; p.lens = lens_dev; p.status = status_dev;
+    FCTC_CUDA(h, fctc::launch_viterbi(p, h->sm_count, static_cast<cudaStream_t>(stream), nullptr));
     return 0;
 }
 
@@ -255,10 +255,64 @@ int drain_slot(fctc_handle* h, Slot& s, HostOut& out) {
                                          size_t(used) * out.qual_bytes, cudaMemcpyDeviceToHost, s.stream));
     }
     // offsets of this chunk are relative to the chunk's device pool: rebase (host, one add per read)
-    for (int64_t i = 0; i < s.count; ++i) out.offsets[s.first + i] += out.used;
-    out.used += used;
+    if (!out.overflow)
+        for (int64_t i = 0; i < s.count; ++i) out.offsets[s.dst_first + i] += out.used;
+    if (!out.overflow) out.used += used;
     s.busy = false;
     return 0;
+}
+
+// launch(slot, count) enqueues the decode kernel for `count` reads resident in slot.post on
+// slot.stream, writing slot.{labels,quals,path,offsets,lens,status,cursor}.
+// Reads [src_first, src_first + n) of post_host go to result rows [dst_first, ...).
+template <class Launch>
+int host_pipeline(fctc_handle* h, const float* post_host, int64_t n_reads, int64_t n_rows, int32_t n_labels,
+                  HostOut& out, int64_t chunk, Launch&& launch) {
+    const int64_t read_bytes = n_rows * int64_t(n_labels) * 4;
+    const int64_t slot_entries = roundup32(n_rows);
+    chunk = std::max<int64_t>(1, std::min(chunk, n_reads));
+    for (int i = 0; i < 2; ++i) {
+        Slot& s = h->slot[i];
+        if (int rc = ensure(h, s.post, size_t(std::max<int64_t>(chunk * read_bytes, 16)))) return rc;
+        if (int rc = ensure(h, s.labels, size_t(chunk * slot_entries))) return rc;
+        if (int rc = ensure(h, s.path, size_t(chunk * slot_entries) * 4)) return rc;
+        if (out.quals)
+            if (int rc = ensure(h, s.quals, size_t(chunk * slot_entries) * out.qual_bytes)) return rc;
+        if (int rc = ensure(h, s.offsets, size_t(chunk) * 8)) return rc;
+        if (int rc = ensure(h, s.lens, size_t(chunk) * 4)) return rc;
+        if (int rc = ensure(h, s.status, size_t(chunk) * 4)) return rc;
+        if (int rc = ensure(h, s.cursor, 256)) return rc;
+        s.busy = false;
+    }
+    int which = 0;
+    for (int64_t first = 0; first < n_reads; first += chunk, which ^= 1) {
+        Slot& s = h->slot[which];
+        if (int rc = drain_slot(h, s, out)) return rc;
+        const int64_t cnt = std::min(chunk, n_reads - first);
+        s.dst_first = first;
+        s.count = cnt;
+        if (read_bytes > 0)
+            FCTC_CUDA(h, cudaMemcpyAsync(s.post.p, post_host + first * n_rows * n_labels, size_t(cnt * read_bytes),
+                                         cudaMemcpyHostToDevice, s.stream));
+        FCTC_CUDA(h, cudaMemsetAsync(s.cursor.p, 0, 8, s.stream));
+        if (int rc = launch(s, cnt)) return rc;
+        FCTC_CUDA(h, cudaMemcpyAsync(s.cursor_host, s.cursor.p, 8, cudaMemcpyDeviceToHost, s.stream));
+        FCTC_CUDA(h, cudaMemcpyAsync(out.offsets + first, s.offsets.p, size_t(cnt) * 8, cudaMemcpyDeviceToHost, s.stream));
+        FCTC_CUDA(h, cudaMemcpyAsync(out.lens + first, s.lens.p, size_t(cnt) * 4, cudaMemcpyDeviceToHost, s.stream));
+        FCTC_CUDA(h, cudaMemcpyAsync(out.status + first, s.status.p, size_t(cnt) * 4, cudaMemcpyDeviceToHost, s.stream));
+        FCTC_CUDA(h, cudaEventRecord(s.done, s.stream));
+        s.busy = true;
+    }
+    // drain in submission order: the slot used before the last one first
+    if (int rc = drain_slot(h, h->slot[which], out)) return rc;
+    if (int rc = drain_slot(h, h->slot[which ^ 1], out)) return rc;
+    FCTC_CUDA(h, cudaStreamSynchronize(h->slot[0].stream));
+    FCTC_CUDA(h, cudaStreamSynchronize(h->slot[1].stream));
+    return 0;
+}
+
+int64_t default_chunk_reads(int64_t read_bytes) {  // ~64 MiB of posteriors per chunk
+    return std::max<int64_t>(1, (int64_t(64) << 20) / std::max<int64_t>(read_bytes, 1));
 }
 
 }  // namespace
@@ -268,6 +322,7 @@ int fctc_viterbi_batch(fctc_handle* h, const float* post_host, int64_t n_reads, 
                        void* quals, int32_t qual_bytes, int32_t* path, int64_t pool_capacity, int64_t* offsets,
                        int32_t* lens, int32_t* status, int64_t* pool_used) {
     if (int rc = check_common(h, n_reads, n_rows, n_labels)) return rc;
+    if (n_rows == 0) return fail(h, FCTC_E_ARGUMENT, "n_rows must be >= 1 (the reference asserts a non-empty matrix)");
     if (!post_host || !labels || !path || !offsets || !lens || !status)
         return fail(h, FCTC_E_ARGUMENT, "null host pointer");
     if (qstring && !quals) return fail(h, FCTC_E_ARGUMENT, "qstring requested but quals is NULL");
@@ -275,76 +330,77 @@ int fctc_viterbi_batch(fctc_handle* h, const float* post_host, int64_t n_reads, 
     if (qstring && qual_bytes == 1 && !quality_fits_u8(qscale, qbias))
         return fail(h, FCTC_E_ARGUMENT, "qual_bytes=1 cannot hold the quality codes of qscale=%g qbias=%g; use 4", qscale,
                     qbias);
-    FCTC_CUDA(h, cudaSetDevice(h->device));
+    const int64_t stride = roundup32(n_rows);
     if (pool_used) *pool_used = 0;
+    if (pool_capacity < n_reads * stride)
+        return fail(h, FCTC_E_CAPACITY, "result pool too small: %lld entries given, n_reads*round_up(n_rows,32) = %lld needed",
+                    (long long)pool_capacity, (long long)(n_reads * stride));
+    FCTC_CUDA(h, cudaSetDevice(h->device));
     if (n_reads == 0) return 0;
 
+    // Slot-form results need no cursor, so the whole pipeline is asynchronous: per chunk
+    // H2D posteriors -> kernel -> D2H of the chunk's slots, alternating between two streams.
     const int64_t read_bytes = n_rows * int64_t(n_labels) * 4;
-    const int64_t slot_entries = roundup32(n_rows);
-    // chunk: ~64 MiB of posteriors, at least one read, at most what keeps 2 x the SM count busy
-    int64_t chunk = std::max<int64_t>(1, (int64_t(64) << 20) / read_bytes);
-    chunk = std::min(chunk, n_reads);
-    HostOut out{labels, qstring ? quals : nullptr, qual_bytes, path, pool_capacity, offsets, lens, status};
-
+    const int64_t chunk = std::min(default_chunk_reads(read_bytes), n_reads);
     for (int i = 0; i < 2; ++i) {
         Slot& s = h->slot[i];
         if (int rc = ensure(h, s.post, size_t(chunk * read_bytes))) return rc;
-        if (int rc = ensure(h, s.labels, size_t(chunk * slot_entries))) return rc;
-        if (int rc = ensure(h, s.path, size_t(chunk * slot_entries) * 4)) return rc;
+        if (int rc = ensure(h, s.labels, size_t(chunk * stride))) return rc;
+        if (int rc = ensure(h, s.path, size_t(chunk * stride) * 4)) return rc;
         if (qstring)
-            if (int rc = ensure(h, s.quals, size_t(chunk * slot_entries) * qual_bytes)) return rc;
+            if (int rc = ensure(h, s.quals, size_t(chunk * stride) * qual_bytes)) return rc;
         if (int rc = ensure(h, s.offsets, size_t(chunk) * 8)) return rc;
         if (int rc = ensure(h, s.lens, size_t(chunk) * 4)) return rc;
         if (int rc = ensure(h, s.status, size_t(chunk) * 4)) return rc;
-        if (int rc = ensure(h, s.cursor, 256)) return rc;
-        s.busy = false;
     }
-
     int which = 0;
     for (int64_t first = 0; first < n_reads; first += chunk, which ^= 1) {
         Slot& s = h->slot[which];
-        if (int rc = drain_slot(h, s, out)) return rc;
         const int64_t cnt = std::min(chunk, n_reads - first);
-        s.first = first;
-        s.count = cnt;
         FCTC_CUDA(h, cudaMemcpyAsync(s.post.p, post_host + first * n_rows * n_labels, size_t(cnt * read_bytes),
                                      cudaMemcpyHostToDevice, s.stream));
-        FCTC_CUDA(h, cudaMemsetAsync(s.cursor.p, 0, 8, s.stream));
         fctc::ViterbiParams p{};
         p.post = static_cast<const float*>(s.post.p); p.N = cnt; p.T = n_rows; p.C = n_labels;
         p.qstring = qstring; p.qscale = qscale; p.qbias = qbias; p.collapse = collapse_repeats;
         p.labels = static_cast<uint8_t*>(s.labels.p); p.quals = s.quals.p; p.qual_bytes = qual_bytes;
-        p.path = static_cast<int32_t*>(s.path.p); p.pool_cap = cnt * slot_entries;
+        p.path = static_cast<int32_t*>(s.path.p); p.slot_stride = stride; p.offset_base = first * stride;
         p.offsets = static_cast<int64_t*>(s.offsets.p); p.lens = static_cast<int32_t*>(s.lens.p);
-        p.status = static_cast<int32_t*>(s.status.p); p.cursor = static_cast<unsigned long long*>(s.cursor.p);
+        p.status = static_cast<int32_t*>(s.status.p);
         FCTC_CUDA(h, fctc::launch_viterbi(p, h->sm_count, s.stream, nullptr));
-        FCTC_CUDA(h, cudaMemcpyAsync(s.cursor_host, s.cursor.p, 8, cudaMemcpyDeviceToHost, s.stream));
+        const size_t ent = size_t(cnt * stride), o = size_t(first * stride);
+        FCTC_CUDA(h, cudaMemcpyAsync(labels + o, s.labels.p, ent, cudaMemcpyDeviceToHost, s.stream));
+        FCTC_CUDA(h, cudaMemcpyAsync(path + o, s.path.p, ent * 4, cudaMemcpyDeviceToHost, s.stream));
+        if (qstring)
+            FCTC_CUDA(h, cudaMemcpyAsync(static_cast<uint8_t*>(quals) + o * qual_bytes, s.quals.p, ent * qual_bytes,
+                                         cudaMemcpyDeviceToHost, s.stream));
         FCTC_CUDA(h, cudaMemcpyAsync(offsets + first, s.offsets.p, size_t(cnt) * 8, cudaMemcpyDeviceToHost, s.stream));
         FCTC_CUDA(h, cudaMemcpyAsync(lens + first, s.lens.p, size_t(cnt) * 4, cudaMemcpyDeviceToHost, s.stream));
         FCTC_CUDA(h, cudaMemcpyAsync(status + first, s.status.p, size_t(cnt) * 4, cudaMemcpyDeviceToHost, s.stream));
-        FCTC_CUDA(h, cudaEventRecord(s.done, s.stream));
-        s.busy = true;
     }
-    // drain in submission order: the slot used before the last one first
-    if (int rc = drain_slot(h, h->slot[which], out)) return rc;
-    if (int rc = drain_slot(h, h->slot[which ^ 1], out)) return rc;
     FCTC_CUDA(h, cudaStreamSynchronize(h->slot[0].stream));
     FCTC_CUDA(h, cudaStreamSynchronize(h->slot[1].stream));
-    if (pool_used) *pool_used = out.used;
-    if (out.overflow)
-        return fail(h, FCTC_E_CAPACITY, "result pool too small: %lld entries given (n_reads*round_up(n_rows,32) always suffices)",
-                    (long long)pool_capacity);
+    if (pool_used) *pool_used = n_reads * stride;
     return 0;
 }
 
-int fctc_viterbi_search(fctc_handle* h, const float* post_host, int64_t n_rows, int32_t n_labels,
-                        int64_t stride_row, int64_t stride_label, int32_t qstring, float qscale, float qbias,
-                        int32_t collapse_repeats, uint8_t* labels, uint32_t* quals, int64_t* path, int64_t capacity,
-                        int64_t* out_len) {
-    if (int rc = check_common(h, 1, n_rows, n_labels)) return rc;
-    if (!post_host || !out_len) return fail(h, FCTC_E_ARGUMENT, "null pointer");
-    FCTC_CUDA(h, cudaSetDevice(h->device));
-    const int64_t slot_entries = roundup32(n_rows);
+namespace {
+
+// Packs a strided [T, C] host view into the handle's pinned staging buffer, followed by room for
+// one read's results; returns the layout.
+struct SingleStage {
+    float* packed;
+    uint8_t* labels;
+    uint32_t* quals;
+    int32_t* path;
+    int64_t* off;
+    int32_t* len;
+    int32_t* st;
+    int64_t slot_entries;
+};
+
+int stage_single(fctc_handle* h, const float* post_host, int64_t n_rows, int32_t n_labels, int64_t stride_row,
+                 int64_t stride_label, SingleStage* S) {
+    const int64_t slot_entries = std::max<int64_t>(roundup32(n_rows), 32);
     const size_t post_bytes = size_t(n_rows) * n_labels * 4;
     const size_t lab_off = (post_bytes + 255) & ~size_t(255);
     const size_t qual_off = lab_off + size_t(slot_entries);
@@ -352,27 +408,186 @@ int fctc_viterbi_search(fctc_handle* h, const float* post_host, int64_t n_rows, 
     const size_t meta_off = path_off + size_t(slot_entries) * 4;
     if (int rc = ensure_pinned(h, meta_off + 64)) return rc;
     unsigned char* pin = static_cast<unsigned char*>(h->pinned);
-    float* packed = reinterpret_cast<float*>(pin);
+    S->packed = reinterpret_cast<float*>(pin);
     for (int64_t t = 0; t < n_rows; ++t)
-        for (int32_t c = 0; c < n_labels; ++c) packed[t * n_labels + c] = post_host[t * stride_row + c * stride_label];
-    int64_t* off1 = reinterpret_cast<int64_t*>(pin + meta_off);
-    int32_t* len1 = reinterpret_cast<int32_t*>(pin + meta_off + 8);
-    int32_t* st1 = reinterpret_cast<int32_t*>(pin + meta_off + 16);
+        for (int32_t c = 0; c < n_labels; ++c) S->packed[t * n_labels + c] = post_host[t * stride_row + c * stride_label];
+    S->labels = pin + lab_off;
+    S->quals = reinterpret_cast<uint32_t*>(pin + qual_off);
+    S->path = reinterpret_cast<int32_t*>(pin + path_off);
+    S->off = reinterpret_cast<int64_t*>(pin + meta_off);
+    S->len = reinterpret_cast<int32_t*>(pin + meta_off + 8);
+    S->st = reinterpret_cast<int32_t*>(pin + meta_off + 16);
+    S->slot_entries = slot_entries;
+    return 0;
+}
+
+}  // namespace
+
+int fctc_viterbi_search(fctc_handle* h, const float* post_host, int64_t n_rows, int32_t n_labels,
+                        int64_t stride_row, int64_t stride_label, int32_t qstring, float qscale, float qbias,
+                        int32_t collapse_repeats, uint8_t* labels, uint32_t* quals, int64_t* path, int64_t capacity,
+                        int64_t* out_len) {
+    if (int rc = check_common(h, 1, n_rows, n_labels)) return rc;
+    if (n_rows == 0) return fail(h, FCTC_E_ARGUMENT, "n_rows must be >= 1 (the reference asserts a non-empty matrix)");
+    if (!post_host || !out_len) return fail(h, FCTC_E_ARGUMENT, "null pointer");
+    FCTC_CUDA(h, cudaSetDevice(h->device));
+    SingleStage S;
+    if (int rc = stage_single(h, post_host, n_rows, n_labels, stride_row, stride_label, &S)) return rc;
     int64_t used = 0;
-    int rc = fctc_viterbi_batch(h, packed, 1, n_rows, n_labels, qstring, qscale, qbias, collapse_repeats, pin + lab_off,
-                                pin + qual_off, 4, reinterpret_cast<int32_t*>(pin + path_off), slot_entries, off1, len1,
-                                st1, &used);
+    int rc = fctc_viterbi_batch(h, S.packed, 1, n_rows, n_labels, qstring, qscale, qbias, collapse_repeats, S.labels,
+                                S.quals, 4, S.path, S.slot_entries, S.off, S.len, S.st, &used);
     if (rc < 0) return rc;
-    const int64_t len = *len1;
+    const int64_t len = *S.len, o = *S.off;
     *out_len = len;
     const int64_t m = std::min<int64_t>(len, capacity);
-    const int64_t o = *off1;
     for (int64_t i = 0; i < m; ++i) {
-        if (labels) labels[i] = pin[lab_off + o + i];
-        if (path) path[i] = reinterpret_cast<int32_t*>(pin + path_off)[o + i];
-        if (quals && qstring) quals[i] = reinterpret_cast<uint32_t*>(pin + qual_off)[o + i];
+        if (labels) labels[i] = S.labels[o + i];
+        if (path) path[i] = S.path[o + i];
+        if (quals && qstring) quals[i] = S.quals[o + i];
     }
-    return *st1;
+    return *S.st;
+}
+
+// ---------------------------------------------------------------------------------------------
+// 1-D beam search
+// ---------------------------------------------------------------------------------------------
+namespace fctc { bool beam_shape_supported(int beam_size, int C); }
+
+namespace {
+
+int check_beam(fctc_handle* h, int32_t n_labels, int32_t beam_size, float thr) {
+    if (beam_size <= 0) return fail(h, FCTC_E_ARGUMENT, "beam_size cannot be 0");                       // src/lib.rs:339-340
+    if (thr < -0.0f) return fail(h, FCTC_E_ARGUMENT, "beam_cut_threshold must be at least 0.0");         // :341-344
+    const float max_cut = 1.0f / float(n_labels);
+    if (thr >= max_cut) return fail(h, FCTC_E_ARGUMENT, "beam_cut_threshold cannot be more than %g", max_cut);  // :345-349
+    if (!fctc::beam_shape_supported(beam_size, n_labels))
+        return fail(h, FCTC_E_UNSUPPORTED, "beam_size %d x %d labels exceeds the per-warp shared-memory plan", beam_size,
+                    n_labels);
+    return 0;
+}
+
+}  // namespace
+
+int64_t fctc_beam_scratch_bytes(const fctc_handle* h, int64_t n_reads, int64_t n_rows, int32_t n_labels,
+                                int32_t beam_size, int32_t nodes_per_row) {
+    if (!h || n_labels <= 0 || beam_size <= 0) return 0;
+    return fctc::beam_scratch_bytes(h->sm_count, n_reads, n_rows, n_labels, beam_size, nodes_per_row, nullptr, nullptr);
+}
+
+int fctc_beam_search_batch_device(fctc_handle* h, const float* post_dev, int64_t n_reads, int64_t n_rows,
+                                  int32_t n_labels, int32_t beam_size, float beam_cut_threshold,
+                                  int32_t collapse_repeats, uint8_t* labels_dev, int32_t* path_dev,
+                                  int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev, int32_t* status_dev,
+                                  unsigned long long* pool_used_dev, void* scratch_dev, int64_t scratch_bytes,
+                                  int32_t nodes_per_row, void* stream) {
+    if (int rc = check_common(h, n_reads, n_rows, n_labels)) return rc;
+    if (int rc = check_beam(h, n_labels, beam_size, beam_cut_threshold)) return rc;
+    if (!post_dev || !labels_dev || !path_dev || !offsets_dev || !lens_dev || !status_dev || !pool_used_dev || !scratch_dev)
+        return fail(h, FCTC_E_ARGUMENT, "null device pointer");
+    if (reinterpret_cast<uintptr_t>(scratch_dev) & 255u) return fail(h, FCTC_E_ARGUMENT, "scratch_dev must be 256-byte aligned");
+    FCTC_CUDA(h, cudaSetDevice(h->device));
+    fctc::BeamParams p{};
+    int64_t need = fctc::beam_scratch_bytes(h->sm_count, n_reads, n_rows, n_labels, beam_size, nodes_per_row,
+                                            &p.nodes_per_slot, &p.n_slots);
+    if (scratch_bytes < need)
+        return fail(h, FCTC_E_CAPACITY, "beam scratch too small: %lld bytes given, %lld needed", (long long)scratch_bytes,
+                    (long long)need);
+    p.post = post_dev; p.N = n_reads; p.T = n_rows; p.C = n_labels; p.beam_size = beam_size;
+    p.threshold = beam_cut_threshold; p.collapse = collapse_repeats; p.labels = labels_dev; p.path = path_dev;
+    p.pool_cap = pool_capacity; p.offsets = offsets_dev; p.lens = lens_dev; p.status = status_dev;
+    p.cursor = pool_used_dev; p.scratch = scratch_dev; p.scratch_bytes = scratch_bytes;
+    p.ticket = static_cast<unsigned long long*>(scratch_dev);
+    FCTC_CUDA(h, fctc::launch_beam(p, h->sm_count, static_cast<cudaStream_t>(stream)));
+    return 0;
+}
+
+namespace {
+
+int beam_host_pass(fctc_handle* h, const float* post_host, int64_t n_reads, int64_t n_rows, int32_t n_labels,
+                   int32_t beam_size, float thr, int32_t collapse, int32_t nodes_per_row, HostOut& out) {
+    const int64_t slot_entries = std::max<int64_t>(roundup32(n_rows), 32);
+    const int64_t chunk = std::min<int64_t>(default_chunk_reads(n_rows * int64_t(n_labels) * 4), n_reads);
+    int64_t nodes_per_slot = 0;
+    int n_slots = 0;
+    const int64_t need = fctc::beam_scratch_bytes(h->sm_count, chunk, n_rows, n_labels, beam_size, nodes_per_row,
+                                                  &nodes_per_slot, &n_slots);
+    for (int i = 0; i < 2; ++i)
+        if (int rc = ensure(h, h->slot[i].scratch, size_t(need))) return rc;
+    auto launch = [&](Slot& s, int64_t cnt) -> int {
+        fctc::BeamParams p{};
+        fctc::beam_scratch_bytes(h->sm_count, cnt, n_rows, n_labels, beam_size, nodes_per_row, &p.nodes_per_slot, &p.n_slots);
+        p.post = static_cast<const float*>(s.post.p); p.N = cnt; p.T = n_rows; p.C = n_labels;
+        p.beam_size = beam_size; p.threshold = thr; p.collapse = collapse;
+        p.labels = static_cast<uint8_t*>(s.labels.p); p.path = static_cast<int32_t*>(s.path.p);
+        p.pool_cap = cnt * slot_entries; p.offsets = static_cast<int64_t*>(s.offsets.p);
+        p.lens = static_cast<int32_t*>(s.lens.p); p.status = static_cast<int32_t*>(s.status.p);
+        p.cursor = static_cast<unsigned long long*>(s.cursor.p); p.scratch = s.scratch.p;
+        p.scratch_bytes = int64_t(s.scratch.bytes); p.ticket = static_cast<unsigned long long*>(s.scratch.p);
+        FCTC_CUDA(h, fctc::launch_beam(p, h->sm_count, s.stream));
+        return 0;
+    };
+    return host_pipeline(h, post_host, n_reads, n_rows, n_labels, out, chunk, launch);
+}
+
+}  // namespace
+
+int fctc_beam_search_batch(fctc_handle* h, const float* post_host, int64_t n_reads, int64_t n_rows, int32_t n_labels,
+                           int32_t beam_size, float beam_cut_threshold, int32_t collapse_repeats, uint8_t* labels,
+                           int32_t* path, int64_t pool_capacity, int64_t* offsets, int32_t* lens, int32_t* status,
+                           int64_t* pool_used) {
+    if (int rc = check_common(h, n_reads, n_rows, n_labels)) return rc;
+    if (int rc = check_beam(h, n_labels, beam_size, beam_cut_threshold)) return rc;
+    if ((!post_host && n_rows > 0) || !labels || !path || !offsets || !lens || !status)
+        return fail(h, FCTC_E_ARGUMENT, "null host pointer");
+    FCTC_CUDA(h, cudaSetDevice(h->device));
+    if (pool_used) *pool_used = 0;
+    if (n_reads == 0) return 0;
+    HostOut out{labels, nullptr, 1, path, pool_capacity, offsets, lens, status};
+    if (int rc = beam_host_pass(h, post_host, n_reads, n_rows, n_labels, beam_size, beam_cut_threshold, collapse_repeats,
+                                0, out))
+        return rc;
+    if (!out.overflow) {
+        // reads whose trie outgrew the default pool: decode again, one at a time, with the hard
+        // bound of (n_labels-1)*beam_size proposals per row
+        const int32_t bound = std::max<int32_t>(1, (n_labels - 1) * beam_size);
+        for (int64_t n = 0; n < n_reads && !out.overflow; ++n) {
+            if (status[n] != FCTC_NODE_POOL_OVERFLOW) continue;
+            HostOut one{labels, nullptr, 1, path, pool_capacity, offsets + n, lens + n, status + n};
+            one.used = out.used;
+            if (int rc = beam_host_pass(h, post_host + n * n_rows * n_labels, 1, n_rows, n_labels, beam_size,
+                                        beam_cut_threshold, collapse_repeats, bound, one))
+                return rc;
+            out.used = one.used;
+            out.overflow = one.overflow;
+        }
+    }
+    if (pool_used) *pool_used = out.used;
+    if (out.overflow)
+        return fail(h, FCTC_E_CAPACITY, "result pool too small: %lld entries given (n_reads*round_up(n_rows,32) always suffices)",
+                    (long long)pool_capacity);
+    return 0;
+}
+
+int fctc_beam_search(fctc_handle* h, const float* post_host, int64_t n_rows, int32_t n_labels, int64_t stride_row,
+                     int64_t stride_label, int32_t beam_size, float beam_cut_threshold, int32_t collapse_repeats,
+                     uint8_t* labels, int64_t* path, int64_t capacity, int64_t* out_len) {
+    if (int rc = check_common(h, 1, n_rows, n_labels)) return rc;
+    if (!out_len || (!post_host && n_rows > 0)) return fail(h, FCTC_E_ARGUMENT, "null pointer");
+    FCTC_CUDA(h, cudaSetDevice(h->device));
+    SingleStage S;
+    if (int rc = stage_single(h, post_host, n_rows, n_labels, stride_row, stride_label, &S)) return rc;
+    int64_t used = 0;
+    int rc = fctc_beam_search_batch(h, S.packed, 1, n_rows, n_labels, beam_size, beam_cut_threshold, collapse_repeats,
+                                    S.labels, S.path, S.slot_entries, S.off, S.len, S.st, &used);
+    if (rc < 0) return rc;
+    const int64_t len = *S.len, o = *S.off;
+    *out_len = len;
+    const int64_t m = std::min<int64_t>(len, capacity);
+    for (int64_t i = 0; i < m; ++i) {
+        if (labels) labels[i] = S.labels[o + i];
+        if (path) path[i] = S.path[o + i];
+    }
+    return *S.st;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -382,8 +597,8 @@ int fctc_synth_posteriors_device(fctc_handle* h, float* post_dev, int64_t n_read
                                  int32_t kind, uint64_t seed, int64_t first_read, void* stream) {
     if (!h || !post_dev) return FCTC_E_ARGUMENT;
     FCTC_CUDA(h, cudaSetDevice(h->device));
-    cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : h->stream;
-    FCTC_CUDA(h, fctc::launch_synth(post_dev, n_reads, n_rows, n_labels, kind, seed, first_read, st));
+    FCTC_CUDA(h, fctc::launch_synth(post_dev, n_reads, n_rows, n_labels, kind, seed, first_read,
+                                    static_cast<cudaStream_t>(stream)));
     return 0;
 }
 
@@ -399,4 +614,3 @@ void fctc_host_log10f(const float* x, float* y, int64_t n) {
     for (int64_t i = 0; i < n; ++i) y[i] = fctc::glibc_log10f(x[i], invc, logc);
 }
 
-}  // extern "C"

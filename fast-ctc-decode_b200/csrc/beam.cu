@@ -1,12 +1,449 @@
-// TEMPORARY: beam-search entry points land in the next commit.
+// beam.cu — batched 1-D CTC prefix beam search for sm_100a: one warp per read.
+//
+// Replaces search::beam_search (src/search.rs:159-301) with its SearchPoint (:7-28), the prefix
+// trie tree::SuffixTree (src/tree.rs:17-194) and its child table vec2d::Vec2D (src/vec2d.rs).
+// The arithmetic is the reference's, operation for operation, in linear f32 probability space
+// (compiled with -fmad=false; '/' is IEEE division): expansion with the beam_cut_threshold prune
+// (blank uses '>', labels use "not <", src/search.rs:191,201), merge of hypotheses that reach the
+// same trie node, ranking by label_prob + gap_prob, cut to beam_size, renormalisation by the top
+// score, and a parent-pointer traceback that reports each label's first-proposal row.
+//
+// What is different is the organisation:
+//   * a read is owned by one warp for its whole life (the search is sequential in time, reads are
+//     independent); warps take reads from an atomic ticket counter;
+//   * the beam lives in shared memory (two buffers of B entries per warp), posterior rows are
+//     prefetched into a shared-memory ring 32 rows ahead;
+//   * the trie is a per-warp node pool in HBM scratch: {parent, first-proposal row} records, a
+//     label byte and a child table row per node, ids in creation order exactly as the reference
+//     allocates them (beam rank major, label minor) so that tie-breaks by node id agree;
+//   * merging needs no sort: a node can only receive its own blank/repeat continuation and its
+//     parent's extension (<= 2 non-zero terms per field, so f32 addition order is immaterial);
+//     each hypothesis looks up its parent in the beam and folds that term in itself;
+//   * ranking is a warp-level selection: lanes keep their best unselected candidate, two
+//     REDUX.MAX per rank pick (score, then lowest node id) — no comparison sort.
+#include "device_utils.cuh"
+#include "kernels.h"
+
 #include "../../include/fctc.h"
-extern "C" {
-int64_t fctc_beam_scratch_bytes(const fctc_handle*, int64_t, int64_t, int32_t, int32_t, int32_t) { return 0; }
-int fctc_beam_search_batch_device(fctc_handle*, const float*, int64_t, int64_t, int32_t, int32_t, float, int32_t, uint8_t*,
-                                  int32_t*, int64_t, int64_t*, int32_t*, int32_t*, unsigned long long*, void*, int64_t,
-                                  int32_t, void*) { return FCTC_E_UNSUPPORTED; }
-int fctc_beam_search_batch(fctc_handle*, const float*, int64_t, int64_t, int32_t, int32_t, float, int32_t, uint8_t*,
-                           int32_t*, int64_t, int64_t*, int32_t*, int32_t*, int64_t*) { return FCTC_E_UNSUPPORTED; }
-int fctc_beam_search(fctc_handle*, const float*, int64_t, int32_t, int64_t, int64_t, int32_t, float, int32_t, uint8_t*,
-                     int64_t*, int64_t, int64_t*) { return FCTC_E_UNSUPPORTED; }
+
+namespace fctc {
+
+constexpr int BM_WARPS = 4;  // warps (= reads in flight) per CTA
+constexpr int BM_THREADS = BM_WARPS * 32;
+constexpr int BM_ROWBUF = 256;  // floats per prefetch buffer
+constexpr unsigned FULL = 0xffffffffu;
+constexpr int ROOT = -1;
+
+// Trie pool of one warp slot in scratch: records, child table, label bytes; each 256-byte aligned.
+__host__ __device__ inline size_t up256(size_t v) { return (v + 255) & ~size_t(255); }
+__host__ __device__ inline size_t beam_slot_child_offset(long long cap) { return up256((size_t)cap * 8); }
+__host__ __device__ inline size_t beam_slot_label_offset(long long cap, int NL) {
+    return beam_slot_child_offset(cap) + up256((size_t)cap * 4 * (size_t)(NL > 0 ? NL : 1));
 }
+__host__ __device__ inline size_t beam_slot_bytes(long long cap, int NL) {
+    return beam_slot_label_offset(cap, NL) + up256((size_t)cap);
+}
+
+struct BeamLayout {  // per-warp shared memory plan, in bytes from the warp's base
+    int beam_stride;  // one beam buffer: 6 arrays of B words
+    int off_newcnt, off_fold, off_key, off_node, off_lp, off_gp, off_src, off_sel, off_rows, off_root;
+    int warp_bytes;
+    int rows_per_chunk;
+};
+
+__device__ __forceinline__ uint32_t order_key(float v) {  // monotone map f32 -> u32, >= 1 for non-NaN
+    uint32_t u = __float_as_uint(v);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+struct BeamView {  // one beam buffer
+    int* nd;
+    int* par;
+    int* dep;
+    int* tip;
+    float* lp;
+    float* gp;
+};
+__device__ __forceinline__ BeamView beam_view(unsigned char* base, int B) {
+    BeamView v;
+    v.nd = reinterpret_cast<int*>(base);
+    v.par = v.nd + B;
+    v.dep = v.par + B;
+    v.tip = v.dep + B;
+    v.lp = reinterpret_cast<float*>(v.tip + B);
+    v.gp = v.lp + B;
+    return v;
+}
+
+__global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParams p, const BeamLayout L) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int slot = blockIdx.x * BM_WARPS + warp;
+    if (slot >= p.n_slots) return;
+    unsigned char* ws = smem + (size_t)warp * L.warp_bytes;
+    const int B = p.beam_size, C = p.C, NL = C - 1;
+    const long long T = p.T;
+    const float thr = p.threshold;
+    const bool collapse = p.collapse != 0;
+
+    int* newcnt = reinterpret_cast<int*>(ws + L.off_newcnt);
+    unsigned char* fold = ws + L.off_fold;
+    uint32_t* ckey = reinterpret_cast<uint32_t*>(ws + L.off_key);
+    int* cnode = reinterpret_cast<int*>(ws + L.off_node);
+    float* clp = reinterpret_cast<float*>(ws + L.off_lp);
+    float* cgp = reinterpret_cast<float*>(ws + L.off_gp);
+    int* sel = reinterpret_cast<int*>(ws + L.off_sel);
+    float* rowbuf = reinterpret_cast<float*>(ws + L.off_rows);
+    int* root_child = reinterpret_cast<int*>(ws + L.off_root);
+
+    // this warp's trie pool
+    const long long cap = p.nodes_per_slot;
+    unsigned char* pool = static_cast<unsigned char*>(p.scratch) + 256 + (size_t)slot * beam_slot_bytes(cap, NL);
+    int2* rec = reinterpret_cast<int2*>(pool);                                  // {parent, first-proposal row}
+    int* child = reinterpret_cast<int*>(pool + beam_slot_child_offset(cap));    // [node][label] -> node | -1
+    uint8_t* nlab = reinterpret_cast<uint8_t*>(pool + beam_slot_label_offset(cap, NL));
+
+    const int R = L.rows_per_chunk;  // rows per prefetch chunk, R*C <= BM_ROWBUF
+    const int chunk_elems = R * C;
+
+    for (int i = lane; i < B * NL; i += 32) fold[i] = 0;
+
+    for (;;) {
+        unsigned long long ticket = 0;
+        if (lane == 0) ticket = atomicAdd(p.ticket, 1ull);
+        ticket = __shfl_sync(FULL, ticket, 0);
+        if (ticket >= (unsigned long long)p.N) break;
+        const long long n = (long long)ticket;
+        const float* rd = p.post + n * T * C;
+
+        int cur = 0;
+        BeamView bv = beam_view(ws, B);
+        if (lane == 0) {  // src/search.rs:170-175
+            bv.nd[0] = ROOT; bv.par[0] = -2; bv.dep[0] = 0; bv.tip[0] = -1; bv.lp[0] = 0.0f; bv.gp[0] = 1.0f;
+        }
+        for (int l = lane; l < NL; l += 32) root_child[l] = -1;
+        int nbeam = 1;
+        long long n_nodes = 0;
+        int status = FCTC_OK;
+
+        // prefetch chunk 0 of the posterior rows
+        float pre[BM_ROWBUF / 32];
+        {
+            const long long total = T * C;
+#pragma unroll
+            for (int j = 0; j < BM_ROWBUF / 32; ++j) {
+                const int e = lane + 32 * j;
+                pre[j] = (e < chunk_elems && e < total) ? __ldg(rd + e) : 0.0f;
+            }
+        }
+        __syncwarp();
+
+        for (long long t0 = 0; t0 < T && status == FCTC_OK; t0 += R) {
+            float* rows = rowbuf + ((t0 / R) & 1) * BM_ROWBUF;
+#pragma unroll
+            for (int j = 0; j < BM_ROWBUF / 32; ++j) {
+                const int e = lane + 32 * j;
+                if (e < chunk_elems) rows[e] = pre[j];
+            }
+            {   // start loading the next chunk; it lands while this one is processed
+                const long long base = (t0 + R) * C, total = T * C;
+#pragma unroll
+                for (int j = 0; j < BM_ROWBUF / 32; ++j) {
+                    const long long e = base + lane + 32 * j;
+                    pre[j] = (lane + 32 * j < chunk_elems && e < total) ? __ldg(rd + e) : 0.0f;
+                }
+            }
+            __syncwarp();
+            const int rows_here = int((T - t0 < R) ? (T - t0) : R);
+
+            for (int rr = 0; rr < rows_here && status == FCTC_OK; ++rr) {
+                const long long t = t0 + rr;
+                const float* pr = rows + rr * C;
+                const float p_blank = pr[0];
+                BeamView nb = beam_view(ws + (cur ^ 1) * L.beam_stride, B);
+
+                // ---- phase A: each hypothesis' own continuation, plus its parent's extension -------
+                for (int b = lane; b < nbeam; b += 32) {
+                    const int node = bv.nd[b];
+                    const float lp = bv.lp[b], gp = bv.gp[b];
+                    const int tip = bv.tip[b];
+                    bool has_self = false;
+                    float s_lp = 0.0f, s_gp = 0.0f;
+                    if (p_blank > thr) {  // src/search.rs:191-198
+                        s_gp = __fmul_rn(__fadd_rn(lp, gp), p_blank);
+                        has_self = true;
+                    }
+                    if (collapse && tip >= 0) {  // src/search.rs:205-211
+                        const float pt = pr[tip + 1];
+                        if (!(pt < thr)) {
+                            s_lp = __fmul_rn(lp, pt);
+                            has_self = true;
+                        }
+                    }
+                    if (has_self && node != ROOT) {
+                        // is my trie parent in the beam?  then its extension by my label lands on me
+                        const int mypar = bv.par[b];
+                        int r = -1;
+                        for (int k = 0; k < nbeam; ++k)
+                            if (bv.nd[k] == mypar) r = k;
+                        if (r >= 0) {
+                            const float pt = pr[tip + 1];
+                            if (!(pt < thr)) {
+                                const float plp = bv.lp[r], pgp = bv.gp[r];
+                                float c;
+                                if (collapse && bv.tip[r] == tip) c = __fmul_rn(pgp, pt);      // :220-226
+                                else c = __fmul_rn(__fadd_rn(plp, pgp), pt);                   // :233-238
+                                s_lp = __fadd_rn(s_lp, c);                                       // :251
+                                fold[r * NL + tip] = 1;
+                            }
+                        }
+                    }
+                    const int s0 = b * C;
+                    cnode[s0] = node;
+                    clp[s0] = s_lp;
+                    cgp[s0] = s_gp;
+                    ckey[s0] = has_self ? 1u : 0u;  // real key is filled in after the merge
+                }
+                __syncwarp();
+
+                // ---- phase B1: child proposals; new nodes get provisional ids -2-k ----------------
+                for (int b = lane; b < nbeam; b += 32) {
+                    const int node = bv.nd[b];
+                    const float lp = bv.lp[b], gp = bv.gp[b];
+                    const int tip = bv.tip[b];
+                    int n_new = 0;
+                    for (int l = 0; l < NL; ++l) {
+                        const int s = b * C + 1 + l;
+                        const float pl = pr[l + 1];
+                        uint32_t key = 0;
+                        if (!(pl < thr)) {  // src/search.rs:201-203
+                            const bool repeat = collapse && l == tip;
+                            int x = (node == ROOT) ? root_child[l] : child[(size_t)node * NL + l];
+                            bool take = true;
+                            if (x < 0) {
+                                if (repeat && !(gp > 0.0f)) take = false;  // src/search.rs:212-218
+                                else x = -2 - (n_new++);
+                            } else if (fold[b * NL + l]) {
+                                fold[b * NL + l] = 0;  // merged into the child's own entry in phase A
+                                take = false;
+                            }
+                            if (take) {
+                                const float v = repeat ? __fmul_rn(gp, pl) : __fmul_rn(__fadd_rn(lp, gp), pl);
+                                cnode[s] = x;
+                                clp[s] = v;
+                                cgp[s] = 0.0f;
+                                key = 1u;
+                            }
+                        }
+                        ckey[s] = key;
+                    }
+                    newcnt[b] = n_new;
+                }
+                __syncwarp();
+
+                // ---- exclusive scan of the new-node counts in beam order (node ids = creation order) --
+                int total_new = 0;
+                for (int b0 = 0; b0 < nbeam; b0 += 32) {
+                    const int b = b0 + lane;
+                    const int v = (b < nbeam) ? newcnt[b] : 0;
+                    const int inc = warp_inclusive_scan(v, lane);
+                    if (b < nbeam) newcnt[b] = total_new + inc - v;
+                    total_new += __shfl_sync(FULL, inc, 31);
+                }
+                if (n_nodes + total_new > cap) {
+                    status = FCTC_NODE_POOL_OVERFLOW;
+                    break;
+                }
+                __syncwarp();
+
+                // ---- phase B2: materialise the new nodes, compute ranking keys ---------------------
+                bool any_nan = false;
+                int n_cand = 0;
+                for (int b = lane; b < nbeam; b += 32) {
+                    const int node = bv.nd[b];
+                    const int base = int(n_nodes) + newcnt[b];
+                    for (int sl = 0; sl < C; ++sl) {
+                        const int s = b * C + sl;
+                        if (ckey[s] == 0u) continue;
+                        if (sl > 0 && cnode[s] <= -2) {
+                            const int l = sl - 1;
+                            const int id = base + (-2 - cnode[s]);
+                            cnode[s] = id;
+                            rec[id] = make_int2(node, int(t));  // src/tree.rs:138-142, data = idx
+                            nlab[id] = uint8_t(l);
+                            for (int j = 0; j < NL; ++j) child[(size_t)id * NL + j] = -1;  // src/tree.rs:143
+                            if (node == ROOT) root_child[l] = id;
+                            else child[(size_t)node * NL + l] = id;
+                        }
+                        const float tot = __fadd_rn(__fadd_rn(clp[s], cgp[s]), 0.0f);  // probability(), -0 -> +0
+                        if (tot != tot) any_nan = true;
+                        ckey[s] = (tot != tot) ? 1u : order_key(tot);
+                        ++n_cand;
+                    }
+                }
+                n_nodes += total_new;
+                n_cand = __reduce_add_sync(FULL, n_cand);
+                any_nan = __any_sync(FULL, any_nan);
+                __syncwarp();
+                if (n_cand >= 2 && any_nan) {  // src/search.rs:261-272 (see oracle note on n >= 2)
+                    status = FCTC_INCOMPARABLE_VALUES;
+                    break;
+                }
+                if (n_cand == 0) {  // src/search.rs:274-277
+                    status = FCTC_RAN_OUT_OF_BEAM;
+                    break;
+                }
+
+                // ---- ranking: select the best min(B, n_cand) candidates in order --------------------
+                const int n_slots_c = nbeam * C;
+                const int n_keep = n_cand < B ? n_cand : B;
+                uint32_t best_hi = 0, best_lo = 0;
+                int best_i = -1;
+                auto rescan = [&]() {
+                    best_hi = 0; best_lo = 0; best_i = -1;
+                    for (int i = lane; i < n_slots_c; i += 32) {
+                        const uint32_t k = ckey[i];
+                        if (k == 0u) continue;
+                        const uint32_t lo = 0x7FFFFFFFu - uint32_t(cnode[i]);  // lower node id ranks first
+                        if (k > best_hi || (k == best_hi && lo > best_lo)) { best_hi = k; best_lo = lo; best_i = i; }
+                    }
+                };
+                rescan();
+                for (int r = 0; r < n_keep; ++r) {
+                    const uint32_t m1 = __reduce_max_sync(FULL, best_hi);
+                    const uint32_t m2 = __reduce_max_sync(FULL, best_hi == m1 ? best_lo : 0u);
+                    if (best_hi == m1 && best_lo == m2) {
+                        sel[r] = best_i;
+                        ckey[best_i] = 0u;
+                        rescan();
+                    }
+                }
+                __syncwarp();
+
+                // ---- new beam, renormalised by the top score (src/search.rs:278-282) -----------------
+                const int i0 = sel[0];
+                const float top = __fadd_rn(clp[i0], cgp[i0]);
+                for (int r = lane; r < n_keep; r += 32) {
+                    const int i = sel[r];
+                    const int b = i / C, sl = i - b * C;
+                    nb.nd[r] = cnode[i];
+                    nb.lp[r] = clp[i] / top;
+                    nb.gp[r] = cgp[i] / top;
+                    if (sl == 0) { nb.par[r] = bv.par[b]; nb.dep[r] = bv.dep[b]; nb.tip[r] = bv.tip[b]; }
+                    else { nb.par[r] = bv.nd[b]; nb.dep[r] = bv.dep[b] + 1; nb.tip[r] = sl - 1; }
+                }
+                __syncwarp();
+                cur ^= 1;
+                bv = nb;
+                nbeam = n_keep;
+            }
+        }
+        if (status != FCTC_OK) {
+            // leave the fold flags clean for the next read
+            for (int i = lane; i < B * NL; i += 32) fold[i] = 0;
+        }
+        __syncwarp();
+
+        // ---- traceback (src/search.rs:285-300) -----------------------------------------------------
+        if (lane == 0) {
+            int len = 0;
+            long long off = 0;
+            if (status == FCTC_OK) {
+                len = bv.dep[0];
+                const unsigned long long want = (unsigned long long)((len + 31) & ~31);
+                const unsigned long long o = atomicAdd(p.cursor, want);
+                if (o + want > (unsigned long long)p.pool_cap) {
+                    status = FCTC_OUTPUT_OVERFLOW;
+                    len = 0;
+                } else {
+                    off = (long long)o;
+                    int node = bv.nd[0];
+                    for (int k = len - 1; k >= 0; --k) {
+                        const int2 rc = rec[node];
+                        p.labels[off + k] = uint8_t(nlab[node] + 1);
+                        p.path[off + k] = rc.y;
+                        node = rc.x;
+                    }
+                }
+            }
+            p.offsets[n] = off;
+            p.lens[n] = len;
+            p.status[n] = status;
+        }
+        __syncwarp();
+    }
+}
+
+static bool plan_beam(int B, int C, BeamLayout* L) {
+    const int NL = C - 1;
+    auto up = [](long long v, int a) { return (v + a - 1) / a * a; };
+    long long o = 0;
+    L->beam_stride = int(up(6LL * 4 * B, 16));
+    o = 2LL * L->beam_stride;
+    L->off_newcnt = int(o); o = up(o + 4LL * B, 16);
+    L->off_fold = int(o);   o = up(o + (long long)B * (NL > 0 ? NL : 1), 16);
+    const long long nc = (long long)B * C;
+    L->off_key = int(o);    o = up(o + 4 * nc, 16);
+    L->off_node = int(o);   o = up(o + 4 * nc, 16);
+    L->off_lp = int(o);     o = up(o + 4 * nc, 16);
+    L->off_gp = int(o);     o = up(o + 4 * nc, 16);
+    L->off_src = int(o);
+    L->off_sel = int(o);    o = up(o + 4LL * B, 16);
+    L->off_rows = int(o);   o = up(o + 2LL * BM_ROWBUF * 4, 16);
+    L->off_root = int(o);   o = up(o + 4LL * (NL > 0 ? NL : 1), 16);
+    L->warp_bytes = int(up(o, 128));
+    int R = BM_ROWBUF / C;
+    if (R > 32) R = 32;
+    if (R < 1) R = 1;
+    L->rows_per_chunk = R;
+    return o * BM_WARPS <= 200 * 1024 && C <= BM_ROWBUF;
+}
+
+static int default_nodes_per_row(int C, int B) {
+    const long long bound = (long long)(C - 1) * B;  // at most (C-1) proposals per hypothesis per row
+    // measured on synthetic posteriors: ~7 proposals per row at beam 5 / threshold 0.1, ~40-68 at
+    // beam 32 / threshold 0 (of a bound of 128); reads that need more are flagged and retried
+    long long d = 3LL * B;
+    if (d < 32) d = 32;
+    if (d > bound) d = bound;
+    if (d < 1) d = 1;
+    return int(d);
+}
+
+int64_t beam_scratch_bytes(int sm_count, int64_t N, int64_t T, int C, int beam_size, int nodes_per_row,
+                           int64_t* nodes_per_slot, int* n_slots) {
+    if (nodes_per_row <= 0) nodes_per_row = default_nodes_per_row(C, beam_size);
+    const long long bound = (long long)(C - 1) * beam_size;
+    if (nodes_per_row > bound) nodes_per_row = int(bound > 0 ? bound : 1);
+    long long slots = (long long)sm_count * 16;
+    if (slots > N) slots = N;
+    if (slots < 1) slots = 1;
+    slots = (slots + BM_WARPS - 1) / BM_WARPS * BM_WARPS;
+    const long long cap = (long long)nodes_per_row * (T > 0 ? T : 1);
+    const long long per_slot = (long long)beam_slot_bytes(cap, C - 1);
+    if (nodes_per_slot) *nodes_per_slot = cap;
+    if (n_slots) *n_slots = int(slots);
+    return 256 + slots * per_slot;
+}
+
+cudaError_t launch_beam(const BeamParams& p, int sm_count, cudaStream_t stream) {
+    (void)sm_count;
+    if (p.N <= 0) return cudaSuccess;
+    BeamLayout L;
+    if (!plan_beam(p.beam_size, p.C, &L)) return cudaErrorInvalidConfiguration;
+    const int smem = L.warp_bytes * BM_WARPS;
+    cudaError_t e = cudaFuncSetAttribute(beam_search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    e = cudaMemsetAsync(p.ticket, 0, sizeof(unsigned long long), stream);
+    if (e != cudaSuccess) return e;
+    const int grid = p.n_slots / BM_WARPS;
+    beam_search_kernel<<<grid, BM_THREADS, smem, stream>>>(p, L);
+    return cudaGetLastError();
+}
+
+bool beam_shape_supported(int beam_size, int C) {
+    BeamLayout L;
+    return plan_beam(beam_size, C, &L);
+}
+
+}  // namespace fctc

@@ -12,15 +12,15 @@ struct ViterbiParams {
     int qstring;
     float qscale, qbias;
     int collapse;
-    uint8_t* labels;  // result pool
+    uint8_t* labels;  // result pool in slot form: read n owns [n*slot_stride, n*slot_stride + lens[n])
     void* quals;      // uint8_t* or uint32_t* (qual_bytes)
     int qual_bytes;
     int32_t* path;
-    int64_t pool_cap;
-    int64_t* offsets;  // [N]
-    int32_t* lens;     // [N]
-    int32_t* status;   // [N]
-    unsigned long long* cursor;
+    int64_t slot_stride;  // round_up(T, 32)
+    int64_t offset_base;  // offsets[n] = offset_base + n*slot_stride (lets a chunk report global offsets)
+    int64_t* offsets;     // [N]
+    int32_t* lens;        // [N]
+    int32_t* status;      // [N]
 };
 
 // Chooses the streaming (bulk-async staged) kernel when the shape allows it, else the generic

@@ -6,17 +6,24 @@
 // repeat collapse, emission row ("path"), and one quality character per emitted label from the
 // *sequential* f32 mean of the winning probabilities over the label's run (src/search.rs:362-365
 // accumulates in time order; a tree reduction would round differently, so each run is summed by
-// one thread in row order).
+// one lane in row order).
 //
-// Memory-bound streaming kernel (20 B/row at C = 5):
-//   * persistent CTAs (SM count x resident CTAs), each walking reads blockIdx.x, +gridDim.x, ...
-//   * posterior rows are staged through shared memory by the TMA engine: 1-D bulk async copies
-//     (cp.async.bulk -> UBLKCP) of 1024-row tiles into an N-stage ring, completion on mbarriers;
-//     the ring runs ahead across read boundaries, so HBM requests are always in flight
-//   * each thread owns 4 consecutive rows: 5 x LDS.128 (80 B, bank-conflict free), 4 argmaxes
-//   * emission flags -> warp-shuffle scan + cross-warp sums give output positions
-//   * a read's labels / qualities / path are collected in shared memory and written out once,
-//     coalesced, into a pool slot obtained with a single atomicAdd per read.
+// Memory-bound streaming kernel (20 B/row at C = 5).  Every warp is autonomous:
+//   * a warp owns whole reads (read = gw, gw + #warps, ...), so no block-level barrier exists
+//     anywhere in the steady state;
+//   * its posterior rows are staged through shared memory by the TMA engine: 1-D bulk async
+//     copies (cp.async.bulk -> UBLKCP) of 32*RPL-row tiles into a per-warp ring of stages,
+//     completion counted on mbarriers; the ring runs ahead across read boundaries, so every warp
+//     always has several HBM requests in flight;
+//   * each lane owns RPL consecutive rows of a tile: 5 x LDS.128 (80 B, bank-conflict free) for
+//     C = 5, then RPL argmaxes in registers;
+//   * emission flags -> warp-shuffle scan -> output positions; records go straight to the read's
+//     slot in the result pool (slot n starts at n * round_up(T, 32): deterministic placement, no
+//     atomics, no second pass);
+//   * quality: the run mean is summed sequentially in shared memory; the phred character uses a
+//     MUFU.LG2 fast path whose result is only trusted when it is provably on the same side of
+//     every rounding boundary as glibc's log10f, else the exact binary64 re-evaluation of glibc's
+//     algorithm (phred.cuh) decides.
 #include "device_utils.cuh"
 #include "kernels.h"
 #include "phred.cuh"
@@ -25,34 +32,45 @@
 
 namespace fctc {
 
-constexpr int VT_THREADS = 256;
-constexpr int VT_RPT = 4;  // rows per thread
-constexpr int VT_TILE = VT_THREADS * VT_RPT;
-constexpr int VT_WARPS = VT_THREADS / 32;
-constexpr int VT_MAX_STAGES = 4;
+constexpr unsigned FULLMASK = 0xffffffffu;
+constexpr int VW_WARPS = 4;  // warps per CTA of the streaming kernel
+constexpr int VW_THREADS = VW_WARPS * 32;
+constexpr int VW_MAX_STAGES = 8;
 constexpr int VT_SMEM_LIMIT = 227 * 1024;
 
 __constant__ double c_logf_invc[16] = FCTC_LOGF_INVC;
 __constant__ double c_logf_logc[16] = FCTC_LOGF_LOGC;
 
-struct RunCarry {  // a label run that reaches the end of a tile and may continue in the next one
-    int active;
-    int label;
-    float sum;
-    int count;
-    int idx;  // output slot whose quality is still pending
-};
+// ---------------------------------------------------------------------------------------------
+// Quality character.  Fast path: q from MUFU.LG2; it differs from the reference's float
+// evaluation (glibc log10f, three rounded f32 ops) by at most
+//     D <= 6e-6*|qscale| + 4e-7*(|q - qbias| + |q|)
+// (2 ulp of lg2 at |lg2 p| <= 128, times 3.0103, plus the roundings on both sides).  If q is
+// farther than eps >> D from every k + 0.5 boundary, both round to the same integer and the
+// fast result is exact; otherwise (about 0.2 % of labels) the binary64 path decides.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool phred_fast(float mean, float qscale, float qbias, uint32_t* code) {
+    const float miss = __fadd_rn(1.0f, -mean);
+    const float pm = (miss < 1e-4f) ? 1e-4f : miss;
+    const float l2 = __log2f(pm);
+    const float a = __fmul_rn(__fmul_rn(-3.0102999566f, l2), qscale);
+    const float q = __fadd_rn(a, qbias);
+    const float eps = 1e-3f * fabsf(qscale) + 1e-5f * (fabsf(a) + fabsf(q)) + 1e-6f;
+    const float fr = q - floorf(q);
+    if (!(fabsf(fr - 0.5f) > eps)) return false;  // also catches NaN / inf / huge |q|
+    *code = saturating_u32(rintf(q)) + 33u;
+    return true;
+}
 
-struct TileShared {  // double-buffered by tile parity so that one tile needs only two barriers
-    uint32_t lab32[2][VT_THREADS];  // 4 labels per word: byte r = row 4*tid + r
-    float4 prob4[2][VT_THREADS];    // winning probability of the same 4 rows
-    int wsum[2][VT_WARPS];
-    RunCarry carry[2];
-    double invc[16];
-    double logc[16];
-    long long off;
-    int flag;
-};
+template <typename QT>
+__device__ __forceinline__ QT quality_char(float sum, int n, float qscale, float qbias, const double* invc,
+                                           const double* logc, bool& bad_char) {
+    const float mean = (n == 1) ? sum : sum / float(n);  // x / 1 == x; IEEE division otherwise (src/search.rs:350)
+    uint32_t code;
+    if (!phred_fast(mean, qscale, qbias, &code)) code = phred_code(mean, qscale, qbias, invc, logc);
+    if (sizeof(QT) == 4 && !is_unicode_scalar(code)) bad_char = true;
+    return QT(code);
+}
 
 __device__ __forceinline__ void argmax_row5(const float* f, int& arg, float& best) {
     best = f[0];
@@ -62,145 +80,52 @@ __device__ __forceinline__ void argmax_row5(const float* f, int& arg, float& bes
         if (f[c] > best) { best = f[c]; arg = c; }
 }
 
-template <typename QT>
-__device__ __forceinline__ QT finish_quality(TileShared& S, float sum, int n, float qscale, float qbias) {
-    float mean = sum / float(n);  // IEEE division (no fast-math), as src/search.rs:350
-    uint32_t code = phred_code(mean, qscale, qbias, S.invc, S.logc);
-    if (sizeof(QT) == 4 && !is_unicode_scalar(code)) S.flag = 1;
-    return QT(code);
-}
-
-// One 1024-row tile whose labels / winning probabilities are already in S.lab32[buf] /
-// S.prob4[buf] (and a __syncthreads() has been passed).  Returns the number of labels emitted by
-// the tile; their records go to out_*[base_count ...].
-template <typename QT>
-__device__ __forceinline__ int process_tile(TileShared& S, int buf, int tid, bool first_tile, bool last_tile,
-                                            int row0, uint32_t my_lab4, const float (&my_prob)[VT_RPT],
-                                            int base_count, bool collapse, bool qstring, float qscale, float qbias,
-                                            uint8_t* out_lab, QT* out_qual, int* out_path) {
-    const int lane = tid & 31, warp = tid >> 5;
-    const uint8_t* labs = reinterpret_cast<const uint8_t*>(S.lab32[buf]);
-    const float* probs = reinterpret_cast<const float*>(S.prob4[buf]);
-
-    int prev = 0;
-    bool prev_valid = true;
-    if (tid > 0) prev = labs[VT_RPT * tid - 1];
-    else if (!first_tile) prev = reinterpret_cast<const uint8_t*>(S.lab32[buf ^ 1])[VT_TILE - 1];
-    else prev_valid = false;  // last_label = None, src/search.rs:337
-
-    int lab[VT_RPT];
-    bool em[VT_RPT];
-    int cnt = 0;
-#pragma unroll
-    for (int r = 0; r < VT_RPT; ++r) {
-        lab[r] = int((my_lab4 >> (8 * r)) & 0xffu);
-        em[r] = lab[r] != 0 && (!collapse || !prev_valid || lab[r] != prev);  // src/search.rs:347
-        prev = lab[r];
-        prev_valid = true;
-        cnt += em[r] ? 1 : 0;
-    }
-    const int incl = warp_inclusive_scan(cnt, lane);
-    if (lane == 31) S.wsum[buf][warp] = incl;
-    __syncthreads();
-    int wbase = 0, total = 0;
-#pragma unroll
-    for (int w = 0; w < VT_WARPS; ++w) {
-        int s = S.wsum[buf][w];
-        if (w < warp) wbase += s;
-        total += s;
-    }
-    int pos = base_count + wbase + incl - cnt;
-
-#pragma unroll
-    for (int r = 0; r < VT_RPT; ++r) {
-        if (!em[r]) continue;
-        const int idx = pos++;
-        out_lab[idx] = uint8_t(lab[r]);
-        out_path[idx] = row0 + VT_RPT * tid + r;
-        if (qstring) {
-            float sum = fadd(0.0f, my_prob[r]);  // label_prob_total starts at 0.0, src/search.rs:339,354
-            int n = 1;
-            bool open = false;
-            if (collapse) {  // without collapse every non-blank row is its own run
-                int r2 = VT_RPT * tid + r + 1;
-                while (r2 < VT_TILE && labs[r2] == lab[r]) {
-                    sum = fadd(sum, probs[r2]);
-                    ++n;
-                    ++r2;
-                }
-                open = (r2 == VT_TILE) && !last_tile;
-            }
-            if (open) S.carry[buf] = RunCarry{1, lab[r], sum, n, idx};
-            else out_qual[idx] = finish_quality<QT>(S, sum, n, qscale, qbias);
-        }
-    }
-    // a run carried in from the previous tile of this read: continue it in row order
-    if (qstring && tid == 0 && !first_tile) {
-        const RunCarry c = S.carry[buf ^ 1];
-        if (c.active) {
-            float sum = c.sum;
-            int n = c.count;
-            int r2 = 0;
-            while (r2 < VT_TILE && labs[r2] == c.label) {
-                sum = fadd(sum, probs[r2]);
-                ++n;
-                ++r2;
-            }
-            if (r2 == VT_TILE && !last_tile) S.carry[buf] = RunCarry{1, c.label, sum, n, c.idx};
-            else out_qual[c.idx] = finish_quality<QT>(S, sum, n, qscale, qbias);
-        }
-    }
-    return total;
-}
-
-// Pool slot for one read: one atomicAdd, rounded up to 32 entries so that every array of the
-// slot starts on a 32-byte sector (128 bytes for path) and 16-byte vector stores may overrun
-// `len` inside the slot.
-__device__ __forceinline__ long long reserve_slot(const ViterbiParams& p, int len) {
-    unsigned long long want = (unsigned long long)((len + 31) & ~31);
-    unsigned long long off = atomicAdd(p.cursor, want);
-    return (off + want <= (unsigned long long)p.pool_cap) ? (long long)off : -1;
-}
-
-// ------------------------------------------------------------------------------------------
-// Streaming kernel.
-// ------------------------------------------------------------------------------------------
-struct StreamLayout {
+struct WarpLayout {  // shared memory plan of the streaming kernel (bytes)
     int nstage;
     int stage_bytes;
-    int out_lab_bytes, out_qual_bytes, out_path_bytes;
-    int total_bytes;
+    int off_stage;   // from the warp's base
+    int off_lab;     // TILE label bytes
+    int off_prob;    // TILE floats
+    int warp_bytes;
+    int cta_fixed;   // log tables at the start of the CTA's shared memory
 };
-constexpr int VT_FIXED_BYTES = 64 + ((int(sizeof(TileShared)) + 127) & ~127);
 
-template <typename QT>
-__global__ void __launch_bounds__(VT_THREADS, 2) viterbi_stream_kernel(const ViterbiParams p, const StreamLayout L) {
+// ------------------------------------------------------------------------------------------
+// Streaming kernel: one warp per read, RPL rows per lane and tile.
+// ------------------------------------------------------------------------------------------
+template <typename QT, int RPL>
+__global__ void __launch_bounds__(VW_THREADS) viterbi_stream_kernel(const ViterbiParams p, const WarpLayout L) {
+    constexpr int TILE = 32 * RPL;
     extern __shared__ __align__(128) unsigned char smem[];
-    uint64_t* full = reinterpret_cast<uint64_t*>(smem);
-    TileShared& S = *reinterpret_cast<TileShared*>(smem + 64);
-    unsigned char* stage0 = smem + VT_FIXED_BYTES;
-    unsigned char* outbuf = stage0 + L.nstage * L.stage_bytes;
-    uint8_t* out_lab = outbuf;
-    QT* out_qual = reinterpret_cast<QT*>(outbuf + L.out_lab_bytes);
-    int* out_path = reinterpret_cast<int*>(outbuf + L.out_lab_bytes + L.out_qual_bytes);
+    double* s_invc = reinterpret_cast<double*>(smem);
+    double* s_logc = s_invc + 16;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned char* ws = smem + L.cta_fixed + (size_t)warp * L.warp_bytes;
+    uint64_t* full = reinterpret_cast<uint64_t*>(ws);
+    unsigned char* stage0 = ws + L.off_stage;
+    uint8_t* slab = ws + L.off_lab;
+    float* sprob = reinterpret_cast<float*>(ws + L.off_prob);
 
-    const int tid = threadIdx.x;
     const int C = p.C;
     const long long T = p.T;
-    const int ntiles = int((T + VT_TILE - 1) / VT_TILE);
-    const long long my_reads = (p.N > blockIdx.x) ? (p.N - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    const int ntiles = int((T + TILE - 1) / TILE);
+    const long long gw = (long long)blockIdx.x * VW_WARPS + warp;
+    const long long nwarps = (long long)gridDim.x * VW_WARPS;
+    const long long my_reads = (p.N > gw) ? (p.N - gw + nwarps - 1) / nwarps : 0;
     const long long total_q = my_reads * ntiles;
     const long long total_elems = p.N * T * C;
     const long long safe_bytes = (total_elems * 4) & ~15LL;  // bulk copies never read past this
     const long long safe_elems = safe_bytes >> 2;
     const bool collapse = p.collapse != 0, qstring = p.qstring != 0;
+    const bool walk = qstring && collapse;  // runs longer than one row exist only with collapse
+    const long long stride = p.slot_stride;
 
-    auto issue = [&](long long q) {  // thread 0 only: start the bulk copy of tile q of this CTA's sequence
+    auto issue = [&](long long q) {  // lane 0: start the bulk copy of tile q of this warp's sequence
         const long long k = q / ntiles;
         const int ti = int(q - k * ntiles);
-        const long long n = blockIdx.x + k * (long long)gridDim.x;
-        const long long row0 = (long long)ti * VT_TILE;
-        const long long rows = (T - row0 < VT_TILE) ? (T - row0) : VT_TILE;
+        const long long n = gw + k * nwarps;
+        const long long row0 = (long long)ti * TILE;
+        const long long rows = (T - row0 < TILE) ? (T - row0) : TILE;
         const long long e0 = (n * T + row0) * C, e1 = e0 + rows * C;
         const long long b0 = (e0 * 4) & ~15LL;
         long long b1 = (e1 * 4 + 15) & ~15LL;
@@ -211,53 +136,57 @@ __global__ void __launch_bounds__(VT_THREADS, 2) viterbi_stream_kernel(const Vit
         if (bytes) bulk_g2s(stage0 + s * L.stage_bytes, reinterpret_cast<const char*>(p.post) + b0, bytes, &full[s]);
     };
 
-    if (tid == 0) {
+    if (threadIdx.x < 16) {
+        s_invc[threadIdx.x] = c_logf_invc[threadIdx.x];
+        s_logc[threadIdx.x] = c_logf_logc[threadIdx.x];
+    }
+    if (lane == 0) {
         for (int s = 0; s < L.nstage; ++s) mbar_init(&full[s], 1);
         mbar_init_fence();
     }
-    if (tid < 16) {
-        S.invc[tid] = c_logf_invc[tid];
-        S.logc[tid] = c_logf_logc[tid];
-    }
-    __syncthreads();
-    if (tid == 0) {
+    __syncthreads();  // the only block-level barrier: tables + barrier inits visible
+    if (lane == 0) {
         const long long pre = total_q < L.nstage ? total_q : L.nstage;
         for (long long q = 0; q < pre; ++q) issue(q);
     }
 
     long long q = 0;
     for (long long k = 0; k < my_reads; ++k) {
-        const long long n = blockIdx.x + k * (long long)gridDim.x;
-        int base = 0;
-        if (tid == 0) S.flag = 0;
+        const long long n = gw + k * nwarps;
+        uint8_t* out_lab = p.labels + n * stride;
+        QT* out_qual = reinterpret_cast<QT*>(p.quals) + n * stride;
+        int* out_path = p.path + n * stride;
+        int out_count = 0;
+        int last_label = -1;  // None, src/search.rs:337
+        bool open_active = false;  // a run that reached the end of the previous tile (warp-uniform)
+        float open_sum = 0.0f;
+        int open_n = 0, open_idx = 0;
+        bool bad_char = false;
+
         for (int ti = 0; ti < ntiles; ++ti, ++q) {
             const int s = int(q % L.nstage);
             const uint32_t phase = uint32_t(q / L.nstage) & 1u;
-            const int buf = int(q & 1);
-            const long long row0 = (long long)ti * VT_TILE;
-            const int rows = int((T - row0 < VT_TILE) ? (T - row0) : VT_TILE);
+            const long long row0 = (long long)ti * TILE;
+            const int rows = int((T - row0 < TILE) ? (T - row0) : TILE);
+            const bool last_tile = (ti == ntiles - 1);
             const long long e0 = (n * T + row0) * C;
             const float* stagef = reinterpret_cast<const float*>(stage0 + s * L.stage_bytes) + int(e0 & 3);
             mbar_wait(&full[s], phase);
 
-            float pr[VT_RPT];
-            uint32_t lab4 = 0;
-            const int r_base = VT_RPT * tid;
-            const bool vec_ok = (C == 5) && ((e0 & 3) == 0) && ((e0 + (long long)rows * C) <= safe_elems);
-            if (vec_ok && r_base + VT_RPT <= rows) {
-                const float4* s4 = reinterpret_cast<const float4*>(stagef) + 5 * tid;
+            float pr[RPL];
+            int lab[RPL];
+            const int r_base = RPL * lane;
+            const bool vec_ok = (RPL == 4) && (C == 5) && ((e0 & 3) == 0) && ((e0 + (long long)rows * C) <= safe_elems);
+            if (vec_ok && r_base + RPL <= rows) {
+                const float4* s4 = reinterpret_cast<const float4*>(stagef) + 5 * lane;
                 const float4 a = s4[0], b = s4[1], c = s4[2], d = s4[3], e = s4[4];
                 const float f[20] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, c.x, c.y,
                                      c.z, c.w, d.x, d.y, d.z, d.w, e.x, e.y, e.z, e.w};
 #pragma unroll
-                for (int r = 0; r < VT_RPT; ++r) {
-                    int arg;
-                    argmax_row5(f + 5 * r, arg, pr[r]);
-                    lab4 |= uint32_t(arg) << (8 * r);
-                }
+                for (int r = 0; r < RPL; ++r) argmax_row5(f + 5 * (r & 3), lab[r], pr[r]);
             } else {
 #pragma unroll
-                for (int r = 0; r < VT_RPT; ++r) {
+                for (int r = 0; r < RPL; ++r) {
                     const int row = r_base + r;
                     int arg = 0;
                     float best = 0.0f;
@@ -271,50 +200,124 @@ __global__ void __launch_bounds__(VT_THREADS, 2) viterbi_stream_kernel(const Vit
                         }
                     }
                     pr[r] = best;
-                    lab4 |= uint32_t(arg) << (8 * r);
+                    lab[r] = arg;  // rows past the end of the read count as blank
                 }
             }
-            S.lab32[buf][tid] = lab4;
-            S.prob4[buf][tid] = make_float4(pr[0], pr[1], pr[2], pr[3]);
-            if (tid == 0) S.carry[buf].active = 0;
-            __syncthreads();  // tile's labels visible; everyone is done reading stage s
-            if (tid == 0 && q + L.nstage < total_q) issue(q + L.nstage);
-            base += process_tile<QT>(S, buf, tid, ti == 0, ti == ntiles - 1, int(row0), lab4, pr, base, collapse,
-                                     qstring, p.qscale, p.qbias, out_lab, out_qual, out_path);
-        }
-        // write the read's records out, coalesced, into its pool slot
-        if (tid == 0) S.off = reserve_slot(p, base);
-        __syncthreads();
-        const long long off = S.off;
-        if (off >= 0) {
-            const int n16 = (base + 15) >> 4, n4 = (base + 3) >> 2;
-            uint4* gl = reinterpret_cast<uint4*>(p.labels + off);
-            const uint4* sl = reinterpret_cast<const uint4*>(out_lab);
-            for (int i = tid; i < n16; i += VT_THREADS) gl[i] = sl[i];
-            uint4* gp = reinterpret_cast<uint4*>(p.path + off);
-            const uint4* sp = reinterpret_cast<const uint4*>(out_path);
-            for (int i = tid; i < n4; i += VT_THREADS) gp[i] = sp[i];
-            if (qstring) {
-                uint4* gq = reinterpret_cast<uint4*>(reinterpret_cast<QT*>(p.quals) + off);
-                const uint4* sq = reinterpret_cast<const uint4*>(out_qual);
-                const int nq = sizeof(QT) == 1 ? n16 : n4;
-                for (int i = tid; i < nq; i += VT_THREADS) gq[i] = sq[i];
+            if (walk) {
+#pragma unroll
+                for (int r = 0; r < RPL; ++r) {
+                    slab[r_base + r] = uint8_t(lab[r]);
+                    sprob[r_base + r] = pr[r];
+                }
+            }
+            __syncwarp();  // stage s fully consumed; run-walk arrays visible
+            if (lane == 0 && q + L.nstage < total_q) issue(q + L.nstage);
+
+            // emission flags (src/search.rs:347) and output positions
+            int prev = __shfl_up_sync(FULLMASK, lab[RPL - 1], 1);
+            if (lane == 0) prev = last_label;
+            bool em[RPL];
+            int cnt = 0;
+#pragma unroll
+            for (int r = 0; r < RPL; ++r) {
+                em[r] = lab[r] != 0 && (!collapse || lab[r] != prev);
+                prev = lab[r];
+                cnt += em[r] ? 1 : 0;
+            }
+            const int incl = warp_inclusive_scan(cnt, lane);
+            int pos = out_count + incl - cnt;
+            const int tile_total = __shfl_sync(FULLMASK, incl, 31);
+
+            bool my_open = false;
+            float my_sum = 0.0f;
+            int my_n = 0, my_idx = 0;
+            // the run carried in from the previous tile continues in row order (lane 0)
+            if (open_active && lane == 0) {
+                float sum = open_sum;
+                int nn = open_n;
+                int r2 = 0;
+                while (r2 < TILE && slab[r2] == last_label) {
+                    sum = __fadd_rn(sum, sprob[r2]);
+                    ++nn;
+                    ++r2;
+                }
+                if (r2 == TILE && !last_tile) { my_open = true; my_sum = sum; my_n = nn; my_idx = open_idx; }
+                else out_qual[open_idx] = quality_char<QT>(sum, nn, p.qscale, p.qbias, s_invc, s_logc, bad_char);
+            }
+#pragma unroll
+            for (int r = 0; r < RPL; ++r) {
+                if (!em[r]) continue;
+                const int idx = pos++;
+                out_lab[idx] = uint8_t(lab[r]);
+                out_path[idx] = int(row0) + r_base + r;
+                if (qstring) {
+                    float sum = __fadd_rn(0.0f, pr[r]);  // label_prob_total starts at 0.0 (src/search.rs:339,354)
+                    int nn = 1;
+                    bool open = false;
+                    if (collapse) {
+                        int r2 = r_base + r + 1;
+                        while (r2 < TILE && slab[r2] == lab[r]) {
+                            sum = __fadd_rn(sum, sprob[r2]);
+                            ++nn;
+                            ++r2;
+                        }
+                        open = (r2 == TILE) && !last_tile;
+                    }
+                    if (open) { my_open = true; my_sum = sum; my_n = nn; my_idx = idx; }
+                    else out_qual[idx] = quality_char<QT>(sum, nn, p.qscale, p.qbias, s_invc, s_logc, bad_char);
+                }
+            }
+            last_label = __shfl_sync(FULLMASK, lab[RPL - 1], 31);
+            out_count += tile_total;
+            if (walk) {
+                const unsigned m = __ballot_sync(FULLMASK, my_open);
+                open_active = (m != 0u);
+                if (open_active) {  // at most one lane holds the run that touches the tile end
+                    const int src = __ffs(m) - 1;
+                    open_sum = __shfl_sync(FULLMASK, my_sum, src);
+                    open_n = __shfl_sync(FULLMASK, my_n, src);
+                    open_idx = __shfl_sync(FULLMASK, my_idx, src);
+                }
+                __syncwarp();  // run walks done before the next tile overwrites slab / sprob
             }
         }
-        if (tid == 0) {
-            p.offsets[n] = off >= 0 ? off : 0;
-            p.lens[n] = off >= 0 ? base : 0;
-            p.status[n] = off < 0 ? FCTC_OUTPUT_OVERFLOW : (S.flag ? FCTC_INVALID_QUALITY_CHAR : FCTC_OK);
+        bad_char = __any_sync(FULLMASK, bad_char);
+        if (lane == 0) {
+            p.offsets[n] = p.offset_base + n * stride;
+            p.lens[n] = out_count;
+            p.status[n] = bad_char ? FCTC_INVALID_QUALITY_CHAR : FCTC_OK;
         }
     }
 }
 
 // ------------------------------------------------------------------------------------------
-// Generic kernel: any alphabet size, any row count, no alignment requirement.  One CTA per read,
-// two passes (count, then decode straight into the pool slot).  Used when the streaming kernel's
-// shared-memory plan does not fit (very long reads / very wide alphabets) or the input pointer
-// is not 16-byte aligned.
+// Generic kernel: any alphabet size, no alignment requirement.  One CTA per read, rows loaded
+// straight from global memory.  Used when the streaming kernel's shared-memory plan does not fit
+// (alphabets above 64 labels) or the input pointer is not 16-byte aligned.
 // ------------------------------------------------------------------------------------------
+constexpr int VG_THREADS = 256;
+constexpr int VG_RPT = 4;
+constexpr int VG_TILE = VG_THREADS * VG_RPT;
+constexpr int VG_WARPS = VG_THREADS / 32;
+
+struct RunCarry {  // a label run that reaches the end of a tile and may continue in the next one
+    int active;
+    int label;
+    float sum;
+    int count;
+    int idx;
+};
+
+struct TileShared {  // double-buffered by tile parity so that one tile needs only two barriers
+    uint32_t lab32[2][VG_THREADS];  // 4 labels per word: byte r = row 4*tid + r
+    float4 prob4[2][VG_THREADS];    // winning probability of the same 4 rows
+    int wsum[2][VG_WARPS];
+    RunCarry carry[2];
+    double invc[16];
+    double logc[16];
+    int flag;
+};
+
 __device__ __forceinline__ void argmax_global(const float* row, int C, int& arg, float& best) {
     best = row[0];
     arg = 0;
@@ -325,128 +328,177 @@ __device__ __forceinline__ void argmax_global(const float* row, int C, int& arg,
 }
 
 template <typename QT>
-__global__ void __launch_bounds__(VT_THREADS) viterbi_generic_kernel(const ViterbiParams p) {
+__global__ void __launch_bounds__(VG_THREADS) viterbi_generic_kernel(const ViterbiParams p) {
     __shared__ TileShared S;
-    __shared__ int s_red[VT_WARPS];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int C = p.C;
     const long long T = p.T;
-    const int ntiles = int((T + VT_TILE - 1) / VT_TILE);
+    const int ntiles = int((T + VG_TILE - 1) / VG_TILE);
     const bool collapse = p.collapse != 0, qstring = p.qstring != 0;
     if (tid < 16) {
         S.invc[tid] = c_logf_invc[tid];
         S.logc[tid] = c_logf_logc[tid];
     }
     __syncthreads();
-    int parity = 0;
+    int buf = 0;
     for (long long n = blockIdx.x; n < p.N; n += gridDim.x) {
         const float* rd = p.post + n * T * C;
-        // pass A: number of emitted labels
-        int cnt = 0;
-        for (long long t = tid; t < T; t += VT_THREADS) {
-            int a;
-            float v;
-            argmax_global(rd + t * C, C, a, v);
-            if (a != 0) {
-                bool emit = true;
-                if (collapse && t > 0) {
-                    int b;
-                    argmax_global(rd + (t - 1) * C, C, b, v);
-                    emit = (b != a);
-                }
-                cnt += emit ? 1 : 0;
-            }
-        }
-        cnt = warp_inclusive_scan(cnt, lane);
-        if (lane == 31) s_red[warp] = cnt;
-        if (tid == 0) S.flag = 0;
-        __syncthreads();
-        if (tid == 0) {
-            int total = 0;
-            for (int w = 0; w < VT_WARPS; ++w) total += s_red[w];
-            S.off = reserve_slot(p, total);
-        }
-        __syncthreads();
-        const long long off = S.off;
+        uint8_t* out_lab = p.labels + n * p.slot_stride;
+        QT* out_qual = reinterpret_cast<QT*>(p.quals) + n * p.slot_stride;
+        int* out_path = p.path + n * p.slot_stride;
         int base = 0;
-        if (off >= 0) {
-            uint8_t* out_lab = p.labels + off;
-            QT* out_qual = reinterpret_cast<QT*>(p.quals) + off;
-            int* out_path = p.path + off;
-            for (int ti = 0; ti < ntiles; ++ti, parity ^= 1) {
-                const long long row0 = (long long)ti * VT_TILE;
-                float pr[VT_RPT];
-                uint32_t lab4 = 0;
+        bool bad_char = false;
+        if (tid == 0) S.flag = 0;
+        for (int ti = 0; ti < ntiles; ++ti, buf ^= 1) {
+            const long long row0 = (long long)ti * VG_TILE;
+            const bool first_tile = ti == 0, last_tile = ti == ntiles - 1;
+            float pr[VG_RPT];
+            uint32_t lab4 = 0;
 #pragma unroll
-                for (int r = 0; r < VT_RPT; ++r) {
-                    const long long row = row0 + VT_RPT * tid + r;
-                    int arg = 0;
-                    float best = 0.0f;
-                    if (row < T) argmax_global(rd + row * C, C, arg, best);
-                    pr[r] = best;
-                    lab4 |= uint32_t(arg) << (8 * r);
-                }
-                S.lab32[parity][tid] = lab4;
-                S.prob4[parity][tid] = make_float4(pr[0], pr[1], pr[2], pr[3]);
-                if (tid == 0) S.carry[parity].active = 0;
-                __syncthreads();
-                base += process_tile<QT>(S, parity, tid, ti == 0, ti == ntiles - 1, int(row0), lab4, pr, base,
-                                         collapse, qstring, p.qscale, p.qbias, out_lab, out_qual, out_path);
+            for (int r = 0; r < VG_RPT; ++r) {
+                const long long row = row0 + VG_RPT * tid + r;
+                int arg = 0;
+                float best = 0.0f;
+                if (row < T) argmax_global(rd + row * C, C, arg, best);
+                pr[r] = best;
+                lab4 |= uint32_t(arg) << (8 * r);
             }
+            S.lab32[buf][tid] = lab4;
+            S.prob4[buf][tid] = make_float4(pr[0], pr[1], pr[2], pr[3]);
+            if (tid == 0) S.carry[buf].active = 0;
+            __syncthreads();
+            const uint8_t* labs = reinterpret_cast<const uint8_t*>(S.lab32[buf]);
+            const float* probs = reinterpret_cast<const float*>(S.prob4[buf]);
+            int prev = 0;
+            bool prev_valid = true;
+            if (tid > 0) prev = labs[VG_RPT * tid - 1];
+            else if (!first_tile) prev = reinterpret_cast<const uint8_t*>(S.lab32[buf ^ 1])[VG_TILE - 1];
+            else prev_valid = false;
+            int lab[VG_RPT];
+            bool em[VG_RPT];
+            int cnt = 0;
+#pragma unroll
+            for (int r = 0; r < VG_RPT; ++r) {
+                lab[r] = int((lab4 >> (8 * r)) & 0xffu);
+                em[r] = lab[r] != 0 && (!collapse || !prev_valid || lab[r] != prev);
+                prev = lab[r];
+                prev_valid = true;
+                cnt += em[r] ? 1 : 0;
+            }
+            const int incl = warp_inclusive_scan(cnt, lane);
+            if (lane == 31) S.wsum[buf][warp] = incl;
+            __syncthreads();
+            int wbase = 0, total = 0;
+#pragma unroll
+            for (int w = 0; w < VG_WARPS; ++w) {
+                const int s = S.wsum[buf][w];
+                if (w < warp) wbase += s;
+                total += s;
+            }
+            int pos = base + wbase + incl - cnt;
+#pragma unroll
+            for (int r = 0; r < VG_RPT; ++r) {
+                if (!em[r]) continue;
+                const int idx = pos++;
+                out_lab[idx] = uint8_t(lab[r]);
+                out_path[idx] = int(row0) + VG_RPT * tid + r;
+                if (qstring) {
+                    float sum = __fadd_rn(0.0f, pr[r]);
+                    int nn = 1;
+                    bool open = false;
+                    if (collapse) {
+                        int r2 = VG_RPT * tid + r + 1;
+                        while (r2 < VG_TILE && labs[r2] == lab[r]) {
+                            sum = __fadd_rn(sum, probs[r2]);
+                            ++nn;
+                            ++r2;
+                        }
+                        open = (r2 == VG_TILE) && !last_tile;
+                    }
+                    if (open) S.carry[buf] = RunCarry{1, lab[r], sum, nn, idx};
+                    else out_qual[idx] = quality_char<QT>(sum, nn, p.qscale, p.qbias, S.invc, S.logc, bad_char);
+                }
+            }
+            if (qstring && tid == 0 && !first_tile) {
+                const RunCarry c = S.carry[buf ^ 1];
+                if (c.active) {
+                    float sum = c.sum;
+                    int nn = c.count;
+                    int r2 = 0;
+                    while (r2 < VG_TILE && labs[r2] == c.label) {
+                        sum = __fadd_rn(sum, probs[r2]);
+                        ++nn;
+                        ++r2;
+                    }
+                    if (r2 == VG_TILE && !last_tile) S.carry[buf] = RunCarry{1, c.label, sum, nn, c.idx};
+                    else out_qual[c.idx] = quality_char<QT>(sum, nn, p.qscale, p.qbias, S.invc, S.logc, bad_char);
+                }
+            }
+            base += total;
         }
+        if (bad_char) S.flag = 1;
         __syncthreads();
         if (tid == 0) {
-            p.offsets[n] = off >= 0 ? off : 0;
-            p.lens[n] = off >= 0 ? base : 0;
-            p.status[n] = off < 0 ? FCTC_OUTPUT_OVERFLOW : (S.flag ? FCTC_INVALID_QUALITY_CHAR : FCTC_OK);
+            p.offsets[n] = p.offset_base + n * p.slot_stride;
+            p.lens[n] = base;
+            p.status[n] = S.flag ? FCTC_INVALID_QUALITY_CHAR : FCTC_OK;
         }
+        __syncthreads();
     }
 }
 
-static bool plan_stream(const ViterbiParams& p, StreamLayout* L) {
+template <int RPL>
+static bool plan_stream(const ViterbiParams& p, WarpLayout* L) {
     if ((reinterpret_cast<uintptr_t>(p.post) & 15u) != 0) return false;
-    if (p.T > (1LL << 30) || p.T <= 0) return false;
-    const long long qb = p.qstring ? p.qual_bytes : 0;
-    const long long out_lab = (p.T + 15) & ~15LL;
-    const long long out_qual = (p.T * qb + 15) & ~15LL;
-    const long long out_path = (p.T * 4 + 15) & ~15LL;
-    const long long rows = p.T < VT_TILE ? p.T : VT_TILE;
+    constexpr int TILE = 32 * RPL;
+    const long long rows = p.T < TILE ? p.T : TILE;
     const long long stage = ((rows * p.C * 4 + 15) & ~15LL) + 32;
-    if (stage > (1 << 19)) return false;  // mbarrier tx-count range
-    for (int ns = VT_MAX_STAGES; ns >= 2; --ns) {
-        const long long total = VT_FIXED_BYTES + ns * stage + out_lab + out_qual + out_path;
-        // prefer a plan that leaves room for two CTAs per SM; fall back to one
-        if (total * 2 <= VT_SMEM_LIMIT - 2048 || (ns == 2 && total <= VT_SMEM_LIMIT)) {
-            L->nstage = ns;
-            L->stage_bytes = int(stage);
-            L->out_lab_bytes = int(out_lab);
-            L->out_qual_bytes = int(out_qual);
-            L->out_path_bytes = int(out_path);
-            L->total_bytes = int(total);
-            return true;
-        }
-    }
-    return false;
+    if (stage > 16 * 1024) return false;
+    // enough bytes in flight per warp to cover HBM latency at ~16-20 resident warps per SM
+    int ns = int((12 * 1024) / stage);
+    if (ns > VW_MAX_STAGES) ns = VW_MAX_STAGES;
+    if (ns < 2) ns = 2;
+    L->nstage = ns;
+    L->stage_bytes = int(stage);
+    L->off_stage = 64;
+    L->off_lab = int(L->off_stage + ns * stage);
+    L->off_prob = L->off_lab + ((TILE + 15) & ~15);
+    L->warp_bytes = (L->off_prob + TILE * 4 + 127) & ~127;
+    L->cta_fixed = 256;
+    return L->cta_fixed + VW_WARPS * L->warp_bytes <= VT_SMEM_LIMIT;
+}
+
+template <typename QT, int RPL>
+static cudaError_t launch_stream(const ViterbiParams& p, const WarpLayout& L, int sm_count, cudaStream_t stream) {
+    const int smem = L.cta_fixed + VW_WARPS * L.warp_bytes;
+    cudaError_t e = cudaFuncSetAttribute(viterbi_stream_kernel<QT, RPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    int per_sm = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, viterbi_stream_kernel<QT, RPL>, VW_THREADS, smem);
+    if (e != cudaSuccess) return e;
+    if (per_sm < 1) per_sm = 1;
+    long long grid = (long long)sm_count * per_sm;
+    const long long need = (p.N + VW_WARPS - 1) / VW_WARPS;
+    if (grid > need) grid = need;
+    viterbi_stream_kernel<QT, RPL><<<dim3((unsigned)grid), VW_THREADS, smem, stream>>>(p, L);
+    return cudaGetLastError();
 }
 
 template <typename QT>
 static cudaError_t launch_viterbi_t(const ViterbiParams& p, int sm_count, cudaStream_t stream, int* which) {
-    StreamLayout L;
-    if (plan_stream(p, &L)) {
-        cudaError_t e = cudaFuncSetAttribute(viterbi_stream_kernel<QT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             L.total_bytes);
-        if (e != cudaSuccess) return e;
-        const int per_sm = (2LL * L.total_bytes <= VT_SMEM_LIMIT - 2048) ? 2 : 1;
-        long long grid = (long long)sm_count * per_sm;
-        if (grid > p.N) grid = p.N;
+    WarpLayout L;
+    if (p.C <= 16 && plan_stream<4>(p, &L)) {
         if (which) *which = 0;
-        viterbi_stream_kernel<QT><<<dim3((unsigned)grid), VT_THREADS, L.total_bytes, stream>>>(p, L);
-        return cudaGetLastError();
+        return launch_stream<QT, 4>(p, L, sm_count, stream);
+    }
+    if (p.C <= 64 && plan_stream<1>(p, &L)) {
+        if (which) *which = 0;
+        return launch_stream<QT, 1>(p, L, sm_count, stream);
     }
     long long grid = (long long)sm_count * 8;
     if (grid > p.N) grid = p.N;
     if (which) *which = 1;
-    viterbi_generic_kernel<QT><<<dim3((unsigned)grid), VT_THREADS, 0, stream>>>(p);
+    viterbi_generic_kernel<QT><<<dim3((unsigned)grid), VG_THREADS, 0, stream>>>(p);
     return cudaGetLastError();
 }
 

@@ -29,7 +29,7 @@ _SIGNATURES = {
     "fctc_status_message": (C.c_char_p, [C.c_int]),
     "fctc_device_sm_count": (C.c_int, [_vp]),
     "fctc_viterbi_batch_device": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _i32, _f32, _f32, _i32, _vp, _vp, _i32, _vp,
-                                            _i64, _vp, _vp, _vp, _vp, _vp]),
+                                            _i64, _vp, _vp, _vp, _vp]),
     "fctc_viterbi_batch": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _i32, _f32, _f32, _i32, _vp, _vp, _i32, _vp, _i64,
                                      _vp, _vp, _vp, _vp]),
     "fctc_viterbi_search": (C.c_int, [_vp, _vp, _i64, _i32, _i64, _i64, _i32, _f32, _f32, _i32, _vp, _vp, _vp, _i64,
@@ -118,12 +118,11 @@ class Decoder:
 
     def viterbi_batch_device(self, post_ptr, n_reads, n_rows, n_labels, qstring, qscale, qbias, collapse_repeats,
                              labels_ptr, quals_ptr, qual_bytes, path_ptr, pool_capacity, offsets_ptr, lens_ptr,
-                             status_ptr, pool_used_ptr, stream=0):
+                             status_ptr, stream=0):
         self._check(self._L.fctc_viterbi_batch_device(self._h, post_ptr, n_reads, n_rows, n_labels, int(qstring),
                                                       qscale, qbias, int(collapse_repeats), labels_ptr,
                                                       quals_ptr or None, qual_bytes, path_ptr, pool_capacity,
-                                                      offsets_ptr, lens_ptr, status_ptr, pool_used_ptr,
-                                                      stream or None))
+                                                      offsets_ptr, lens_ptr, status_ptr, stream or None))
 
     def beam_scratch_bytes(self, n_reads, n_rows, n_labels, beam_size, nodes_per_row=0):
         return int(self._L.fctc_beam_scratch_bytes(self._h, n_reads, n_rows, n_labels, beam_size, nodes_per_row))

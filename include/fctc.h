@@ -11,10 +11,11 @@
  *   - Posteriors are float32, label axis innermost, blank label first (src/lib.rs:604-616).
  *   - Decoders return *alphabet indices* (1..n_labels-1, blank never appears); the caller maps
  *     them to label strings exactly as src/search.rs:291,358 do (labels may be multi-character).
- *   - Batch results are a pool in "unordered CSR" form: read n owns entries
- *     [offsets[n], offsets[n]+lens[n]) of `labels` / `quals` / `path`.  Slots are handed out with one
- *     atomic add per read (rounded up to 32 entries), so the *placement* of a read inside the pool
- *     depends on scheduling; the *content* per read is deterministic.
+ *   - Batch results are a pool: read n owns entries [offsets[n], offsets[n]+lens[n]) of `labels` /
+ *     `quals` / `path`.  Viterbi uses fixed slots (offsets[n] = n * round_up(n_rows, 32), so the
+ *     layout is fully deterministic and needs no atomics); beam search packs reads with one atomic
+ *     add per read (rounded up to 32 entries), so there the *placement* of a read depends on
+ *     scheduling while the *content* per read is deterministic.
  *   - `path` entries are row indices into the read (int32 on the device, the reference's
  *     Vec<usize>): emission row for Viterbi, first-proposal row for beam search.
  *   - Return value: >= 0 is a per-call decode status for single-read calls (FCTC_OK or one of the
@@ -68,27 +69,26 @@ int fctc_device_sm_count(const fctc_handle* h);
  * :303-318, phred :31-36) as called from src/lib.rs:200-207.
  *
  * fctc_viterbi_batch_device: posteriors already in HBM, C-contiguous [n_reads, n_rows, n_labels];
- *   results stay in HBM (pool form, see above).  Asynchronous on `stream` (a cudaStream_t, may be
- *   NULL for the handle's stream).  qual_bytes selects the quality element type: 1 = uint8
+ *   results stay in HBM (pool form, see above).  Asynchronous on `stream` (a cudaStream_t; NULL is
+ *   the legacy default stream, as everywhere in CUDA).  qual_bytes selects the quality element type: 1 = uint8
  *   (enough whenever 40*|qscale|+|qbias|+33 < 256), 4 = uint32 (any Unicode scalar, as the
  *   reference's `char`); 1 is refused (FCTC_E_ARGUMENT) when a code could exceed 255.  quals_dev
- *   may be NULL when qstring == 0.  *pool_used_dev is the pool
- *   cursor (entries handed out so far): the caller zeroes it before the first call and may keep
- *   appending batches to one pool.
+ *   may be NULL when qstring == 0.  pool_capacity (entries of labels_dev / quals_dev / path_dev)
+ *   must be at least n_reads * round_up(n_rows, 32), else FCTC_E_CAPACITY.
  * ------------------------------------------------------------------------------------------ */
 int fctc_viterbi_batch_device(fctc_handle* h, const float* post_dev, int64_t n_reads, int64_t n_rows,
                               int32_t n_labels, int32_t qstring, float qscale, float qbias,
                               int32_t collapse_repeats, uint8_t* labels_dev, void* quals_dev, int32_t qual_bytes,
                               int32_t* path_dev, int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev,
-                              int32_t* status_dev, unsigned long long* pool_used_dev, void* stream);
+                              int32_t* status_dev, void* stream);
 
 /* fctc_viterbi_batch: the same over HOST memory (new batched entry point of the north star):
  *   post_host is C-contiguous [n_reads, n_rows, n_labels]; outputs are host arrays in pool form
  *   (quals: qual_bytes 1 = uint8, 4 = uint32 Unicode scalars; path is int32).  Reads are streamed
  *   through the device in chunks, host<->device copies overlapped with decoding; synchronous.
  *   Pinned (page-locked) host buffers give full copy overlap; pageable ones work, slower.
- *   pool_capacity >= n_reads * round_up(n_rows, 32) always suffices; *pool_used receives the
- *   entries used.  If the pool is too small the call returns FCTC_E_CAPACITY.  qual_bytes == 1 is
+ *   pool_capacity must be >= n_reads * round_up(n_rows, 32) (else FCTC_E_CAPACITY); *pool_used
+ *   receives that product.  qual_bytes == 1 is
  *   refused (FCTC_E_ARGUMENT) when a quality code could exceed 255 for the given qscale/qbias. */
 int fctc_viterbi_batch(fctc_handle* h, const float* post_host, int64_t n_reads, int64_t n_rows, int32_t n_labels,
                        int32_t qstring, float qscale, float qbias, int32_t collapse_repeats, uint8_t* labels,

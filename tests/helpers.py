@@ -35,7 +35,7 @@ def peaked_posteriors(rng, shape, p_blank=0.65):
     """Nanopore-like peaked rows: one dominant label per row, blank with probability p_blank."""
     *lead, C = shape
     n = int(np.prod(lead))
-    dom = np.where(rng.random(n) < p_blank, 0, rng.integers(1, C, n))
+    dom = np.where(rng.random(n) < p_blank, 0, rng.integers(1, max(C, 2), n) % C)
     x = (0.05 * rng.random((n, C), dtype=np.float32) ** 2).astype(np.float32)
     x[np.arange(n), dom] = 1.0
     x /= x.sum(axis=1, keepdims=True, dtype=np.float32)
