@@ -1,0 +1,369 @@
+#!/usr/bin/env python3
+"""bench.py — headline benchmark of the B200 batched CTC decoder (driver contract).
+
+Workload (BASELINE.json configs[1]): Viterbi batch, 1M reads x T=4000 x C=5 float32 posteriors,
+qstring on, qscale/qbias, collapse_repeats — per GPU ("weak" scaling: reads are independent, every
+rank decodes its own 1M-read shard, no collective on the data path).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload viterbi|beam5|beam32]
+
+One "step" = one pass of the hot path over the whole resident batch (one kernel launch).
+  value     rows/s, inputs resident in HBM, device-timed with CUDA events on the launching stream,
+            barrier + synchronize on both sides, max over ranks.
+  e2e       the same metric through the C ABI host entry point (fctc_viterbi_batch) with pinned HOST
+            buffers: host->device and device->host copies inside the timed region.
+  roofline  algorithmic bytes per launch / mean launch time, vs the measured HBM copy peak.
+  cpu_baseline  the CPU oracle (C++ restatement of the reference; the Rust reference itself cannot be
+            built in this image) on the box's host cores, on a bounded sample of the same bytes.
+--impl reference prints the reference arm's line (CPU oracle, all host threads, bounded sample).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "fast-ctc-decode_b200")
+for _p in (ROOT, PKG):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import numpy as np  # noqa: E402
+
+METRIC = "posterior rows decoded/s (Viterbi; beam 5 & 32) at 1/2/4/8 B200 vs host CPU"
+UNIT = "rows/s"
+SEED = 0xC7C00001
+
+WORKLOADS = {
+    # name: reads per GPU, rows, labels, decoder, parameters
+    "viterbi": dict(reads=1_000_000, T=4000, C=5, kind="viterbi", qstring=1, qscale=0.7, qbias=2.0, collapse=1,
+                    cpu_sample=32768, e2e_reads=32768,
+                    label="viterbi 1M reads x T=4000 x C=5 f32, qstring qscale=0.7 qbias=2.0, collapse_repeats"),
+    "beam5": dict(reads=262_144, T=4000, C=5, kind="beam", beam=5, thr=0.1, collapse=1, cpu_sample=2048,
+                  e2e_reads=16384, label="beam_search 262,144 reads x T=4000 x C=5, beam_size=5, beam_cut_threshold=0.1"),
+    "beam32": dict(reads=65_536, T=10_000, C=5, kind="beam", beam=32, thr=0.0, collapse=1, cpu_sample=128,
+                   e2e_reads=4096, label="beam_search 65,536 reads x T=10,000 x C=5, beam_size=32, beam_cut_threshold=0.0"),
+}
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return json.load(f), "measured (MEASURED_PEAKS.json hbm_gbs, burst copy)"
+    return {"hbm_gbs": 6650.0}, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu, self.proc, self.lines = gpu_index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.gpu), "-lms", "50"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.12)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, power, reasons = [], [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); power.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "power_w_max": float(max(power)),
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def host_threads():
+    import oracle
+    return max(1, oracle.hardware_threads())
+
+
+def cpu_rate(w, post_np, n_threads):
+    """rows/s of the CPU oracle over post_np [n, T, C] (results discarded)."""
+    import oracle
+    t0 = time.perf_counter()
+    if w["kind"] == "viterbi":
+        oracle.viterbi_batch(post_np, bool(w["qstring"]), w["qscale"], w["qbias"], bool(w["collapse"]),
+                             n_threads=n_threads, keep=False)
+    else:
+        oracle.beam_search_batch(post_np, w["beam"], w["thr"], bool(w["collapse"]), n_threads=n_threads, keep=False)
+    dt = time.perf_counter() - t0
+    return post_np.shape[0] * post_np.shape[1] / dt, dt
+
+
+def synth_host_sample(w, n_reads, first_read=0):
+    """The first n_reads reads of rank 0's shard, as host float32 (generated by the device generator
+    when a GPU is present so that both arms see identical bytes; numpy restatement otherwise)."""
+    try:
+        import torch
+        if torch.cuda.is_available():
+            import fctc_b200
+            dec = fctc_b200.Decoder(0)
+            t = torch.empty((n_reads, w["T"], w["C"]), dtype=torch.float32, device="cuda:0")
+            dec.synth_posteriors_device(t.data_ptr(), n_reads, w["T"], w["C"], 0, SEED, first_read,
+                                        torch.cuda.current_stream().cuda_stream)
+            torch.cuda.synchronize()
+            out = t.cpu().numpy()
+            del t
+            dec.close()
+            return out, "device generator (same bytes as the GPU arm)"
+    except Exception:
+        pass
+    rng = np.random.default_rng(SEED)
+    z = (rng.random((n_reads, w["T"], w["C"]), dtype=np.float32) * 2 - 1) * 3
+    e = np.exp(z - z.max(axis=-1, keepdims=True))
+    return (e / e.sum(axis=-1, keepdims=True)).astype(np.float32), "numpy softmax(3(2u-1)) (no GPU present)"
+
+
+def run_reference(args, w):
+    """Reference arm: the reference's CPU algorithm (oracle port; the Rust build is unavailable here)
+    on all host threads; every step decodes one bounded sample of the workload."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import oracle
+    oracle.build()
+    n = w["cpu_sample"]
+    post, how = synth_host_sample(w, n)
+    threads = host_threads()
+    for _ in range(max(args.warmup, 0)):
+        cpu_rate(w, post[: max(1, n // 8)], threads)
+    t_total = 0.0
+    for _ in range(args.steps):
+        _, dt = cpu_rate(w, post, threads)
+        t_total += dt
+    rows = n * w["T"] * args.steps
+    value = rows / t_total
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * t_total / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": w["label"], "sample": f"{n} reads per step ({how})"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
+                         "sample": f"{n} reads x {w['T']} rows per step, {args.steps} steps, one read per worker thread; "
+                                   "C++ restatement of the reference (Rust toolchain absent)"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+
+
+def run_ours(args, w):
+    import torch
+    import torch.distributed as dist
+
+    import fctc_b200
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the decoder has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    dec = fctc_b200.Decoder(local_rank)
+    N, T, Cn = args.reads or w["reads"], w["T"], w["C"]
+    stream = torch.cuda.current_stream().cuda_stream
+    stride = (T + 31) // 32 * 32
+
+    # ---- resident synthetic input: rank r decodes reads [r*N, (r+1)*N) of the global job ----------
+    post = torch.empty((N, T, Cn), dtype=torch.float32, device=dev)
+    from fctc_b200.sharding import weak_shard_first_read
+    dec.synth_posteriors_device(post.data_ptr(), N, T, Cn, 0, SEED, weak_shard_first_read(N, rank), stream)
+    cap = N * stride
+    labels = torch.empty(cap, dtype=torch.uint8, device=dev)
+    path = torch.empty(cap, dtype=torch.int32, device=dev)
+    offsets = torch.empty(N, dtype=torch.int64, device=dev)
+    lens = torch.empty(N, dtype=torch.int32, device=dev)
+    status = torch.empty(N, dtype=torch.int32, device=dev)
+    used = torch.zeros(1, dtype=torch.int64, device=dev)
+    if w["kind"] == "viterbi":
+        quals = torch.empty(cap, dtype=torch.uint8, device=dev)
+        scratch = None
+
+        def step():
+            dec.viterbi_batch_device(post.data_ptr(), N, T, Cn, w["qstring"], w["qscale"], w["qbias"], w["collapse"],
+                                     labels.data_ptr(), quals.data_ptr(), 1, path.data_ptr(), cap, offsets.data_ptr(),
+                                     lens.data_ptr(), status.data_ptr(), stream)
+        launches_per_step = 1
+    else:
+        nbytes = dec.beam_scratch_bytes(N, T, Cn, w["beam"], 0)
+        scratch = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+
+        def step():
+            used.zero_()
+            dec.beam_search_batch_device(post.data_ptr(), N, T, Cn, w["beam"], w["thr"], w["collapse"], labels.data_ptr(),
+                                         path.data_ptr(), cap, offsets.data_ptr(), lens.data_ptr(), status.data_ptr(),
+                                         used.data_ptr(), scratch.data_ptr(), nbytes, 0, stream)
+        launches_per_step = 1
+    torch.cuda.synchronize()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    time.sleep(0.1)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    ev[0].record()
+    for i in range(args.steps):
+        step()
+        ev[i + 1].record()
+    barrier()
+    clocks = sampler.stop()
+    total_ms = ev[0].elapsed_time(ev[-1])
+    step_ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps)]
+    if world > 1:
+        t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms = float(t.item())
+    ms_per_step = total_ms / args.steps
+    rows_all = N * T * world
+    value = rows_all / (ms_per_step * 1e-3)
+
+    # ---- algorithmic bytes of one launch: 4*C per row in, per emitted label 1 (label)
+    #      + 1 (quality) + 4 (path) out, + 16 B per read (offset, len, status) -------------------------
+    emitted = int(lens.sum(dtype=torch.int64).item())
+    ok_reads = int((status == 0).sum().item())
+    out_per_label = (1 + 4 + (1 if w.get("qstring") else 0))
+    alg_bytes = N * T * Cn * 4 + emitted * out_per_label + N * 16
+    mean_launch_ms = float(np.mean(step_ms))
+    peaks, peak_src = measured_peaks()
+    achieved = alg_bytes / (mean_launch_ms * 1e-3) / 1e9
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        with open(tpath) as f:
+            tj = json.load(f).get(args.workload)
+        if tj:
+            traffic = tj["dram_bytes_per_read"] * N
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                "frac": achieved / peaks["hbm_gbs"], "traffic": traffic, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": alg_bytes, "mean_launch_ms": mean_launch_ms,
+                "input_stream_gbs": N * T * Cn * 4 / (mean_launch_ms * 1e-3) / 1e9}
+
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": w["label"], "reads_per_gpu": N, "rows_per_read": T, "labels": Cn,
+                       "input": "device generator, softmax(3(2u-1)) rows, seed 0xC7C00001",
+                       "l2": f"input {N * T * Cn * 4 / 1e9:.1f} GB per GPU is larger than the 126 MB L2 (no flush needed)",
+                       "parallelism": f"reads sharded over {world} GPU(s), no collective",
+                       "emitted_labels_per_row": emitted / (N * T), "reads_ok": ok_reads},
+            "clocks": clocks, "gpu_launches": launches_per_step * args.steps, "roofline": roofline}
+
+    if rank == 0:
+        # ---- end to end through the C ABI with pinned HOST buffers (copies inside the timed region) --
+        ne = min(w["e2e_reads"], N)
+        hpost = torch.empty((ne, T, Cn), dtype=torch.float32).pin_memory()
+        hpost.copy_(post[:ne])
+        hcap = ne * stride
+        hl = torch.empty(hcap, dtype=torch.uint8).pin_memory()
+        hq = torch.empty(hcap, dtype=torch.uint8).pin_memory()
+        hp = torch.empty(hcap, dtype=torch.int32).pin_memory()
+        ho = torch.empty(ne, dtype=torch.int64).pin_memory()
+        hn = torch.empty(ne, dtype=torch.int32).pin_memory()
+        hs = torch.empty(ne, dtype=torch.int32).pin_memory()
+        outd = dict(labels=hl.numpy(), quals=hq.numpy(), path=hp.numpy(), offsets=ho.numpy(), lens=hn.numpy(),
+                    status=hs.numpy())
+        hnp = hpost.numpy()
+
+        def e2e_step():
+            if w["kind"] == "viterbi":
+                return dec.viterbi_batch(hnp, bool(w["qstring"]), w["qscale"], w["qbias"], bool(w["collapse"]),
+                                         qual_bytes=1, out=outd)
+            return dec.beam_search_batch(hnp, w["beam"], w["thr"], bool(w["collapse"]), out=outd)
+        for _ in range(3):
+            res = e2e_step()
+        torch.cuda.synchronize()
+        reps = 5
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            res = e2e_step()
+        dt = (time.perf_counter() - t0) / reps
+        h2d = ne * T * Cn * 4
+        if w["kind"] == "viterbi":
+            d2h = hcap * (1 + 4 + (1 if w["qstring"] else 0)) + ne * 16
+        else:
+            d2h = int(res["used"]) * 5 + ne * 16 + 8
+        line["e2e"] = {"value": ne * T / dt, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                       "reads_per_step": ne, "ms_per_step": dt * 1e3,
+                       "note": "fctc_*_batch (host pointers, pinned memory), rank 0, one GPU; x n_gpus when every rank "
+                               "streams its own shard"}
+        if world > 1:
+            line["e2e"]["value"] *= 1  # rank 0's rate; ranks are independent
+        # ---- CPU baseline on a bounded sample of the same bytes ------------------------------------------
+        import oracle
+        oracle.build()
+        nc = min(w["cpu_sample"], ne)
+        threads = host_threads()
+        rate, dtc = cpu_rate(w, hnp[:nc], threads)
+        line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": threads, "kind": "port",
+                                "sample": f"first {nc} reads of rank 0's shard ({nc * T} rows, {dtc:.1f} s), one read per "
+                                          "worker thread; C++ restatement of the reference (Rust toolchain absent)"}
+        print(json.dumps(line))
+    barrier()
+    dec.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--workload", choices=sorted(WORKLOADS), default="viterbi")
+    ap.add_argument("--reads", type=int, default=0, help="override reads per GPU (development only)")
+    args = ap.parse_args()
+    w = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        run_reference(args, w)
+    else:
+        run_ours(args, w)
+
+
+if __name__ == "__main__":
+    main()
