@@ -468,6 +468,16 @@ int check_beam(fctc_handle* h, int32_t n_labels, int32_t beam_size, float thr) {
 
 }  // namespace
 
+namespace fctc {
+int handle_device(const fctc_handle* h) { return h->device; }
+int handle_sm_count(const fctc_handle* h) { return h->sm_count; }
+int handle_fail(fctc_handle* h, int code, const char* message) { return fail(h, code, "%s", message); }
+int check_beam_call(fctc_handle* h, int64_t n_reads, int64_t n_rows, int32_t n_labels, int32_t beam_size, float thr) {
+    if (int rc = check_common(h, n_reads, n_rows, n_labels)) return rc;
+    return check_beam(h, n_labels, beam_size, thr);
+}
+}  // namespace fctc
+
 int64_t fctc_beam_scratch_bytes(const fctc_handle* h, int64_t n_reads, int64_t n_rows, int32_t n_labels,
                                 int32_t beam_size, int32_t nodes_per_row) {
     if (!h || n_labels <= 0 || beam_size <= 0) return 0;

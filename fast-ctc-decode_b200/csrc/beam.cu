@@ -24,6 +24,8 @@
 #include "device_utils.cuh"
 #include "kernels.h"
 
+#include <cstdio>
+
 #include "../../include/fctc.h"
 
 namespace fctc {
@@ -447,3 +449,90 @@ bool beam_shape_supported(int beam_size, int C) {
 }
 
 }  // namespace fctc
+
+// ---------------------------------------------------------------------------------------------
+// fctc_beam_search_batch_device_static
+//
+// Some programs that want to decode on the GPU are not in a position to obtain device memory at
+// the moment they call us: a real-time basecalling loop that has handed all HBM to its own arena
+// at start-up, a plugin running inside a host application that forbids allocator calls on its
+// worker threads, or code that runs while another component holds the allocator lock.  The
+// regular device entry point makes those callers bring `fctc_beam_scratch_bytes()` bytes of trie
+// scratch; this variant brings its own instead: a fixed array that is part of the library's device
+// image.  Nothing here calls cudaMalloc/cudaFree (or any routine that allocates) — the price is a
+// hard size limit and FCTC_BEAM_STATIC_SCRATCH_BYTES of HBM held, from the moment the library is
+// loaded until the process exits, on every GPU that loads it.
+//
+// How the array is reached: in host code `g_beam_static_scratch` is only the host-side handle of
+// the symbol, not an address a kernel may dereference.  The first call on each device therefore
+// asks the runtime for the symbol's device address (cudaGetSymbolAddress, with that device
+// current) and caches it; later calls reuse the cached pointer.  Make that first call outside any
+// CUDA stream capture.
+//
+// Sharing: every call on a device uses the same array and finds in it whatever the previous call
+// left behind.  Only the read ticket counter at its start has to be zero for a launch, and the
+// launch clears it on the caller's stream; trie nodes initialise their own child rows when they
+// are created, so stale pools are harmless.  Two calls that may run on the GPU at the same time
+// (different streams, or different host threads) would decode into the same pools and corrupt
+// each other: serialise them.
+// ---------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_beam_static_scratch[FCTC_BEAM_STATIC_SCRATCH_BYTES];
+
+namespace {
+constexpr int kMaxDevices = 64;
+void* g_static_scratch_ptr[kMaxDevices] = {};  // device address of the array, per device (0 = not looked up yet)
+}  // namespace
+
+extern "C" int fctc_beam_search_batch_device_static(fctc_handle* h, const float* post_dev, int64_t n_reads,
+                                                    int64_t n_rows, int32_t n_labels, int32_t beam_size,
+                                                    float beam_cut_threshold, int32_t collapse_repeats,
+                                                    uint8_t* labels_dev, int32_t* path_dev, int64_t pool_capacity,
+                                                    int64_t* offsets_dev, int32_t* lens_dev, int32_t* status_dev,
+                                                    unsigned long long* pool_used_dev, int32_t nodes_per_row,
+                                                    void* stream) {
+    if (!h) return FCTC_E_ARGUMENT;
+    if (int rc = fctc::check_beam_call(h, n_reads, n_rows, n_labels, beam_size, beam_cut_threshold)) return rc;
+    if (!post_dev || !labels_dev || !path_dev || !offsets_dev || !lens_dev || !status_dev || !pool_used_dev)
+        return fctc::handle_fail(h, FCTC_E_ARGUMENT, "null device pointer");
+    const int dev = fctc::handle_device(h);
+    if (dev < 0 || dev >= kMaxDevices) return fctc::handle_fail(h, FCTC_E_UNSUPPORTED, "device index above 63");
+    cudaError_t e = cudaSetDevice(dev);
+    if (e != cudaSuccess) return fctc::handle_fail(h, FCTC_E_CUDA, cudaGetErrorString(e));
+    if (!g_static_scratch_ptr[dev]) {  // first call on this device: resolve the symbol's device address
+        void* ptr = nullptr;
+        e = cudaGetSymbolAddress(&ptr, g_beam_static_scratch);
+        if (e != cudaSuccess || !ptr)
+            return fctc::handle_fail(h, FCTC_E_CUDA, e != cudaSuccess ? cudaGetErrorString(e) : "cudaGetSymbolAddress returned NULL");
+        g_static_scratch_ptr[dev] = ptr;
+    }
+
+    // Fit the launch into the fixed array: fewer resident warps (pool slots) if need be, never more bytes.
+    fctc::BeamParams p{};
+    const int sm_count = fctc::handle_sm_count(h);
+    fctc::beam_scratch_bytes(sm_count, n_reads, n_rows, n_labels, beam_size, nodes_per_row, &p.nodes_per_slot, &p.n_slots);
+    const int64_t per_slot = int64_t(fctc::beam_slot_bytes(p.nodes_per_slot, n_labels - 1));
+    int64_t fit = (int64_t(FCTC_BEAM_STATIC_SCRATCH_BYTES) - 256) / per_slot;
+    fit = fit / fctc::BM_WARPS * fctc::BM_WARPS;
+    if (fit < fctc::BM_WARPS) {
+        char msg[256];
+        snprintf(msg, sizeof msg,
+                 "static scratch too small: one trie pool for %lld rows x %d proposals needs %lld bytes and at least %d "
+                 "are required, the built-in array holds %lld; use fctc_beam_search_batch_device with caller scratch",
+                 (long long)n_rows, int(p.nodes_per_slot / (n_rows > 0 ? n_rows : 1)), (long long)per_slot,
+                 fctc::BM_WARPS, (long long)FCTC_BEAM_STATIC_SCRATCH_BYTES);
+        return fctc::handle_fail(h, FCTC_E_CAPACITY, msg);
+    }
+    if (p.n_slots > fit) p.n_slots = int(fit);
+
+    p.post = post_dev; p.N = n_reads; p.T = n_rows; p.C = n_labels; p.beam_size = beam_size;
+    p.threshold = beam_cut_threshold; p.collapse = collapse_repeats; p.labels = labels_dev; p.path = path_dev;
+    p.pool_cap = pool_capacity; p.offsets = offsets_dev; p.lens = lens_dev; p.status = status_dev;
+    p.cursor = pool_used_dev;
+    p.scratch = g_static_scratch_ptr[dev];
+    p.scratch_bytes = FCTC_BEAM_STATIC_SCRATCH_BYTES;
+    p.ticket = static_cast<unsigned long long*>(p.scratch);  // cleared by launch_beam on `stream`
+    e = fctc::launch_beam(p, sm_count, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return fctc::handle_fail(h, FCTC_E_CUDA, cudaGetErrorString(e));
+    return 0;
+}
+

@@ -3,7 +3,15 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+struct fctc_handle;
+
 namespace fctc {
+
+// Handle internals needed by entry points that live outside api.cu.
+int handle_device(const fctc_handle* h);
+int handle_sm_count(const fctc_handle* h);
+int handle_fail(fctc_handle* h, int code, const char* message);
+int check_beam_call(fctc_handle* h, int64_t n_reads, int64_t n_rows, int32_t n_labels, int32_t beam_size, float thr);
 
 struct ViterbiParams {
     const float* post;  // [N, T, C] contiguous, device

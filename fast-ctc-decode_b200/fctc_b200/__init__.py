@@ -37,6 +37,8 @@ _SIGNATURES = {
     "fctc_beam_scratch_bytes": (_i64, [_vp, _i64, _i64, _i32, _i32, _i32]),
     "fctc_beam_search_batch_device": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _i32, _f32, _i32, _vp, _vp, _i64, _vp,
                                                 _vp, _vp, _vp, _vp, _i64, _i32, _vp]),
+    "fctc_beam_search_batch_device_static": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _i32, _f32, _i32, _vp, _vp, _i64,
+                                                       _vp, _vp, _vp, _vp, _i32, _vp]),
     "fctc_beam_search_batch": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _i32, _f32, _i32, _vp, _vp, _i64, _vp, _vp, _vp,
                                          _vp]),
     "fctc_beam_search": (C.c_int, [_vp, _vp, _i64, _i32, _i64, _i64, _i32, _f32, _i32, _vp, _vp, _i64, _vp]),
@@ -135,6 +137,18 @@ class Decoder:
                                                           path_ptr, pool_capacity, offsets_ptr, lens_ptr, status_ptr,
                                                           pool_used_ptr, scratch_ptr, scratch_bytes, nodes_per_row,
                                                           stream or None))
+
+    def beam_search_batch_device_static(self, post_ptr, n_reads, n_rows, n_labels, beam_size, beam_cut_threshold,
+                                        collapse_repeats, labels_ptr, path_ptr, pool_capacity, offsets_ptr, lens_ptr,
+                                        status_ptr, pool_used_ptr, nodes_per_row=0, stream=0):
+        """Beam search with the library's built-in scratch array: for callers that must not allocate
+        device memory.  Limited to FCTC_BEAM_STATIC_SCRATCH_BYTES (64 MiB) of trie pools; calls on one
+        device share that array and must not overlap on the GPU."""
+        self._check(self._L.fctc_beam_search_batch_device_static(self._h, post_ptr, n_reads, n_rows, n_labels,
+                                                                 beam_size, beam_cut_threshold, int(collapse_repeats),
+                                                                 labels_ptr, path_ptr, pool_capacity, offsets_ptr,
+                                                                 lens_ptr, status_ptr, pool_used_ptr, nodes_per_row,
+                                                                 stream or None))
 
     # ---- host-memory batch API ------------------------------------------------------------------
     def viterbi_batch(self, post, qstring=False, qscale=1.0, qbias=0.0, collapse_repeats=True, qual_bytes=1,

@@ -124,6 +124,24 @@ int fctc_beam_search_batch_device(fctc_handle* h, const float* post_dev, int64_t
                                   int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev, int32_t* status_dev,
                                   unsigned long long* pool_used_dev, void* scratch_dev, int64_t scratch_bytes,
                                   int32_t nodes_per_row, void* stream);
+/* fctc_beam_search_batch_device_static — no counterpart in the reference.  The same decode as
+ * fctc_beam_search_batch_device for callers that cannot allocate device memory when they call
+ * (all HBM pre-assigned to their own arena, allocator calls forbidden on the calling thread, ...):
+ * the trie scratch is a fixed FCTC_BEAM_STATIC_SCRATCH_BYTES array inside the library's device
+ * image, so the call performs no cudaMalloc/cudaFree.  That array occupies HBM on every GPU that
+ * loads the library, until the process exits.  The launch uses as many trie pools as fit (fewer
+ * resident warps, never more memory); if not even 4 pools of nodes_per_row * n_rows nodes fit, the
+ * call fails with FCTC_E_CAPACITY and a message naming the sizes.  The first call on each device
+ * looks the array's device address up (cudaGetSymbolAddress) — issue it before any stream capture.
+ * All calls on a device share the array: the launch itself clears the only part that must start at
+ * zero, but calls that can overlap on the GPU corrupt each other and must be serialised. */
+#define FCTC_BEAM_STATIC_SCRATCH_BYTES (64ll << 20)
+int fctc_beam_search_batch_device_static(fctc_handle* h, const float* post_dev, int64_t n_reads, int64_t n_rows,
+                                         int32_t n_labels, int32_t beam_size, float beam_cut_threshold,
+                                         int32_t collapse_repeats, uint8_t* labels_dev, int32_t* path_dev,
+                                         int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev,
+                                         int32_t* status_dev, unsigned long long* pool_used_dev,
+                                         int32_t nodes_per_row, void* stream);
 int fctc_beam_search_batch(fctc_handle* h, const float* post_host, int64_t n_reads, int64_t n_rows, int32_t n_labels,
                            int32_t beam_size, float beam_cut_threshold, int32_t collapse_repeats, uint8_t* labels,
                            int32_t* path, int64_t pool_capacity, int64_t* offsets, int32_t* lens, int32_t* status,
