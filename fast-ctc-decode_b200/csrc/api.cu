@@ -43,6 +43,9 @@ struct fctc_handle {
     DevBuf misc;
     void* pinned = nullptr;  // staging for single-read calls
     size_t pinned_bytes = 0;
+    DevBuf extra_dev[16];    // buffers of entry points that live outside api.cu (duplex, crf)
+    void* extra_pin[16] = {};
+    size_t extra_pin_bytes[16] = {};
 };
 
 namespace {
@@ -186,6 +189,9 @@ void fctc_destroy(fctc_handle* h) {
         if (s.stream) cudaStreamDestroy(s.stream);
     }
     release(h->misc);
+    for (DevBuf& b : h->extra_dev) release(b);
+    for (void* q : h->extra_pin)
+        if (q) cudaFreeHost(q);
     if (h->pinned) cudaFreeHost(h->pinned);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -476,6 +482,34 @@ int check_beam_call(fctc_handle* h, int64_t n_reads, int64_t n_rows, int32_t n_l
     if (int rc = check_common(h, n_reads, n_rows, n_labels)) return rc;
     return check_beam(h, n_labels, beam_size, thr);
 }
+int check_threshold_call(fctc_handle* h, int32_t n_labels, int32_t beam_size, float thr) {
+    if (beam_size <= 0) return fail(h, FCTC_E_ARGUMENT, "beam_size cannot be 0");
+    if (thr < -0.0f) return fail(h, FCTC_E_ARGUMENT, "beam_cut_threshold must be at least 0.0");
+    const float max_cut = 1.0f / float(n_labels);
+    if (thr >= max_cut) return fail(h, FCTC_E_ARGUMENT, "beam_cut_threshold cannot be more than %g", max_cut);
+    return 0;
+}
+void* handle_device_buffer(fctc_handle* h, int index, size_t bytes) {
+    if (index < 0 || index >= 16) return nullptr;
+    if (ensure(h, h->extra_dev[index], bytes)) return nullptr;
+    return h->extra_dev[index].p;
+}
+void* handle_pinned_buffer(fctc_handle* h, int index, size_t bytes) {
+    if (index < 0 || index >= 16) return nullptr;
+    if (bytes <= h->extra_pin_bytes[index]) return h->extra_pin[index];
+    if (h->extra_pin[index]) cudaFreeHost(h->extra_pin[index]);
+    h->extra_pin[index] = nullptr;
+    h->extra_pin_bytes[index] = 0;
+    const size_t want = std::max<size_t>(bytes, 256);
+    cudaError_t e = cudaMallocHost(&h->extra_pin[index], want);
+    if (e != cudaSuccess) {
+        fail(h, FCTC_E_NOMEM, "cudaMallocHost(%zu): %s", want, cudaGetErrorString(e));
+        return nullptr;
+    }
+    h->extra_pin_bytes[index] = want;
+    return h->extra_pin[index];
+}
+cudaStream_t handle_stream(fctc_handle* h) { return h->stream; }
 }  // namespace fctc
 
 int64_t fctc_beam_scratch_bytes(const fctc_handle* h, int64_t n_reads, int64_t n_rows, int32_t n_labels,
@@ -616,6 +650,12 @@ uint32_t fctc_host_phred(float prob, float qscale, float qbias) {
     static const double invc[16] = FCTC_LOGF_INVC;
     static const double logc[16] = FCTC_LOGF_LOGC;
     return fctc::phred_code(prob, qscale, qbias, invc, logc);
+}
+
+void fctc_host_logf(const float* x, float* y, int64_t n) {
+    static const double invc[16] = FCTC_LOGF_INVC;
+    static const double logc[16] = FCTC_LOGF_LOGC;
+    for (int64_t i = 0; i < n; ++i) y[i] = fctc::glibc_logf(x[i], invc, logc);
 }
 
 void fctc_host_log10f(const float* x, float* y, int64_t n) {

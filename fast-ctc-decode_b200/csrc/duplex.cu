@@ -1,0 +1,868 @@
+// duplex.cu — batched 2-D ("duplex", pair-consensus) CTC beam search for sm_100a: one warp per pair.
+//
+// Replaces duplex::beam_search (src/duplex.rs:443-650) with its support types: LogSpace
+// (src/duplex.rs:7-80), ProbPair / SearchPoint / SecondaryProbs (:84-210), build_ /
+// extend_secondary_probs (:212-249, :338-387), root_probs (:389-409), and the SuffixTree that
+// carries a SecondaryProbs per node.  Network 1 drives a prefix beam search in log space; every
+// trie node carries the forward probabilities of its labelling over an envelope window of
+// network 2; hypotheses are ranked by P1(node) * max_window P2(node).
+//
+// Organisation (same skeleton as beam.cu):
+//   * one warp per pair, pairs taken from an atomic ticket; lane b owns beam entry b (beam <= 32);
+//   * both networks are mapped to log space with a re-evaluation of glibc's logf (phred.cuh), so
+//     every value that does not pass through exp / log1p is bit-identical to the CPU oracle; in
+//     exp_mode 1 (the reference's default build, whose fastexp() evaluates to 0 and turns
+//     LogSpace '+' into max) the whole search is exact; in exp_mode 0 (exact exp, the parity
+//     target) CUDA's expf / log1pf differ from glibc's in the last bits: tolerance parity;
+//   * a node's SecondaryProbs is a ring buffer of W = max window + 1 cells {label, gap, total} in
+//     HBM scratch (the reference's Vec with discard_until becomes offset/end indices); `total`
+//     (= label (+) gap) is stored so that update_max and children's recurrences need no log-add;
+//   * new nodes of a row are built in parallel, one lane per node (each recurrence is sequential
+//     in the network-2 row index); extension of the beam's nodes runs in lockstep over that index,
+//     which preserves the reference's parents-before-children order (a cell needs its parent's
+//     cell of the previous index only).
+#include <algorithm>
+#include <cstdio>
+
+#include "device_utils.cuh"
+#include "kernels.h"
+#include "phred.cuh"
+
+#include "../../include/fctc.h"
+
+namespace fctc {
+
+constexpr int DX_WARPS = 4;
+constexpr int DX_THREADS = DX_WARPS * 32;
+constexpr int DX_MAX_BEAM = 32;
+constexpr unsigned DXFULL = 0xffffffffu;
+constexpr int DXROOT = -1;
+
+__constant__ double c_dx_invc[16] = FCTC_LOGF_INVC;
+__constant__ double c_dx_logc[16] = FCTC_LOGF_LOGC;
+
+__device__ __forceinline__ float dx_neg_inf() { return __uint_as_float(0xff800000u); }
+
+// LogSpace '+' (src/duplex.rs:42-63): operands ordered so that a+b == b+a, -inf is an exact unit.
+__device__ __forceinline__ float lg_add(float a, float b, int mode) {
+    float big, small;
+    if (a <= b) { big = b; small = a; } else { big = a; small = b; }
+    if (small == dx_neg_inf()) return big;
+    if (mode != 0) return __fadd_rn(big, 0.0f);  // shipped fastexp() == 0: big + ln_1p(0)
+    return __fadd_rn(big, log1pf(expf(__fadd_rn(small, -big))));
+}
+__device__ __forceinline__ float lg_max(float a, float b) { return (a < b) ? b : a; }  // src/duplex.rs:33-39
+
+__device__ __forceinline__ uint32_t dx_order_key(float v) {
+    uint32_t u = __float_as_uint(v);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+struct DuplexLayout {  // per-warp shared memory plan (bytes from the warp's base)
+    int beam_stride;   // one beam buffer: 7 arrays of B words
+    int off_newcnt, off_fold, off_key, off_node, off_lab, off_gap, off_p2, off_sel, off_row, off_root, off_newlist;
+    int warp_bytes;
+    int cta_fixed;
+};
+
+struct DxBeam {
+    int* nd;
+    int* par;
+    int* tip;
+    int* dep;
+    float* lab;
+    float* gap;
+    float* p2;
+};
+__device__ __forceinline__ DxBeam dx_beam(unsigned char* base, int B) {
+    DxBeam v;
+    v.nd = reinterpret_cast<int*>(base);
+    v.par = v.nd + B;
+    v.tip = v.par + B;
+    v.dep = v.tip + B;
+    v.lab = reinterpret_cast<float*>(v.dep + B);
+    v.gap = v.lab + B;
+    v.p2 = v.gap + B;
+    return v;
+}
+
+// Scratch of one warp slot (all sections 256-byte aligned).
+struct DxSlot {
+    float* logp2;   // [T2][C]
+    float* rootv;   // [T2 + 1] running product of network-2 blank probabilities (src/duplex.rs:389-409)
+    int* parent;    // [cap]
+    int* child;     // [cap][C-1]
+    uint8_t* nlab;  // [cap]
+    int* voff;      // [cap]  first valid network-2 index of the node's vector
+    int* vend;      // [cap]  one past the last
+    float* vmx;     // [cap]  max_prob
+    float* vdata;   // [cap][3][W]: label, gap, total
+};
+__host__ __device__ inline size_t dx_up256(size_t v) { return (v + 255) & ~size_t(255); }
+__host__ __device__ inline size_t dx_slot_bytes(long long cap, int T2, int C, int W) {
+    const int NL = C - 1 > 0 ? C - 1 : 1;
+    return dx_up256((size_t)T2 * C * 4) + dx_up256((size_t)(T2 + 1) * 4) + dx_up256((size_t)cap * 4) +
+           dx_up256((size_t)cap * NL * 4) + dx_up256((size_t)cap) + 3 * dx_up256((size_t)cap * 4) +
+           dx_up256((size_t)cap * 3 * (size_t)W * 4);
+}
+__device__ __forceinline__ DxSlot dx_slot(unsigned char* base, long long cap, int T2, int C, int W) {
+    const int NL = C - 1 > 0 ? C - 1 : 1;
+    DxSlot s;
+    unsigned char* p = base;
+    s.logp2 = reinterpret_cast<float*>(p); p += dx_up256((size_t)T2 * C * 4);
+    s.rootv = reinterpret_cast<float*>(p); p += dx_up256((size_t)(T2 + 1) * 4);
+    s.parent = reinterpret_cast<int*>(p);  p += dx_up256((size_t)cap * 4);
+    s.child = reinterpret_cast<int*>(p);   p += dx_up256((size_t)cap * NL * 4);
+    s.nlab = p;                            p += dx_up256((size_t)cap);
+    s.voff = reinterpret_cast<int*>(p);    p += dx_up256((size_t)cap * 4);
+    s.vend = reinterpret_cast<int*>(p);    p += dx_up256((size_t)cap * 4);
+    s.vmx = reinterpret_cast<float*>(p);   p += dx_up256((size_t)cap * 4);
+    s.vdata = reinterpret_cast<float*>(p);
+    return s;
+}
+
+struct DxCell {
+    float label, gap, total;
+};
+
+// SecondaryProbs::get of the parent at index `at` (src/duplex.rs:167-179); only gap and
+// probability() are ever used by the recurrences.
+__device__ __forceinline__ void dx_parent_get(const DxSlot& S, int par, int at, int root_len, int par_end, int W,
+                                              int mode, float& pgap, float& ptotal) {
+    pgap = dx_neg_inf();
+    ptotal = dx_neg_inf();
+    if (par == DXROOT) {
+        const int idx = at + 1;  // root offset is -1
+        if (idx >= 0 && idx < root_len) {
+            pgap = S.rootv[idx];
+            ptotal = lg_add(dx_neg_inf(), pgap, mode);
+        }
+    } else {
+        const int off = S.voff[par];
+        if (at >= off && at < par_end) {
+            const int slot = at % W;
+            const float* v = S.vdata + (size_t)par * 3 * W;
+            pgap = v[W + slot];
+            ptotal = v[2 * W + slot];
+        }
+    }
+}
+
+// One step of the forward recurrence (src/duplex.rs:234-246 and :373-385).
+__device__ __forceinline__ DxCell dx_step(const DxCell& last, float pgap, float ptotal, float p_blank, float p_label,
+                                          bool repeat, int mode) {
+    DxCell c;
+    c.gap = __fadd_rn(last.total, p_blank);
+    c.label = __fadd_rn(p_label, lg_add(last.label, repeat ? pgap : ptotal, mode));
+    c.total = lg_add(c.label, c.gap, mode);
+    return c;
+}
+
+__global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexParams p, const DuplexLayout L) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    double* s_invc = reinterpret_cast<double*>(smem);
+    double* s_logc = s_invc + 16;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x < 16) {
+        s_invc[threadIdx.x] = c_dx_invc[threadIdx.x];
+        s_logc[threadIdx.x] = c_dx_logc[threadIdx.x];
+    }
+    __syncthreads();
+    const int slot_id = blockIdx.x * DX_WARPS + warp;
+    if (slot_id >= p.n_slots) return;
+    unsigned char* ws = smem + L.cta_fixed + (size_t)warp * L.warp_bytes;
+    const int B = p.beam_size, C = p.C, NL = C - 1;
+    const int T1 = p.T1, T2 = p.T2, W = p.W;
+    const int mode = p.exp_mode;
+    const bool collapse = p.collapse != 0;
+    const float NEG = dx_neg_inf();
+
+    int* newcnt = reinterpret_cast<int*>(ws + L.off_newcnt);
+    unsigned char* fold = ws + L.off_fold;
+    uint32_t* ckey = reinterpret_cast<uint32_t*>(ws + L.off_key);
+    int* cnode = reinterpret_cast<int*>(ws + L.off_node);
+    float* clab = reinterpret_cast<float*>(ws + L.off_lab);
+    float* cgap = reinterpret_cast<float*>(ws + L.off_gap);
+    float* cp2 = reinterpret_cast<float*>(ws + L.off_p2);
+    int* sel = reinterpret_cast<int*>(ws + L.off_sel);
+    float* lp1 = reinterpret_cast<float*>(ws + L.off_row);
+    int* root_child = reinterpret_cast<int*>(ws + L.off_root);
+    int* newlist = reinterpret_cast<int*>(ws + L.off_newlist);
+
+    const long long cap = p.nodes_per_slot;
+    const DxSlot S = dx_slot(static_cast<unsigned char*>(p.scratch) + 256 + (size_t)slot_id * dx_slot_bytes(cap, T2, C, W),
+                             cap, T2, C, W);
+    const float thr = glibc_logf(p.threshold, s_invc, s_logc);  // src/duplex.rs:454
+
+    for (int i = lane; i < B * (NL > 0 ? NL : 1); i += 32) fold[i] = 0;
+
+    for (;;) {
+        unsigned long long ticket = 0;
+        if (lane == 0) ticket = atomicAdd(p.ticket, 1ull);
+        ticket = __shfl_sync(DXFULL, ticket, 0);
+        if (ticket >= (unsigned long long)p.N) break;
+        const long long n = (long long)ticket;
+        const float* rd1 = p.post1 + n * (long long)T1 * C;
+        const float* rd2 = p.post2 + n * (long long)T2 * C;
+        const long long* env = p.env ? p.env + n * (long long)T1 * 2 : nullptr;
+        int status = FCTC_OK;
+
+        // network 2 in log space (src/duplex.rs:453)
+        for (int i = lane; i < T2 * C; i += 32) S.logp2[i] = glibc_logf(rd2[i], s_invc, s_logc);
+        // root vector over envelope[(0,1)] rows (src/duplex.rs:476-477, 389-409)
+        unsigned long long ub0 = env ? (unsigned long long)env[1] : (unsigned long long)T2;
+        if (ub0 > (unsigned long long)T2) status = FCTC_INVALID_ENVELOPE;  // the reference would panic on the slice
+        __syncwarp();
+        int root_len = 0;
+        if (status == FCTC_OK) {
+            root_len = int(ub0) + 1;
+            if (lane == 0) {
+                float cur = 0.0f;
+                S.rootv[0] = cur;
+                for (int i = 0; i < int(ub0); ++i) {
+                    cur = __fadd_rn(cur, S.logp2[(size_t)i * C]);
+                    S.rootv[i + 1] = cur;
+                }
+            }
+        }
+        int cur = 0;
+        DxBeam bv = dx_beam(ws, B);
+        if (lane == 0) {  // src/duplex.rs:465-473
+            bv.nd[0] = DXROOT; bv.par[0] = -2; bv.tip[0] = -1; bv.dep[0] = 0;
+            bv.lab[0] = NEG; bv.gap[0] = 0.0f; bv.p2[0] = 0.0f;
+        }
+        for (int l = lane; l < NL; l += 32) root_child[l] = -1;
+        int nbeam = 1;
+        long long n_nodes = 0;
+        int last_hi = 0;
+        __syncwarp();
+
+        for (int t = 0; t < T1 && status == FCTC_OK; ++t) {
+            // ---- envelope row (src/duplex.rs:485-488) ----------------------------------------------
+            const unsigned long long lo_u = env ? (unsigned long long)env[2 * t] : 0ull;
+            const unsigned long long hi_u = env ? (unsigned long long)env[2 * t + 1] : (unsigned long long)T2;
+            const int hi = hi_u > (unsigned long long)T2 ? T2 : int(hi_u);
+            if (lo_u >= (unsigned long long)hi || lo_u > (unsigned long long)last_hi) {
+                status = FCTC_INVALID_ENVELOPE;
+                break;
+            }
+            const int lo = int(lo_u);
+            if (hi - lo + 1 > W) {  // window wider than the scratch plan (max_window too small)
+                status = FCTC_NODE_POOL_OVERFLOW;
+                break;
+            }
+            for (int c = lane; c < C; c += 32) lp1[c] = glibc_logf(rd1[(size_t)t * C + c], s_invc, s_logc);
+
+            // ---- extend the vectors of the beam's nodes (src/duplex.rs:490-522) ----------------------
+            if (hi > last_hi) {
+                // beam.sort_by_key(node): parents before children; node ids are unique in the beam
+                DxBeam nb = dx_beam(ws + (cur ^ 1) * L.beam_stride, B);
+                if (lane < nbeam) {
+                    const int me = bv.nd[lane];
+                    int r = 0;
+                    for (int k = 0; k < nbeam; ++k) r += (bv.nd[k] < me) ? 1 : 0;
+                    nb.nd[r] = me; nb.par[r] = bv.par[lane]; nb.tip[r] = bv.tip[lane]; nb.dep[r] = bv.dep[lane];
+                    nb.lab[r] = bv.lab[lane]; nb.gap[r] = bv.gap[lane]; nb.p2[r] = bv.p2[lane];
+                }
+                __syncwarp();
+                cur ^= 1;
+                bv = nb;
+
+                const int node = (lane < nbeam) ? bv.nd[lane] : DXROOT;
+                const bool active = node >= 0;
+                int my_par = -2, my_lab = 0, v_end = 0, par_end = 0;
+                bool repeat = false;
+                float mx = NEG;
+                DxCell last{NEG, NEG, NEG};
+                float* vd = nullptr;
+                if (active) {
+                    my_par = bv.par[lane];
+                    my_lab = bv.tip[lane];
+                    vd = S.vdata + (size_t)node * 3 * W;
+                    int off = S.voff[node];
+                    v_end = S.vend[node];
+                    mx = S.vmx[node];
+                    if (lo > off) {  // src/duplex.rs:351-359
+                        const int keep = lo - 1;
+                        if (keep > off) {  // discard_until (:181-191)
+                            if (keep - off >= v_end - off) v_end = keep;  // cleared
+                            off = keep;
+                        }
+                        if (v_end == off) { off = lo; v_end = lo; }
+                        // update_max(lo, hi) (:193-204)
+                        const int b0 = lo > off ? lo : off;
+                        const int e0 = hi < v_end ? hi : v_end;
+                        mx = NEG;
+                        for (int i = b0; i < e0; ++i) mx = lg_max(mx, vd[2 * W + (i % W)]);
+                        S.voff[node] = off;
+                    }
+                    if (v_end > off) {
+                        const int sl = (v_end - 1) % W;
+                        last.label = vd[sl]; last.gap = vd[W + sl]; last.total = vd[2 * W + sl];
+                    }
+                    // the parent's label decides the repeat case, independent of collapse (:511)
+                    const int plab = (my_par >= 0) ? int(S.nlab[my_par]) : -1;
+                    repeat = (plab == my_lab);
+                    bool par_in_beam = false;
+                    for (int k = 0; k < nbeam; ++k) par_in_beam |= (bv.nd[k] == my_par);
+                    par_end = (my_par >= 0) ? ((par_in_beam) ? hi : S.vend[my_par]) : 0;
+                }
+                __syncwarp();  // every node's new offset is visible before children read their parents
+                int imin = active ? v_end : hi;
+#pragma unroll
+                for (int d = 16; d > 0; d >>= 1) {
+                    const int o = __shfl_xor_sync(DXFULL, imin, d);
+                    imin = o < imin ? o : imin;
+                }
+                for (int i = imin; i < hi; ++i) {  // lockstep over the network-2 row index
+                    if (active && v_end <= i) {
+                        float pgap, ptot;
+                        // a parent that is in the beam has (by now) cells up to i-1; others are as stored
+                        dx_parent_get(S, my_par, i - 1, root_len, (my_par >= 0 && par_end == hi) ? i : par_end, W, mode,
+                                      pgap, ptot);
+                        const DxCell c = dx_step(last, pgap, ptot, S.logp2[(size_t)i * C], S.logp2[(size_t)i * C + my_lab + 1],
+                                                 repeat, mode);
+                        const int sl = i % W;
+                        vd[sl] = c.label; vd[W + sl] = c.gap; vd[2 * W + sl] = c.total;
+                        mx = lg_max(mx, c.total);
+                        last = c;
+                    }
+                    __syncwarp();
+                }
+                if (active) {
+                    S.vend[node] = hi;
+                    S.vmx[node] = mx;
+                }
+                __syncwarp();
+            }
+            last_hi = hi;
+            __syncwarp();  // lp1 row visible to every lane
+
+            const float p_blank = lp1[0];
+            DxBeam nb = dx_beam(ws + (cur ^ 1) * L.beam_stride, B);
+
+            // ---- phase A: own continuation (+ the parent's extension, folded in) ------------------
+            if (lane < nbeam) {
+                const int b = lane;
+                const int node = bv.nd[b];
+                const float lab = bv.lab[b], gap = bv.gap[b];
+                const int tip = bv.tip[b];
+                bool has_self = false;
+                float s_lab = NEG, s_gap = NEG;
+                if (p_blank > thr) {  // src/duplex.rs:529-534
+                    s_gap = __fadd_rn(lg_add(lab, gap, mode), p_blank);
+                    has_self = true;
+                }
+                if (collapse && tip >= 0) {  // :540-544
+                    const float pt = lp1[tip + 1];
+                    if (!(pt < thr)) {
+                        s_lab = __fadd_rn(lab, pt);
+                        has_self = true;
+                    }
+                }
+                if (has_self && node != DXROOT) {
+                    const int mypar = bv.par[b];
+                    int r = -1;
+                    for (int k = 0; k < nbeam; ++k)
+                        if (bv.nd[k] == mypar) r = k;
+                    if (r >= 0) {
+                        const float pt = lp1[tip + 1];
+                        if (!(pt < thr)) {
+                            float c;
+                            if (collapse && bv.tip[r] == tip) c = __fadd_rn(bv.gap[r], pt);           // :563-568
+                            else c = __fadd_rn(lg_add(bv.lab[r], bv.gap[r], mode), pt);               // :586-590
+                            s_lab = lg_add(s_lab, c, mode);                                            // :604
+                            fold[r * NL + tip] = 1;
+                        }
+                    }
+                }
+                const int s0 = b * C;
+                cnode[s0] = node;
+                clab[s0] = s_lab;
+                cgap[s0] = s_gap;
+                cp2[s0] = bv.p2[b];
+                ckey[s0] = has_self ? 1u : 0u;
+            }
+            __syncwarp();
+
+            // ---- phase B1: child proposals; new nodes get provisional ids -2-k -----------------------
+            int n_new = 0;
+            if (lane < nbeam) {
+                const int b = lane;
+                const int node = bv.nd[b];
+                const float lab = bv.lab[b], gap = bv.gap[b];
+                const int tip = bv.tip[b];
+                for (int l = 0; l < NL; ++l) {
+                    const int s = b * C + 1 + l;
+                    const float pl = lp1[l + 1];
+                    uint32_t key = 0;
+                    if (!(pl < thr)) {  // :537-539
+                        const bool repeat = collapse && l == tip;
+                        int x = (node == DXROOT) ? root_child[l] : S.child[(size_t)node * NL + l];
+                        bool take = true;
+                        if (x < 0) {
+                            if (repeat && !(gap > NEG)) take = false;  // :545-561
+                            else x = -2 - (n_new++);
+                        } else if (fold[b * NL + l]) {
+                            fold[b * NL + l] = 0;
+                            take = false;
+                        }
+                        if (take) {
+                            cnode[s] = x;
+                            clab[s] = repeat ? __fadd_rn(gap, pl) : __fadd_rn(lg_add(lab, gap, mode), pl);
+                            cgap[s] = NEG;
+                            cp2[s] = bv.p2[b];
+                            key = 1u;
+                        }
+                    }
+                    ckey[s] = key;
+                }
+            }
+            const int incl = warp_inclusive_scan(n_new, lane);
+            const int total_new = __shfl_sync(DXFULL, incl, 31);
+            const int my_base = incl - n_new;
+            if (n_nodes + total_new > cap) {
+                status = FCTC_NODE_POOL_OVERFLOW;
+                break;
+            }
+            // list the new nodes in creation order (beam rank major, label minor)
+            if (lane < nbeam) {
+                int k = 0;
+                for (int l = 0; l < NL; ++l) {
+                    const int s = lane * C + 1 + l;
+                    if (ckey[s] != 0u && cnode[s] <= -2) {
+                        newlist[my_base + k] = (lane << 16) | l;
+                        cnode[s] = int(n_nodes) + my_base + k;
+                        ++k;
+                    }
+                }
+            }
+            __syncwarp();
+
+            // ---- phase B2: build the new nodes' vectors, one lane per node (src/duplex.rs:212-249) ----
+            for (int j0 = 0; j0 < total_new; j0 += 32) {
+                const int j = j0 + lane;
+                if (j < total_new) {
+                    const int b = newlist[j] >> 16, l = newlist[j] & 0xffff;
+                    const int id = int(n_nodes) + j;
+                    const int pnode = bv.nd[b];
+                    const bool repeat = collapse && l == bv.tip[b];
+                    const int par_end = (pnode >= 0) ? S.vend[pnode] : 0;
+                    float* vd = S.vdata + (size_t)id * 3 * W;
+                    DxCell last{NEG, NEG, NEG};
+                    float mx = NEG;
+                    int sl = lo % W;
+                    for (int i = lo; i < hi; ++i) {
+                        float pgap, ptot;
+                        dx_parent_get(S, pnode, i - 1, root_len, par_end, W, mode, pgap, ptot);
+                        const DxCell c = dx_step(last, pgap, ptot, S.logp2[(size_t)i * C], S.logp2[(size_t)i * C + l + 1], repeat, mode);
+                        vd[sl] = c.label; vd[W + sl] = c.gap; vd[2 * W + sl] = c.total;
+                        mx = lg_max(mx, c.total);
+                        last = c;
+                        if (++sl == W) sl = 0;
+                    }
+                    S.parent[id] = pnode;
+                    S.nlab[id] = uint8_t(l);
+                    S.voff[id] = lo;
+                    S.vend[id] = hi;
+                    S.vmx[id] = mx;
+                    for (int q = 0; q < NL; ++q) S.child[(size_t)id * NL + q] = -1;
+                    if (pnode == DXROOT) root_child[l] = id;
+                    else S.child[(size_t)pnode * NL + l] = id;
+                }
+            }
+            n_nodes += total_new;
+            __syncwarp();
+
+            // ---- refresh prob_2_max, scores (src/duplex.rs:613-630) -------------------------------------
+            bool any_nan = false;
+            int n_cand = 0;
+            if (lane < nbeam) {
+                for (int sl = 0; sl < C; ++sl) {
+                    const int s = lane * C + sl;
+                    if (ckey[s] == 0u) continue;
+                    const int node = cnode[s];
+                    if (node >= 0) cp2[s] = S.vmx[node];
+                    const float tot = __fadd_rn(__fadd_rn(lg_add(clab[s], cgap[s], mode), cp2[s]), 0.0f);
+                    if (tot != tot) any_nan = true;
+                    ckey[s] = (tot != tot) ? 1u : dx_order_key(tot);
+                    ++n_cand;
+                }
+            }
+            n_cand = __reduce_add_sync(DXFULL, n_cand);
+            any_nan = __any_sync(DXFULL, any_nan);
+            __syncwarp();
+            if (n_cand >= 2 && any_nan) { status = FCTC_INCOMPARABLE_VALUES; break; }
+            if (n_cand == 0) { status = FCTC_RAN_OUT_OF_BEAM; break; }
+
+            // ---- ranking (as beam.cu) -----------------------------------------------------------------------
+            const int n_slots_c = nbeam * C;
+            const int n_keep = n_cand < B ? n_cand : B;
+            uint32_t best_hi = 0, best_lo = 0;
+            int best_i = -1;
+            auto rescan = [&]() {
+                best_hi = 0; best_lo = 0; best_i = -1;
+                for (int i = lane; i < n_slots_c; i += 32) {
+                    const uint32_t k = ckey[i];
+                    if (k == 0u) continue;
+                    const uint32_t lo2 = 0x7FFFFFFFu - uint32_t(cnode[i]);
+                    if (k > best_hi || (k == best_hi && lo2 > best_lo)) { best_hi = k; best_lo = lo2; best_i = i; }
+                }
+            };
+            rescan();
+            for (int r = 0; r < n_keep; ++r) {
+                const uint32_t m1 = __reduce_max_sync(DXFULL, best_hi);
+                const uint32_t m2 = __reduce_max_sync(DXFULL, best_hi == m1 ? best_lo : 0u);
+                if (best_hi == m1 && best_lo == m2) {
+                    sel[r] = best_i;
+                    ckey[best_i] = 0u;
+                    rescan();
+                }
+            }
+            __syncwarp();
+            if (lane < n_keep) {
+                const int i = sel[lane];
+                const int b = i / C, sl = i - b * C;
+                nb.nd[lane] = cnode[i];
+                nb.lab[lane] = clab[i];
+                nb.gap[lane] = cgap[i];
+                nb.p2[lane] = cp2[i];
+                if (sl == 0) { nb.par[lane] = bv.par[b]; nb.tip[lane] = bv.tip[b]; nb.dep[lane] = bv.dep[b]; }
+                else { nb.par[lane] = bv.nd[b]; nb.tip[lane] = sl - 1; nb.dep[lane] = bv.dep[b] + 1; }
+            }
+            __syncwarp();
+            cur ^= 1;
+            bv = nb;
+            nbeam = n_keep;
+        }
+        if (status != FCTC_OK)
+            for (int i = lane; i < B * (NL > 0 ? NL : 1); i += 32) fold[i] = 0;
+        __syncwarp();
+
+        // ---- labels of the best hypothesis (src/duplex.rs:638-649) -----------------------------------------------
+        if (lane == 0) {
+            int len = 0;
+            long long off = 0;
+            if (status == FCTC_OK) {
+                len = bv.dep[0];
+                const unsigned long long want = (unsigned long long)((len + 31) & ~31);
+                const unsigned long long o = atomicAdd(p.cursor, want);
+                if (o + want > (unsigned long long)p.pool_cap) {
+                    status = FCTC_OUTPUT_OVERFLOW;
+                    len = 0;
+                } else {
+                    off = (long long)o;
+                    int node = bv.nd[0];
+                    for (int k = len - 1; k >= 0; --k) {
+                        p.labels[off + k] = uint8_t(S.nlab[node] + 1);
+                        node = S.parent[node];
+                    }
+                }
+            }
+            p.offsets[n] = off;
+            p.lens[n] = len;
+            p.status[n] = status;
+        }
+        __syncwarp();
+    }
+}
+
+static bool plan_duplex(int B, int C, DuplexLayout* L) {
+    if (B > DX_MAX_BEAM || B < 1 || C < 1 || C > 256) return false;
+    const int NL = C - 1 > 0 ? C - 1 : 1;
+    auto up = [](long long v, int a) { return (v + a - 1) / a * a; };
+    L->beam_stride = int(up(7LL * 4 * B, 16));
+    long long o = 2LL * L->beam_stride;
+    L->off_newcnt = int(o);  o = up(o + 4LL * B, 16);
+    L->off_fold = int(o);    o = up(o + (long long)B * NL, 16);
+    const long long nc = (long long)B * C;
+    L->off_key = int(o);     o = up(o + 4 * nc, 16);
+    L->off_node = int(o);    o = up(o + 4 * nc, 16);
+    L->off_lab = int(o);     o = up(o + 4 * nc, 16);
+    L->off_gap = int(o);     o = up(o + 4 * nc, 16);
+    L->off_p2 = int(o);      o = up(o + 4 * nc, 16);
+    L->off_sel = int(o);     o = up(o + 4LL * B, 16);
+    L->off_row = int(o);     o = up(o + 4LL * C, 16);
+    L->off_root = int(o);    o = up(o + 4LL * NL, 16);
+    L->off_newlist = int(o); o = up(o + 4LL * B * NL, 16);
+    L->warp_bytes = int(up(o, 128));
+    L->cta_fixed = 256;
+    return L->cta_fixed + (long long)L->warp_bytes * DX_WARPS <= 200 * 1024;
+}
+
+bool duplex_shape_supported(int beam_size, int C) {
+    DuplexLayout L;
+    return plan_duplex(beam_size, C, &L);
+}
+
+static int dx_default_nodes_per_row(int C, int B) {
+    const long long bound = (long long)(C - 1) * B;
+    long long d = 2LL * B;
+    if (d < 12) d = 12;
+    if (d > bound) d = bound;
+    if (d < 1) d = 1;
+    return int(d);
+}
+
+int64_t duplex_scratch_bytes(int sm_count, int64_t N, int T1, int T2, int C, int beam_size, int W, int nodes_per_row,
+                             int64_t budget_bytes, int64_t* nodes_per_slot, int* n_slots) {
+    if (nodes_per_row <= 0) nodes_per_row = dx_default_nodes_per_row(C, beam_size);
+    const long long bound = (long long)(C - 1) * beam_size;
+    if (nodes_per_row > bound) nodes_per_row = int(bound > 0 ? bound : 1);
+    const long long cap = (long long)nodes_per_row * (T1 > 0 ? T1 : 1);
+    const long long per_slot = (long long)dx_slot_bytes(cap, T2, C, W);
+    long long slots = (long long)sm_count * 16;
+    if (slots > N) slots = N;
+    if (slots < 1) slots = 1;
+    slots = (slots + DX_WARPS - 1) / DX_WARPS * DX_WARPS;
+    if (budget_bytes > 0) {  // fewer pairs in flight rather than more memory
+        long long fit = (budget_bytes - 256) / per_slot;
+        fit = fit / DX_WARPS * DX_WARPS;
+        if (fit < DX_WARPS) fit = DX_WARPS;
+        if (slots > fit) slots = fit;
+    }
+    if (nodes_per_slot) *nodes_per_slot = cap;
+    if (n_slots) *n_slots = int(slots);
+    return 256 + slots * per_slot;
+}
+
+cudaError_t launch_duplex(const DuplexParams& p, cudaStream_t stream) {
+    if (p.N <= 0) return cudaSuccess;
+    DuplexLayout L;
+    if (!plan_duplex(p.beam_size, p.C, &L)) return cudaErrorInvalidConfiguration;
+    const int smem = L.cta_fixed + L.warp_bytes * DX_WARPS;
+    cudaError_t e = cudaFuncSetAttribute(duplex_search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    e = cudaMemsetAsync(p.ticket, 0, sizeof(unsigned long long), stream);
+    if (e != cudaSuccess) return e;
+    duplex_search_kernel<<<p.n_slots / DX_WARPS, DX_THREADS, smem, stream>>>(p, L);
+    return cudaGetLastError();
+}
+
+}  // namespace fctc
+
+// =============================================================================================
+// C ABI (include/fctc.h)
+// =============================================================================================
+namespace {
+
+int dx_check(fctc_handle* h, int64_t n_pairs, int64_t T1, int64_t T2, int32_t C, int32_t beam, float thr) {
+    if (!h) return FCTC_E_ARGUMENT;
+    if (n_pairs < 0 || T1 < 0 || T2 < 0) return fctc::handle_fail(h, FCTC_E_ARGUMENT, "negative size");
+    if (C <= 0) return fctc::handle_fail(h, FCTC_E_ARGUMENT, "Empty alphabet given");
+    if (C > 256) return fctc::handle_fail(h, FCTC_E_UNSUPPORTED, "alphabets above 256 labels are not supported");
+    if (T1 == 0) return fctc::handle_fail(h, FCTC_E_ARGUMENT, "network_output_1 has no rows (the reference aborts on envelope[(0,1)])");
+    if (T1 >= (1 << 30) || T2 >= (1 << 30) || T2 * int64_t(C) >= (int64_t(1) << 31))
+        return fctc::handle_fail(h, FCTC_E_UNSUPPORTED, "network outputs above 2^30 rows are not supported");
+    if (int rc = fctc::check_threshold_call(h, C, beam, thr)) return rc;  // src/lib.rs:433-443
+    if (!fctc::duplex_shape_supported(beam, C))
+        return fctc::handle_fail(h, FCTC_E_UNSUPPORTED, "duplex search supports beam_size <= 32 in this release");
+    return 0;
+}
+
+int64_t dx_free_budget() {
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return int64_t(8) << 30;
+    return int64_t(free_b / 2);
+}
+
+}  // namespace
+
+extern "C" int64_t fctc_duplex_scratch_bytes(const fctc_handle* h, int64_t n_pairs, int64_t n_rows_1, int64_t n_rows_2,
+                                             int32_t n_labels, int32_t beam_size, int32_t max_window,
+                                             int32_t nodes_per_row) {
+    if (!h || n_labels <= 0 || beam_size <= 0 || n_rows_1 <= 0 || n_rows_2 < 0) return 0;
+    const int W = int((max_window > 0 && max_window < n_rows_2 ? max_window : n_rows_2) + 1);
+    return fctc::duplex_scratch_bytes(fctc::handle_sm_count(h), n_pairs, int(n_rows_1), int(n_rows_2), n_labels, beam_size, W,
+                                      nodes_per_row, 0, nullptr, nullptr);
+}
+
+extern "C" int fctc_beam_search_duplex_batch_device(fctc_handle* h, const float* post1_dev, const float* post2_dev,
+                                                    int64_t n_pairs, int64_t n_rows_1, int64_t n_rows_2,
+                                                    int32_t n_labels, const int64_t* envelope_dev, int32_t max_window,
+                                                    int32_t beam_size, float beam_cut_threshold,
+                                                    int32_t collapse_repeats, int32_t exp_mode, uint8_t* labels_dev,
+                                                    int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev,
+                                                    int32_t* status_dev, unsigned long long* pool_used_dev,
+                                                    void* scratch_dev, int64_t scratch_bytes, int32_t nodes_per_row,
+                                                    void* stream) {
+    if (int rc = dx_check(h, n_pairs, n_rows_1, n_rows_2, n_labels, beam_size, beam_cut_threshold)) return rc;
+    if (!post1_dev || !post2_dev || !labels_dev || !offsets_dev || !lens_dev || !status_dev || !pool_used_dev || !scratch_dev)
+        return fctc::handle_fail(h, FCTC_E_ARGUMENT, "null device pointer");
+    if (reinterpret_cast<uintptr_t>(scratch_dev) & 255u)
+        return fctc::handle_fail(h, FCTC_E_ARGUMENT, "scratch_dev must be 256-byte aligned");
+    if (exp_mode != 0 && exp_mode != 1) return fctc::handle_fail(h, FCTC_E_ARGUMENT, "exp_mode must be 0 (exact exp) or 1 (fastexp as shipped)");
+    cudaError_t e = cudaSetDevice(fctc::handle_device(h));
+    if (e != cudaSuccess) return fctc::handle_fail(h, FCTC_E_CUDA, cudaGetErrorString(e));
+    fctc::DuplexParams p{};
+    p.W = int((max_window > 0 && max_window < n_rows_2 ? max_window : n_rows_2) + 1);
+    // use as many pair slots as the caller's scratch holds
+    const int64_t need = fctc::duplex_scratch_bytes(fctc::handle_sm_count(h), n_pairs, int(n_rows_1), int(n_rows_2), n_labels,
+                                                    beam_size, p.W, nodes_per_row, scratch_bytes, &p.nodes_per_slot, &p.n_slots);
+    if (need > scratch_bytes) {
+        char msg[200];
+        snprintf(msg, sizeof msg, "duplex scratch too small: %lld bytes given, %lld needed for %d pair slots",
+                 (long long)scratch_bytes, (long long)need, p.n_slots);
+        return fctc::handle_fail(h, FCTC_E_CAPACITY, msg);
+    }
+    p.post1 = post1_dev; p.post2 = post2_dev; p.env = reinterpret_cast<const long long*>(envelope_dev);
+    p.N = n_pairs; p.T1 = int(n_rows_1); p.T2 = int(n_rows_2); p.C = n_labels; p.beam_size = beam_size;
+    p.threshold = beam_cut_threshold; p.collapse = collapse_repeats; p.exp_mode = exp_mode;
+    p.labels = labels_dev; p.pool_cap = pool_capacity; p.offsets = offsets_dev; p.lens = lens_dev; p.status = status_dev;
+    p.cursor = pool_used_dev; p.scratch = scratch_dev; p.ticket = static_cast<unsigned long long*>(scratch_dev);
+    e = fctc::launch_duplex(p, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return fctc::handle_fail(h, FCTC_E_CUDA, cudaGetErrorString(e));
+    return 0;
+}
+
+namespace {
+
+// One synchronous pass over pairs [first, first+cnt) of host arrays.  Results are appended to the
+// host pool at *used.
+int dx_host_chunk(fctc_handle* h, const float* post1, const float* post2, const int64_t* env, int64_t cnt, int64_t T1,
+                  int64_t T2, int32_t C, int W, int32_t beam, float thr, int32_t collapse, int32_t exp_mode,
+                  int32_t nodes_per_row, uint8_t* labels, int64_t pool_cap, int64_t* offsets, int32_t* lens,
+                  int32_t* status, int64_t* used) {
+    cudaStream_t st = fctc::handle_stream(h);
+    const int64_t stride = (T1 + 31) & ~int64_t(31);
+    const size_t b1 = size_t(cnt) * T1 * C * 4, b2 = size_t(cnt) * T2 * C * 4, be = size_t(cnt) * T1 * 16;
+    float* d1 = static_cast<float*>(fctc::handle_device_buffer(h, 0, b1));
+    float* d2 = static_cast<float*>(fctc::handle_device_buffer(h, 1, std::max<size_t>(b2, 16)));
+    long long* de = env ? static_cast<long long*>(fctc::handle_device_buffer(h, 2, be)) : nullptr;
+    uint8_t* dl = static_cast<uint8_t*>(fctc::handle_device_buffer(h, 3, size_t(cnt * stride)));
+    int64_t* doff = static_cast<int64_t*>(fctc::handle_device_buffer(h, 4, size_t(cnt) * 8));
+    int32_t* dlen = static_cast<int32_t*>(fctc::handle_device_buffer(h, 5, size_t(cnt) * 4));
+    int32_t* dst = static_cast<int32_t*>(fctc::handle_device_buffer(h, 6, size_t(cnt) * 4));
+    unsigned long long* dcur = static_cast<unsigned long long*>(fctc::handle_device_buffer(h, 7, 256));
+    unsigned long long* hcur = static_cast<unsigned long long*>(fctc::handle_pinned_buffer(h, 0, 64));
+    if (!d1 || !d2 || (env && !de) || !dl || !doff || !dlen || !dst || !dcur || !hcur) return FCTC_E_NOMEM;
+    fctc::DuplexParams p{};
+    p.W = W;
+    const int64_t need = fctc::duplex_scratch_bytes(fctc::handle_sm_count(h), cnt, int(T1), int(T2), C, beam, W, nodes_per_row,
+                                                    dx_free_budget(), &p.nodes_per_slot, &p.n_slots);
+    void* scratch = fctc::handle_device_buffer(h, 8, size_t(need));
+    if (!scratch) return FCTC_E_NOMEM;
+#define DX_CUDA(call)                                                                          \
+    do {                                                                                       \
+        cudaError_t e__ = (call);                                                              \
+        if (e__ != cudaSuccess) return fctc::handle_fail(h, FCTC_E_CUDA, cudaGetErrorString(e__)); \
+    } while (0)
+    DX_CUDA(cudaMemcpyAsync(d1, post1, b1, cudaMemcpyHostToDevice, st));
+    if (b2) DX_CUDA(cudaMemcpyAsync(d2, post2, b2, cudaMemcpyHostToDevice, st));
+    if (env) DX_CUDA(cudaMemcpyAsync(de, env, be, cudaMemcpyHostToDevice, st));
+    DX_CUDA(cudaMemsetAsync(dcur, 0, 8, st));
+    p.post1 = d1; p.post2 = d2; p.env = de; p.N = cnt; p.T1 = int(T1); p.T2 = int(T2); p.C = C; p.beam_size = beam;
+    p.threshold = thr; p.collapse = collapse; p.exp_mode = exp_mode; p.labels = dl; p.pool_cap = cnt * stride;
+    p.offsets = doff; p.lens = dlen; p.status = dst; p.cursor = dcur; p.scratch = scratch;
+    p.ticket = static_cast<unsigned long long*>(scratch);
+    DX_CUDA(fctc::launch_duplex(p, st));
+    DX_CUDA(cudaMemcpyAsync(hcur, dcur, 8, cudaMemcpyDeviceToHost, st));
+    DX_CUDA(cudaMemcpyAsync(offsets, doff, size_t(cnt) * 8, cudaMemcpyDeviceToHost, st));
+    DX_CUDA(cudaMemcpyAsync(lens, dlen, size_t(cnt) * 4, cudaMemcpyDeviceToHost, st));
+    DX_CUDA(cudaMemcpyAsync(status, dst, size_t(cnt) * 4, cudaMemcpyDeviceToHost, st));
+    DX_CUDA(cudaStreamSynchronize(st));
+    const int64_t got = int64_t(*hcur);
+    if (*used + got > pool_cap) return fctc::handle_fail(h, FCTC_E_CAPACITY, "result pool too small (n_pairs*round_up(n_rows_1,32) always suffices)");
+    if (got) DX_CUDA(cudaMemcpyAsync(labels + *used, dl, size_t(got), cudaMemcpyDeviceToHost, st));
+    DX_CUDA(cudaStreamSynchronize(st));
+#undef DX_CUDA
+    for (int64_t i = 0; i < cnt; ++i) offsets[i] += *used;
+    *used += got;
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int fctc_beam_search_duplex_batch(fctc_handle* h, const float* post1_host, const float* post2_host,
+                                             int64_t n_pairs, int64_t n_rows_1, int64_t n_rows_2, int32_t n_labels,
+                                             const int64_t* envelope_host, int32_t beam_size, float beam_cut_threshold,
+                                             int32_t collapse_repeats, int32_t exp_mode, uint8_t* labels,
+                                             int64_t pool_capacity, int64_t* offsets, int32_t* lens, int32_t* status,
+                                             int64_t* pool_used) {
+    if (int rc = dx_check(h, n_pairs, n_rows_1, n_rows_2, n_labels, beam_size, beam_cut_threshold)) return rc;
+    if (!post1_host || (!post2_host && n_rows_2 > 0) || !labels || !offsets || !lens || !status)
+        return fctc::handle_fail(h, FCTC_E_ARGUMENT, "null host pointer");
+    if (exp_mode != 0 && exp_mode != 1) return fctc::handle_fail(h, FCTC_E_ARGUMENT, "exp_mode must be 0 (exact exp) or 1 (fastexp as shipped)");
+    cudaError_t e = cudaSetDevice(fctc::handle_device(h));
+    if (e != cudaSuccess) return fctc::handle_fail(h, FCTC_E_CUDA, cudaGetErrorString(e));
+    if (pool_used) *pool_used = 0;
+    if (n_pairs == 0) return 0;
+    // ring size of the per-node vectors: the widest window the envelope asks for (clamped as the
+    // kernel clamps), or all of network 2 without an envelope
+    int64_t wmax = n_rows_2;
+    if (envelope_host) {
+        wmax = 1;
+        for (int64_t i = 0; i < n_pairs * n_rows_1; ++i) {
+            const uint64_t lo = uint64_t(envelope_host[2 * i]), hi_u = uint64_t(envelope_host[2 * i + 1]);
+            const int64_t hi = hi_u > uint64_t(n_rows_2) ? n_rows_2 : int64_t(hi_u);
+            if (lo < uint64_t(hi) && hi - int64_t(lo) > wmax) wmax = hi - int64_t(lo);
+        }
+    }
+    const int W = int(wmax + 1);
+    const int64_t pair_bytes = (n_rows_1 + n_rows_2) * int64_t(n_labels) * 4;
+    const int64_t chunk = std::max<int64_t>(1, std::min<int64_t>(n_pairs, (int64_t(256) << 20) / std::max<int64_t>(pair_bytes, 1)));
+    int64_t used = 0;
+    for (int64_t first = 0; first < n_pairs; first += chunk) {
+        const int64_t cnt = std::min(chunk, n_pairs - first);
+        if (int rc = dx_host_chunk(h, post1_host + first * n_rows_1 * n_labels, post2_host + first * n_rows_2 * n_labels,
+                                   envelope_host ? envelope_host + first * n_rows_1 * 2 : nullptr, cnt, n_rows_1, n_rows_2,
+                                   n_labels, W, beam_size, beam_cut_threshold, collapse_repeats, exp_mode, 0, labels,
+                                   pool_capacity, offsets + first, lens + first, status + first, &used))
+            return rc;
+    }
+    // pairs whose trie outgrew the default pool: again, one at a time, at the hard bound
+    const int32_t bound = std::max<int32_t>(1, (n_labels - 1) * beam_size);
+    for (int64_t n = 0; n < n_pairs; ++n) {
+        if (status[n] != FCTC_NODE_POOL_OVERFLOW) continue;
+        if (int rc = dx_host_chunk(h, post1_host + n * n_rows_1 * n_labels, post2_host + n * n_rows_2 * n_labels,
+                                   envelope_host ? envelope_host + n * n_rows_1 * 2 : nullptr, 1, n_rows_1, n_rows_2, n_labels, W,
+                                   beam_size, beam_cut_threshold, collapse_repeats, exp_mode, bound, labels, pool_capacity,
+                                   offsets + n, lens + n, status + n, &used))
+            return rc;
+    }
+    if (pool_used) *pool_used = used;
+    return 0;
+}
+
+extern "C" int fctc_beam_search_duplex(fctc_handle* h, const float* post1_host, int64_t n_rows_1, int64_t stride_row_1,
+                                       int64_t stride_label_1, const float* post2_host, int64_t n_rows_2,
+                                       int64_t stride_row_2, int64_t stride_label_2, int32_t n_labels,
+                                       const uint64_t* envelope, int64_t env_stride_row, int64_t env_stride_col,
+                                       int32_t beam_size, float beam_cut_threshold, int32_t collapse_repeats,
+                                       int32_t exp_mode, uint8_t* labels, int64_t capacity, int64_t* out_len) {
+    if (int rc = dx_check(h, 1, n_rows_1, n_rows_2, n_labels, beam_size, beam_cut_threshold)) return rc;
+    if (!post1_host || (!post2_host && n_rows_2 > 0) || !out_len) return fctc::handle_fail(h, FCTC_E_ARGUMENT, "null pointer");
+    const int64_t stride = std::max<int64_t>((n_rows_1 + 31) & ~int64_t(31), 32);
+    const size_t o2 = (size_t(n_rows_1) * n_labels * 4 + 255) & ~size_t(255);
+    const size_t oe = (o2 + size_t(n_rows_2) * n_labels * 4 + 255) & ~size_t(255);
+    const size_t ol = (oe + size_t(n_rows_1) * 16 + 255) & ~size_t(255);
+    const size_t om = ol + size_t(stride);
+    unsigned char* pin = static_cast<unsigned char*>(fctc::handle_pinned_buffer(h, 1, om + 64));
+    if (!pin) return FCTC_E_NOMEM;
+    float* p1 = reinterpret_cast<float*>(pin);
+    float* p2 = reinterpret_cast<float*>(pin + o2);
+    int64_t* env = reinterpret_cast<int64_t*>(pin + oe);
+    for (int64_t t = 0; t < n_rows_1; ++t)
+        for (int32_t c = 0; c < n_labels; ++c) p1[t * n_labels + c] = post1_host[t * stride_row_1 + c * stride_label_1];
+    for (int64_t t = 0; t < n_rows_2; ++t)
+        for (int32_t c = 0; c < n_labels; ++c) p2[t * n_labels + c] = post2_host[t * stride_row_2 + c * stride_label_2];
+    if (envelope)
+        for (int64_t t = 0; t < n_rows_1; ++t) {
+            env[2 * t] = int64_t(envelope[t * env_stride_row]);
+            env[2 * t + 1] = int64_t(envelope[t * env_stride_row + env_stride_col]);
+        }
+    int64_t* off1 = reinterpret_cast<int64_t*>(pin + om);
+    int32_t* len1 = reinterpret_cast<int32_t*>(pin + om + 8);
+    int32_t* st1 = reinterpret_cast<int32_t*>(pin + om + 16);
+    int64_t used = 0;
+    int rc = fctc_beam_search_duplex_batch(h, p1, p2, 1, n_rows_1, n_rows_2, n_labels, envelope ? env : nullptr, beam_size,
+                                           beam_cut_threshold, collapse_repeats, exp_mode, pin + ol, stride, off1, len1, st1,
+                                           &used);
+    if (rc < 0) return rc;
+    *out_len = *len1;
+    const int64_t m = std::min<int64_t>(*len1, capacity);
+    for (int64_t i = 0; i < m; ++i)
+        if (labels) labels[i] = pin[ol + *off1 + i];
+    return *st1;
+}
+

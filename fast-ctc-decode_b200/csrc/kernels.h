@@ -12,6 +12,11 @@ int handle_device(const fctc_handle* h);
 int handle_sm_count(const fctc_handle* h);
 int handle_fail(fctc_handle* h, int code, const char* message);
 int check_beam_call(fctc_handle* h, int64_t n_reads, int64_t n_rows, int32_t n_labels, int32_t beam_size, float thr);
+int check_threshold_call(fctc_handle* h, int32_t n_labels, int32_t beam_size, float thr);  // src/lib.rs:433-443
+// Persistent, growable device / pinned-host buffers owned by the handle (index 0..15 each).
+void* handle_device_buffer(fctc_handle* h, int index, size_t bytes);  // NULL on failure (error text set)
+void* handle_pinned_buffer(fctc_handle* h, int index, size_t bytes);
+cudaStream_t handle_stream(fctc_handle* h);
 
 struct ViterbiParams {
     const float* post;  // [N, T, C] contiguous, device
@@ -60,6 +65,33 @@ struct BeamParams {
 int64_t beam_scratch_bytes(int sm_count, int64_t N, int64_t T, int C, int beam_size, int nodes_per_row,
                            int64_t* nodes_per_slot, int* n_slots);
 cudaError_t launch_beam(const BeamParams& p, int sm_count, cudaStream_t stream);
+
+struct DuplexParams {
+    const float* post1;    // [N, T1, C]
+    const float* post2;    // [N, T2, C]
+    const long long* env;  // [N, T1, 2] network-2 row bounds per network-1 row, or NULL (= [0, T2) everywhere)
+    int64_t N;
+    int T1, T2, C;
+    int beam_size;
+    float threshold;
+    int collapse;
+    int exp_mode;  // 0 exact exp (parity target), 1 the reference's default build (fastexp == 0: '+' is max)
+    int W;         // ring size of a node's vector: max window + 1
+    uint8_t* labels;
+    int64_t pool_cap;
+    int64_t* offsets;
+    int32_t* lens;
+    int32_t* status;
+    unsigned long long* cursor;
+    void* scratch;
+    int64_t nodes_per_slot;
+    int n_slots;
+    unsigned long long* ticket;
+};
+bool duplex_shape_supported(int beam_size, int C);
+int64_t duplex_scratch_bytes(int sm_count, int64_t N, int T1, int T2, int C, int beam_size, int W, int nodes_per_row,
+                             int64_t budget_bytes, int64_t* nodes_per_slot, int* n_slots);
+cudaError_t launch_duplex(const DuplexParams& p, cudaStream_t stream);
 
 cudaError_t launch_synth(float* post, int64_t N, int64_t T, int C, int kind, uint64_t seed, int64_t first_read,
                          cudaStream_t stream);

@@ -42,9 +42,18 @@ _SIGNATURES = {
     "fctc_beam_search_batch": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _i32, _f32, _i32, _vp, _vp, _i64, _vp, _vp, _vp,
                                          _vp]),
     "fctc_beam_search": (C.c_int, [_vp, _vp, _i64, _i32, _i64, _i64, _i32, _f32, _i32, _vp, _vp, _i64, _vp]),
+    "fctc_duplex_scratch_bytes": (_i64, [_vp, _i64, _i64, _i64, _i32, _i32, _i32, _i32]),
+    "fctc_beam_search_duplex_batch_device": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i64, _i32, _vp, _i32, _i32, _f32,
+                                                       _i32, _i32, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _i64, _i32,
+                                                       _vp]),
+    "fctc_beam_search_duplex_batch": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i64, _i32, _vp, _i32, _f32, _i32, _i32,
+                                                _vp, _i64, _vp, _vp, _vp, _vp]),
+    "fctc_beam_search_duplex": (C.c_int, [_vp, _vp, _i64, _i64, _i64, _vp, _i64, _i64, _i64, _i32, _vp, _i64, _i64,
+                                          _i32, _f32, _i32, _i32, _vp, _i64, _vp]),
     "fctc_synth_posteriors_device": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _i32, _u64, _i64, _vp]),
     "fctc_host_phred": (C.c_uint32, [_f32, _f32, _f32]),
     "fctc_host_log10f": (None, [_vp, _vp, _i64]),
+    "fctc_host_logf": (None, [_vp, _vp, _i64]),
 }
 
 
@@ -199,6 +208,60 @@ class Decoder:
                                                    labels.size, offsets.ctypes.data, lens.ctypes.data,
                                                    status.ctypes.data, C.byref(used)))
         return dict(labels=labels, path=path, offsets=offsets, lens=lens, status=status, used=used.value)
+
+    def beam_search_duplex_batch(self, post1, post2, envelope=None, beam_size=5, beam_cut_threshold=0.0,
+                                 collapse_repeats=True, exp_mode=0):
+        """post1 [N,T1,C], post2 [N,T2,C] float32 C-contiguous; envelope int64 [N,T1,2] or None."""
+        post1, post2 = _as_f32_3d(post1), _as_f32_3d(post2)
+        N, T1, Cn = post1.shape
+        T2 = post2.shape[1]
+        if post2.shape[0] != N or post2.shape[2] != Cn:
+            raise ValueError("inner axes of the network outputs do not match")
+        env = None
+        if envelope is not None:
+            env = np.ascontiguousarray(envelope, dtype=np.int64)
+            if env.shape != (N, T1, 2):
+                raise ValueError("envelope must have shape [N, T1, 2]")
+        cap = N * max(round_up32(T1), 32)
+        labels = np.empty(cap, np.uint8)
+        offsets = np.empty(N, np.int64)
+        lens = np.empty(N, np.int32)
+        status = np.empty(N, np.int32)
+        used = _i64(0)
+        self._check(self._L.fctc_beam_search_duplex_batch(self._h, post1.ctypes.data, post2.ctypes.data, N, T1, T2, Cn,
+                                                          _np_ptr(env), beam_size, beam_cut_threshold,
+                                                          int(collapse_repeats), exp_mode, labels.ctypes.data, cap,
+                                                          offsets.ctypes.data, lens.ctypes.data, status.ctypes.data,
+                                                          C.byref(used)))
+        return dict(labels=labels, offsets=offsets, lens=lens, status=status, used=used.value)
+
+    def beam_search_duplex(self, post1, post2, envelope=None, beam_size=5, beam_cut_threshold=0.0,
+                           collapse_repeats=True, exp_mode=0):
+        post1, post2 = _as_f32_2d(post1), _as_f32_2d(post2)
+        T1, Cn = post1.shape
+        T2 = post2.shape[0]
+        if post2.shape[1] != Cn:
+            raise ValueError("inner axes of the network outputs do not match")
+        s1r, s1c = (s // 4 for s in post1.strides)
+        s2r, s2c = (s // 4 for s in post2.strides)
+        env, er, ec = None, 0, 0
+        if envelope is not None:
+            env = np.asarray(envelope)
+            if env.dtype != np.uint64:
+                raise TypeError("envelope must be a uint64 (usize) array")
+            if env.shape[0] != T1:
+                raise ValueError("the lengths of network_output_1 and envelope do not match")
+            if env.ndim != 2 or env.shape[1] != 2:
+                raise ValueError("the inner axis of envelope must have size 2")
+            er, ec = (s // 8 for s in env.strides)
+        cap = max(T1, 1)
+        labels = np.empty(cap, np.uint8)
+        n = _i64(0)
+        status = self._check(self._L.fctc_beam_search_duplex(self._h, post1.ctypes.data, T1, s1r, s1c,
+                                                             post2.ctypes.data, T2, s2r, s2c, Cn, _np_ptr(env), er, ec,
+                                                             beam_size, beam_cut_threshold, int(collapse_repeats),
+                                                             exp_mode, labels.ctypes.data, cap, C.byref(n)))
+        return status, labels[:n.value].copy()
 
     # ---- single-read API (shape of the pyo3 functions; any strides) --------------------------------
     def viterbi_search(self, post, qstring=False, qscale=1.0, qbias=0.0, collapse_repeats=True):

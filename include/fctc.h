@@ -151,6 +151,42 @@ int fctc_beam_search(fctc_handle* h, const float* post_host, int64_t n_rows, int
                      uint8_t* labels, int64_t* path, int64_t capacity, int64_t* out_len);
 
 /* ------------------------------------------------------------------------------------------
+ * 2-D ("duplex") beam search — replaces duplex::beam_search, src/duplex.rs:443-650, with LogSpace
+ * (:7-80; fastexp src/fastexp.rs), ProbPair/SearchPoint/SecondaryProbs (:84-210), build_/
+ * extend_secondary_probs (:212-249, :338-387) and root_probs (:389-409), as called from
+ * src/lib.rs:475-483.  Two posterior arrays per pair, [n_rows_1, C] and [n_rows_2, C]; `envelope`
+ * gives, per network-1 row, the [lower, upper) network-2 rows to align against ([n_pairs,
+ * n_rows_1, 2]; NULL = all of network 2, src/lib.rs:457-469).  Output: labels only (the reference
+ * returns just the sequence).  exp_mode 0 = exact exp (the --no-default-features build, the parity
+ * target), 1 = the reference's default build (its fastexp() evaluates to 0, so '+' is max).
+ * beam_size <= 32 in this release.  max_window (device API): the widest upper-lower of the
+ * envelope, 0 = n_rows_2; a row wider than that gets FCTC_NODE_POOL_OVERFLOW.  The device API
+ * uses as many pair slots as scratch_bytes holds (at least 4 must fit).
+ * ------------------------------------------------------------------------------------------ */
+int64_t fctc_duplex_scratch_bytes(const fctc_handle* h, int64_t n_pairs, int64_t n_rows_1, int64_t n_rows_2,
+                                  int32_t n_labels, int32_t beam_size, int32_t max_window, int32_t nodes_per_row);
+int fctc_beam_search_duplex_batch_device(fctc_handle* h, const float* post1_dev, const float* post2_dev,
+                                         int64_t n_pairs, int64_t n_rows_1, int64_t n_rows_2, int32_t n_labels,
+                                         const int64_t* envelope_dev, int32_t max_window, int32_t beam_size,
+                                         float beam_cut_threshold, int32_t collapse_repeats, int32_t exp_mode,
+                                         uint8_t* labels_dev, int64_t pool_capacity, int64_t* offsets_dev,
+                                         int32_t* lens_dev, int32_t* status_dev, unsigned long long* pool_used_dev,
+                                         void* scratch_dev, int64_t scratch_bytes, int32_t nodes_per_row, void* stream);
+int fctc_beam_search_duplex_batch(fctc_handle* h, const float* post1_host, const float* post2_host, int64_t n_pairs,
+                                  int64_t n_rows_1, int64_t n_rows_2, int32_t n_labels, const int64_t* envelope_host,
+                                  int32_t beam_size, float beam_cut_threshold, int32_t collapse_repeats,
+                                  int32_t exp_mode, uint8_t* labels, int64_t pool_capacity, int64_t* offsets,
+                                  int32_t* lens, int32_t* status, int64_t* pool_used);
+/* One pair, any strides (elements) — the shape of the pyo3 entry point src/lib.rs:402-488;
+ * envelope is the reference's usize array [n_rows_1, 2] (strides in elements) or NULL. */
+int fctc_beam_search_duplex(fctc_handle* h, const float* post1_host, int64_t n_rows_1, int64_t stride_row_1,
+                            int64_t stride_label_1, const float* post2_host, int64_t n_rows_2, int64_t stride_row_2,
+                            int64_t stride_label_2, int32_t n_labels, const uint64_t* envelope,
+                            int64_t env_stride_row, int64_t env_stride_col, int32_t beam_size,
+                            float beam_cut_threshold, int32_t collapse_repeats, int32_t exp_mode, uint8_t* labels,
+                            int64_t capacity, int64_t* out_len);
+
+/* ------------------------------------------------------------------------------------------
  * Synthetic posterior generator used by bench.py and the tests (no reference counterpart; it
  * implements SURVEY.md §8d's input definition): fills post_dev[n_reads, n_rows, n_labels] with
  * kind 0: softmax(3*(2u-1)) rows, kind 1: peaked rows (dominant label, blank w.p. 0.65),
@@ -163,6 +199,7 @@ int fctc_synth_posteriors_device(fctc_handle* h, float* post_dev, int64_t n_read
  * that CPU tests can compare it with glibc without a GPU.  Replaces nothing; test hook. */
 uint32_t fctc_host_phred(float prob, float qscale, float qbias);
 void fctc_host_log10f(const float* x, float* y, int64_t n);
+void fctc_host_logf(const float* x, float* y, int64_t n);
 
 #ifdef __cplusplus
 }

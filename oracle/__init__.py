@@ -39,6 +39,8 @@ def lib():
         L.oracle_phred.argtypes = [C.c_float, C.c_float, C.c_float, C.POINTER(C.c_int)]
         L.oracle_log10f_n.restype = None
         L.oracle_log10f_n.argtypes = [vp, vp, i64]
+        L.oracle_logf_n.restype = None
+        L.oracle_logf_n.argtypes = [vp, vp, i64]
         L.oracle_fastexp_as_shipped.restype = C.c_float
         L.oracle_fastexp_as_shipped.argtypes = [C.c_float]
         L.oracle_logadd.restype = C.c_float

@@ -737,6 +737,8 @@ uint32_t oracle_phred(float prob, float qscale, float qbias, int* valid) {
 // glibc's log10f over an array: what Rust's f32::log10 calls on linux-gnu (src/search.rs:34)
 void oracle_log10f_n(const float* x, float* y, int64_t n) { for (int64_t i = 0; i < n; ++i) y[i] = log10f(x[i]); }
 
+void oracle_logf_n(const float* x, float* y, int64_t n) { for (int64_t i = 0; i < n; ++i) y[i] = logf(x[i]); }
+
 float oracle_fastexp_as_shipped(float a) { return fastexp_as_shipped(a); }
 float oracle_logadd(float a, float b, int exp_mode) { g_exp_mode = exp_mode; return (Lg{a} + Lg{b}).v; }
 

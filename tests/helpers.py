@@ -40,3 +40,30 @@ def peaked_posteriors(rng, shape, p_blank=0.65):
     x[np.arange(n), dom] = 1.0
     x /= x.sum(axis=1, keepdims=True, dtype=np.float32)
     return x.reshape(shape).astype(np.float32)
+
+
+def duplex_pairs(rng, n_pairs, T1, T2, C=5, p_blank=0.6, noise=0.08):
+    """Template/complement-like posterior pairs: one hidden label track rendered twice with
+    independent noise; the second rendering is resampled to T2 rows."""
+    hid = np.where(rng.random((n_pairs, T1)) < p_blank, 0, rng.integers(1, C, (n_pairs, T1)))
+
+    def render(track, T):
+        idx = np.minimum((np.arange(T) * track.shape[1]) // max(T, 1), track.shape[1] - 1)
+        tr = track[:, idx]
+        x = (noise * rng.random((n_pairs, T, C), dtype=np.float32)).astype(np.float32)
+        n, t = np.meshgrid(np.arange(n_pairs), np.arange(T), indexing="ij")
+        x[n, t, tr] = 1.0
+        flip = rng.random((n_pairs, T)) < 0.05  # a few disagreeing rows
+        x[flip] = rng.random((int(flip.sum()), C), dtype=np.float32)
+        x /= x.sum(axis=2, keepdims=True, dtype=np.float32)
+        return x.astype(np.float32)
+    return render(hid, T1), render(hid, T2)
+
+
+def band_envelope(n_pairs, T1, T2, half_width):
+    """Monotone band [max(0, c-w), min(T2, c+w+1)) around the diagonal."""
+    c = (np.arange(T1) * T2) // max(T1, 1)
+    lo = np.maximum(0, c - half_width)
+    hi = np.minimum(T2, c + half_width + 1)
+    env = np.stack([lo, hi], axis=1).astype(np.int64)
+    return np.ascontiguousarray(np.broadcast_to(env, (n_pairs, T1, 2)))

@@ -70,6 +70,25 @@ def test_log10f_replica_matches_glibc(fctc, oracle):
     assert np.array_equal(mine.view(np.uint32), ref.view(np.uint32))
 
 
+def test_logf_replica_matches_glibc(fctc, oracle):
+    """The duplex kernel maps posteriors to log space with the same re-evaluation of glibc's logf;
+    sweep every binade incl. subnormals, plus the special values."""
+    L, O = fctc.lib(), oracle.lib()
+    bits = np.concatenate([
+        np.arange(0x00000001, 0x7F800000, 4099, dtype=np.uint32),
+        np.array([0, 0x80000000, 0x7F800000, 0xFF800000, 0x7FC00000, 0xBF800000, 0x3F800000, 0x00800000, 0x007FFFFF, 1],
+                 dtype=np.uint32),
+    ])
+    x = bits.view(np.float32).copy()
+    mine = np.empty_like(x)
+    ref = np.empty_like(x)
+    L.fctc_host_logf(x.ctypes.data, mine.ctypes.data, x.size)
+    O.oracle_logf_n(x.ctypes.data, ref.ctypes.data, x.size)
+    nan = np.isnan(ref)
+    assert np.array_equal(np.isnan(mine), nan)
+    assert np.array_equal(mine.view(np.uint32)[~nan], ref.view(np.uint32)[~nan])
+
+
 def test_phred_host_build_matches_oracle(fctc, oracle):
     L = fctc.lib()
     rng = np.random.default_rng(3)

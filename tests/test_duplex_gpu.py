@@ -1,0 +1,113 @@
+"""GPU parity tests for the 2-D (duplex) beam search through the C ABI vs the CPU oracle.
+
+exp_mode 1 (the reference's default build: fastexp() == 0, LogSpace '+' is max) involves no
+exp/log1p at all and the kernel maps inputs to log space with glibc's logf algorithm, so results
+must be identical.  exp_mode 0 (exact exp, the north-star parity target) goes through CUDA's
+expf/log1pf, which differ from glibc's in the last bits: sequences are compared with a tolerance
+on the fraction of identical pairs (SURVEY.md §7 hard part 7)."""
+import numpy as np
+import pytest
+
+from helpers import band_envelope, duplex_pairs, load_kats, softmax_posteriors
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def dec():
+    import fctc_b200
+    d = fctc_b200.Decoder(0)
+    yield d
+    d.close()
+
+
+def seqs(res):
+    return [res["labels"][o:o + n].tolist() for o, n in zip(res["offsets"], res["lens"])]
+
+
+@pytest.mark.parametrize("exp_mode", [0, 1])
+@pytest.mark.parametrize("kat", [pytest.param(k, id=k["name"]) for k in load_kats() if k["fn"] == "beam_search_duplex"])
+def test_reference_kats(dec, oracle, kat, exp_mode):
+    a = np.asarray(kat["post"], np.float32)
+    b = np.asarray(kat["post2"], np.float32)
+    st, labels = dec.beam_search_duplex(a, b, None, kat["beam_size"], kat["beam_cut_threshold"], kat["collapse_repeats"],
+                                        exp_mode)
+    assert st == 0
+    assert oracle.to_text(kat["alphabet"], labels) == kat["expect_seq"]
+
+
+CASES = [
+    # n_pairs, T1, T2, C, beam, thr, collapse, band half width (None = default full envelope)
+    (12, 200, 200, 5, 5, 0.0, True, 8), (12, 200, 230, 5, 5, 0.1, True, 12), (8, 300, 300, 5, 5, 0.0, False, 6),
+    (6, 120, 120, 5, 5, 0.0, True, None), (6, 150, 140, 3, 5, 0.0, True, 10), (4, 200, 200, 5, 16, 0.0, True, 8),
+    (4, 160, 160, 5, 32, 0.0, True, 5), (6, 100, 100, 5, 1, 0.0, True, 4), (3, 1, 7, 5, 5, 0.0, True, None),
+    (4, 400, 400, 5, 5, 0.1, True, 32),
+]
+
+
+@pytest.mark.parametrize("case", CASES, ids=lambda c: "N{}_T{}x{}_C{}_b{}_thr{}_c{}_w{}".format(*c))
+def test_max_plus_mode_is_exact(dec, oracle, case):
+    N, T1, T2, Cn, beam, thr, collapse, w = case
+    rng = np.random.default_rng(1009 * (N + T1 + T2 + beam))
+    p1, p2 = duplex_pairs(rng, N, T1, T2, Cn)
+    env = None if w is None else band_envelope(N, T1, T2, w)
+    res = dec.beam_search_duplex_batch(p1, p2, env, beam, thr, collapse, exp_mode=1)
+    ol, olen, ost = oracle.beam_search_duplex_batch(p1, p2, None if env is None else env.astype(np.uint64), beam, thr,
+                                                    collapse, exp_mode=1)
+    assert res["status"].tolist() == ost.tolist()
+    got = seqs(res)
+    want = [ol[n, :olen[n]].tolist() for n in range(N)]
+    assert got == want
+
+
+@pytest.mark.parametrize("case", CASES, ids=lambda c: "N{}_T{}x{}_C{}_b{}_thr{}_c{}_w{}".format(*c))
+def test_exact_exp_mode_tolerance(dec, oracle, case):
+    N, T1, T2, Cn, beam, thr, collapse, w = case
+    rng = np.random.default_rng(2003 * (N + T1 + T2 + beam))
+    p1, p2 = duplex_pairs(rng, N, T1, T2, Cn)
+    env = None if w is None else band_envelope(N, T1, T2, w)
+    res = dec.beam_search_duplex_batch(p1, p2, env, beam, thr, collapse, exp_mode=0)
+    ol, olen, ost = oracle.beam_search_duplex_batch(p1, p2, None if env is None else env.astype(np.uint64), beam, thr,
+                                                    collapse, exp_mode=0)
+    assert res["status"].tolist() == ost.tolist()
+    got = seqs(res)
+    want = [ol[n, :olen[n]].tolist() for n in range(N)]
+    same = sum(g == w_ for g, w_ in zip(got, want))
+    # last-bit differences of expf/log1pf may flip a near-tie in a few pairs; lengths must stay close
+    assert same >= int(np.ceil(0.75 * N)), f"only {same}/{N} pairs identical"
+    for g, w_ in zip(got, want):
+        assert abs(len(g) - len(w_)) <= max(2, len(w_) // 20)
+
+
+def test_error_statuses(dec, oracle):
+    import fctc_b200
+    rng = np.random.default_rng(5)
+    p1, p2 = duplex_pairs(rng, 4, 60, 60)
+    p1[1] = np.nan                                     # tests/test_decode.py:370-374
+    env = band_envelope(4, 60, 60, 6)
+    env[2, 30:, 0] += 40                               # lower bound jumps past the last upper bound
+    env[3, 10, :] = (20, 20)                           # empty window
+    res = dec.beam_search_duplex_batch(p1, p2, env, 5, 0.0, True, exp_mode=0)
+    ol, olen, ost = oracle.beam_search_duplex_batch(p1, p2, env.astype(np.uint64), 5, 0.0, True, 0)
+    assert res["status"].tolist() == ost.tolist() == [0, fctc_b200.INCOMPARABLE_VALUES, fctc_b200.INVALID_ENVELOPE,
+                                                      fctc_b200.INVALID_ENVELOPE]
+    st, labels = dec.beam_search_duplex(p1[1], p2[1])
+    assert st == fctc_b200.INCOMPARABLE_VALUES
+    assert fctc_b200.lib().fctc_status_message(3) == b"Invalid envelope values"
+    with pytest.raises(fctc_b200.FctcError):
+        dec.beam_search_duplex(p1[0], p2[0], beam_size=0)
+    with pytest.raises(ValueError):
+        dec.beam_search_duplex(p1[0], p2[0][:, :4])
+    with pytest.raises(ValueError):
+        dec.beam_search_duplex(p1[0], p2[0], np.zeros((59, 2), np.uint64))
+
+
+def test_single_pair_with_envelope_and_strides(dec, oracle):
+    rng = np.random.default_rng(6)
+    p1, p2 = duplex_pairs(rng, 1, 90, 100)
+    big1 = np.zeros((180, 10), np.float32)
+    big1[::2, ::2] = p1[0]
+    env = band_envelope(1, 90, 100, 9)[0].astype(np.uint64)
+    st, labels = dec.beam_search_duplex(big1[::2, ::2], p2[0], env, 5, 0.0, True, exp_mode=1)
+    ost, ol = oracle.beam_search_duplex(p1[0], p2[0], env, 5, 0.0, True, exp_mode=1)
+    assert st == ost == 0 and labels.tolist() == ol.tolist()
