@@ -65,6 +65,7 @@ struct BeamView {  // one beam buffer
     int* tip;
     float* lp;
     float* gp;
+    int* st;  // crf transition state (src/search.rs:11-12); unused by the plain search
 };
 __device__ __forceinline__ BeamView beam_view(unsigned char* base, int B) {
     BeamView v;
@@ -74,9 +75,14 @@ __device__ __forceinline__ BeamView beam_view(unsigned char* base, int B) {
     v.tip = v.dep + B;
     v.lp = reinterpret_cast<float*>(v.tip + B);
     v.gp = v.lp + B;
+    v.st = reinterpret_cast<int*>(v.gp + B);
     return v;
 }
 
+// CRF = true gives search::crf_beam_search (src/search.rs:38-157): posteriors are [T, S, C], every
+// hypothesis carries a transition state and reads row probs[t][state][:], a label moves it to
+// (state * n_base) % n_state + label, and there is no repeat-collapse case.
+template <bool CRF>
 __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParams p, const BeamLayout L) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -86,7 +92,8 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
     const int B = p.beam_size, C = p.C, NL = C - 1;
     const long long T = p.T;
     const float thr = p.threshold;
-    const bool collapse = p.collapse != 0;
+    const bool collapse = !CRF && p.collapse != 0;
+    const int S = CRF ? p.S : 1;
 
     int* newcnt = reinterpret_cast<int*>(ws + L.off_newcnt);
     unsigned char* fold = ws + L.off_fold;
@@ -116,21 +123,36 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
         ticket = __shfl_sync(FULL, ticket, 0);
         if (ticket >= (unsigned long long)p.N) break;
         const long long n = (long long)ticket;
-        const float* rd = p.post + n * T * C;
+        const float* rd = p.post + n * T * C * S;
 
         int cur = 0;
         BeamView bv = beam_view(ws, B);
+        int status = FCTC_OK;
         if (lane == 0) {  // src/search.rs:170-175
             bv.nd[0] = ROOT; bv.par[0] = -2; bv.dep[0] = 0; bv.tip[0] = -1; bv.lp[0] = 0.0f; bv.gp[0] = 1.0f;
+            bv.st[0] = 0;
+            if (CRF) {  // src/search.rs:54-59: label_prob = max(init), gap_prob = init[0], state = argmax(init)
+                const float* init = p.init + n * p.n_init;
+                float best = init[0];
+                int arg = 0;
+                bool bad = (best != best) && p.n_init > 1;
+                for (int i = 1; i < p.n_init; ++i) {
+                    const float v = init[i];
+                    if (v != v) bad = true;
+                    if (v > best) { best = v; arg = i; }
+                }
+                bv.lp[0] = best; bv.gp[0] = init[0]; bv.st[0] = arg;
+                if (bad || arg >= S) status = FCTC_REFERENCE_PANIC;  // unwrap() on a NaN / slice out of range
+            }
         }
+        status = __shfl_sync(FULL, status, 0);
         for (int l = lane; l < NL; l += 32) root_child[l] = -1;
         int nbeam = 1;
         long long n_nodes = 0;
-        int status = FCTC_OK;
 
-        // prefetch chunk 0 of the posterior rows
+        // prefetch chunk 0 of the posterior rows (the crf search reads its state-dependent rows directly)
         float pre[BM_ROWBUF / 32];
-        {
+        if (!CRF) {
             const long long total = T * C;
 #pragma unroll
             for (int j = 0; j < BM_ROWBUF / 32; ++j) {
@@ -142,12 +164,14 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
 
         for (long long t0 = 0; t0 < T && status == FCTC_OK; t0 += R) {
             float* rows = rowbuf + ((t0 / R) & 1) * BM_ROWBUF;
+            if (!CRF) {
 #pragma unroll
-            for (int j = 0; j < BM_ROWBUF / 32; ++j) {
-                const int e = lane + 32 * j;
-                if (e < chunk_elems) rows[e] = pre[j];
+                for (int j = 0; j < BM_ROWBUF / 32; ++j) {
+                    const int e = lane + 32 * j;
+                    if (e < chunk_elems) rows[e] = pre[j];
+                }
             }
-            {   // start loading the next chunk; it lands while this one is processed
+            if (!CRF) {   // start loading the next chunk; it lands while this one is processed
                 const long long base = (t0 + R) * C, total = T * C;
 #pragma unroll
                 for (int j = 0; j < BM_ROWBUF / 32; ++j) {
@@ -160,8 +184,8 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
 
             for (int rr = 0; rr < rows_here && status == FCTC_OK; ++rr) {
                 const long long t = t0 + rr;
-                const float* pr = rows + rr * C;
-                const float p_blank = pr[0];
+                const float* pr_shared = rows + rr * C;
+                const float* pr_time = rd + t * S * C;  // crf: [S][C] block of this time step
                 BeamView nb = beam_view(ws + (cur ^ 1) * L.beam_stride, B);
 
                 // ---- phase A: each hypothesis' own continuation, plus its parent's extension -------
@@ -169,6 +193,8 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
                     const int node = bv.nd[b];
                     const float lp = bv.lp[b], gp = bv.gp[b];
                     const int tip = bv.tip[b];
+                    const float* pr = CRF ? pr_time + (size_t)bv.st[b] * C : pr_shared;
+                    const float p_blank = pr[0];
                     bool has_self = false;
                     float s_lp = 0.0f, s_gp = 0.0f;
                     if (p_blank > thr) {  // src/search.rs:191-198
@@ -189,7 +215,8 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
                         for (int k = 0; k < nbeam; ++k)
                             if (bv.nd[k] == mypar) r = k;
                         if (r >= 0) {
-                            const float pt = pr[tip + 1];
+                            const float* prp = CRF ? pr_time + (size_t)bv.st[r] * C : pr_shared;  // the parent's row
+                            const float pt = prp[tip + 1];
                             if (!(pt < thr)) {
                                 const float plp = bv.lp[r], pgp = bv.gp[r];
                                 float c;
@@ -213,6 +240,7 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
                     const int node = bv.nd[b];
                     const float lp = bv.lp[b], gp = bv.gp[b];
                     const int tip = bv.tip[b];
+                    const float* pr = CRF ? pr_time + (size_t)bv.st[b] * C : pr_shared;
                     int n_new = 0;
                     for (int l = 0; l < NL; ++l) {
                         const int s = b * C + 1 + l;
@@ -331,9 +359,16 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
                     nb.nd[r] = cnode[i];
                     nb.lp[r] = clp[i] / top;
                     nb.gp[r] = cgp[i] / top;
-                    if (sl == 0) { nb.par[r] = bv.par[b]; nb.dep[r] = bv.dep[b]; nb.tip[r] = bv.tip[b]; }
-                    else { nb.par[r] = bv.nd[b]; nb.dep[r] = bv.dep[b] + 1; nb.tip[r] = sl - 1; }
+                    if (sl == 0) { nb.par[r] = bv.par[b]; nb.dep[r] = bv.dep[b]; nb.tip[r] = bv.tip[b]; nb.st[r] = bv.st[b]; }
+                    else {
+                        nb.par[r] = bv.nd[b]; nb.dep[r] = bv.dep[b] + 1; nb.tip[r] = sl - 1;
+                        nb.st[r] = CRF ? int(((long long)bv.st[b] * NL) % S) + (sl - 1) : 0;  // src/search.rs:97
+                    }
                 }
+                bool bad_state = false;
+                if (CRF)
+                    for (int r = lane; r < n_keep; r += 32) bad_state |= (nb.st[r] >= S);
+                if (CRF && __any_sync(FULL, bad_state)) status = FCTC_REFERENCE_PANIC;  // slice out of bounds in the reference
                 __syncwarp();
                 cur ^= 1;
                 bv = nb;
@@ -380,7 +415,7 @@ static bool plan_beam(int B, int C, BeamLayout* L) {
     const int NL = C - 1;
     auto up = [](long long v, int a) { return (v + a - 1) / a * a; };
     long long o = 0;
-    L->beam_stride = int(up(6LL * 4 * B, 16));
+    L->beam_stride = int(up(7LL * 4 * B, 16));
     o = 2LL * L->beam_stride;
     L->off_newcnt = int(o); o = up(o + 4LL * B, 16);
     L->off_fold = int(o);   o = up(o + (long long)B * (NL > 0 ? NL : 1), 16);
@@ -434,12 +469,15 @@ cudaError_t launch_beam(const BeamParams& p, int sm_count, cudaStream_t stream) 
     BeamLayout L;
     if (!plan_beam(p.beam_size, p.C, &L)) return cudaErrorInvalidConfiguration;
     const int smem = L.warp_bytes * BM_WARPS;
-    cudaError_t e = cudaFuncSetAttribute(beam_search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    const bool crf = p.S > 0;
+    cudaError_t e = crf ? cudaFuncSetAttribute(beam_search_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
+                        : cudaFuncSetAttribute(beam_search_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
     e = cudaMemsetAsync(p.ticket, 0, sizeof(unsigned long long), stream);
     if (e != cudaSuccess) return e;
     const int grid = p.n_slots / BM_WARPS;
-    beam_search_kernel<<<grid, BM_THREADS, smem, stream>>>(p, L);
+    if (crf) beam_search_kernel<true><<<grid, BM_THREADS, smem, stream>>>(p, L);
+    else beam_search_kernel<false><<<grid, BM_THREADS, smem, stream>>>(p, L);
     return cudaGetLastError();
 }
 

@@ -60,11 +60,16 @@ struct BeamParams {
     int64_t nodes_per_slot;  // node capacity of one slot
     int n_slots;             // slots available in scratch
     unsigned long long* ticket;  // read counter for dynamic scheduling (inside scratch)
+    // crf variant (search::crf_beam_search): S > 0 selects it; post is [N, T, S, C]
+    int S;
+    const float* init;  // [N, n_init] initial state scores
+    int n_init;
 };
 
 int64_t beam_scratch_bytes(int sm_count, int64_t N, int64_t T, int C, int beam_size, int nodes_per_row,
                            int64_t* nodes_per_slot, int* n_slots);
 cudaError_t launch_beam(const BeamParams& p, int sm_count, cudaStream_t stream);
+bool beam_shape_supported(int beam_size, int C);
 
 struct DuplexParams {
     const float* post1;    // [N, T1, C]

@@ -13,7 +13,8 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(os.path.dirname(_HERE), "libfctc_b200.so")
 
-OK, RAN_OUT_OF_BEAM, INCOMPARABLE_VALUES, INVALID_ENVELOPE, NODE_POOL_OVERFLOW, OUTPUT_OVERFLOW, INVALID_QUALITY_CHAR = range(7)
+OK, RAN_OUT_OF_BEAM, INCOMPARABLE_VALUES, INVALID_ENVELOPE, NODE_POOL_OVERFLOW, OUTPUT_OVERFLOW, INVALID_QUALITY_CHAR, \
+    REFERENCE_PANIC = range(8)
 E_CUDA, E_ARGUMENT, E_NOMEM, E_UNSUPPORTED, E_CAPACITY = -1, -2, -3, -4, -5
 
 _lib = None
@@ -50,6 +51,13 @@ _SIGNATURES = {
                                                 _vp, _i64, _vp, _vp, _vp, _vp]),
     "fctc_beam_search_duplex": (C.c_int, [_vp, _vp, _i64, _i64, _i64, _vp, _i64, _i64, _i64, _i32, _vp, _i64, _i64,
                                           _i32, _f32, _i32, _i32, _vp, _i64, _vp]),
+    "fctc_crf_greedy_batch_device": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i32, _i32, _i32, _i32, _f32, _f32, _vp, _vp,
+                                               _i32, _vp, _i64, _vp, _vp, _vp, _vp]),
+    "fctc_crf_beam_search_batch_device": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i32, _i32, _i32, _i32, _f32, _vp, _vp,
+                                                    _i64, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _vp]),
+    "fctc_crf_greedy_search": (C.c_int, [_vp, _vp, _i64, _i32, _i32, _vp, _i32, _i32, _f32, _f32, _vp, _vp, _vp, _i64,
+                                         _vp]),
+    "fctc_crf_beam_search": (C.c_int, [_vp, _vp, _i64, _i32, _i32, _vp, _i32, _i32, _f32, _vp, _vp, _i64, _vp]),
     "fctc_synth_posteriors_device": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _i32, _u64, _i64, _vp]),
     "fctc_host_phred": (C.c_uint32, [_f32, _f32, _f32]),
     "fctc_host_log10f": (None, [_vp, _vp, _i64]),
@@ -278,6 +286,40 @@ class Decoder:
                                                          quals.ctypes.data, path.ctypes.data, cap, C.byref(n)))
         k = n.value
         return status, labels[:k].copy(), (quals[:k].copy() if qstring else None), path[:k].copy()
+
+    def crf_greedy_search(self, post, init_state, qstring=False, qscale=1.0, qbias=0.0):
+        post = np.ascontiguousarray(post)
+        init_state = np.ascontiguousarray(init_state)
+        if post.dtype != np.float32 or post.ndim != 3 or init_state.dtype != np.float32 or init_state.ndim != 1:
+            raise TypeError("expected float32 arrays [T, S, C] and [n_init]")
+        T, S, Cn = post.shape
+        cap = max(T, 1)
+        labels = np.empty(cap, np.uint8)
+        quals = np.empty(cap, np.uint32)
+        path = np.empty(cap, np.int64)
+        n = _i64(0)
+        status = self._check(self._L.fctc_crf_greedy_search(self._h, post.ctypes.data, T, S, Cn, init_state.ctypes.data,
+                                                            init_state.size, int(qstring), qscale, qbias,
+                                                            labels.ctypes.data, quals.ctypes.data, path.ctypes.data, cap,
+                                                            C.byref(n)))
+        k = n.value
+        return status, labels[:k].copy(), (quals[:k].copy() if qstring else None), path[:k].copy()
+
+    def crf_beam_search(self, post, init_state, beam_size=5, beam_cut_threshold=0.0):
+        post = np.ascontiguousarray(post)
+        init_state = np.ascontiguousarray(init_state)
+        if post.dtype != np.float32 or post.ndim != 3 or init_state.dtype != np.float32 or init_state.ndim != 1:
+            raise TypeError("expected float32 arrays [T, S, C] and [n_init]")
+        T, S, Cn = post.shape
+        cap = max(T, 1)
+        labels = np.empty(cap, np.uint8)
+        path = np.empty(cap, np.int64)
+        n = _i64(0)
+        status = self._check(self._L.fctc_crf_beam_search(self._h, post.ctypes.data, T, S, Cn, init_state.ctypes.data,
+                                                          init_state.size, beam_size, beam_cut_threshold,
+                                                          labels.ctypes.data, path.ctypes.data, cap, C.byref(n)))
+        k = n.value
+        return status, labels[:k].copy(), path[:k].copy()
 
     def beam_search(self, post, beam_size=5, beam_cut_threshold=0.0, collapse_repeats=True):
         post = _as_f32_2d(post)

@@ -44,6 +44,10 @@ extern "C" {
 #define FCTC_INVALID_QUALITY_CHAR 6 /* phred code is not a Unicode scalar: the reference's
                                        char::from_u32(..).unwrap() (src/search.rs:35) would abort */
 
+#define FCTC_REFERENCE_PANIC 7      /* a condition on which the reference aborts the process: NaN met by a crf
+                                       search's argmax().unwrap() (src/search.rs:404-412), or a crf state that
+                                       leaves [0, n_state) */
+
 /* Call-level failures. */
 #define FCTC_E_CUDA (-1)
 #define FCTC_E_ARGUMENT (-2)
@@ -185,6 +189,34 @@ int fctc_beam_search_duplex(fctc_handle* h, const float* post1_host, int64_t n_r
                             int64_t env_stride_row, int64_t env_stride_col, int32_t beam_size,
                             float beam_cut_threshold, int32_t collapse_repeats, int32_t exp_mode, uint8_t* labels,
                             int64_t capacity, int64_t* out_len);
+
+/* ------------------------------------------------------------------------------------------
+ * State-conditioned ("crf") decoders over [n_rows, n_state, n_labels] posteriors plus an initial
+ * state score vector — replace search::crf_greedy_search (src/search.rs:385-423) and
+ * search::crf_beam_search (src/search.rs:38-157) as called from src/lib.rs:238-245, 275-281.
+ * A label moves the state to (state * (n_labels-1)) % n_state + label.  NaNs (the reference's
+ * argmax().unwrap()) and states outside [0, n_state) abort the reference; here the read gets
+ * FCTC_REFERENCE_PANIC.  Greedy results are in slot form (as Viterbi), beam results in the packed
+ * pool (as beam search; scratch from fctc_beam_scratch_bytes).  Host arrays of the single-read
+ * calls must be C-contiguous.  crf_beam_search_duplex (src/duplex.rs:652-834) is not built yet.
+ * ------------------------------------------------------------------------------------------ */
+int fctc_crf_greedy_batch_device(fctc_handle* h, const float* post_dev, const float* init_dev, int64_t n_reads,
+                                 int64_t n_rows, int32_t n_state, int32_t n_labels, int32_t n_init, int32_t qstring,
+                                 float qscale, float qbias, uint8_t* labels_dev, void* quals_dev, int32_t qual_bytes,
+                                 int32_t* path_dev, int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev,
+                                 int32_t* status_dev, void* stream);
+int fctc_crf_beam_search_batch_device(fctc_handle* h, const float* post_dev, const float* init_dev, int64_t n_reads,
+                                      int64_t n_rows, int32_t n_state, int32_t n_labels, int32_t n_init,
+                                      int32_t beam_size, float beam_cut_threshold, uint8_t* labels_dev,
+                                      int32_t* path_dev, int64_t pool_capacity, int64_t* offsets_dev,
+                                      int32_t* lens_dev, int32_t* status_dev, unsigned long long* pool_used_dev,
+                                      void* scratch_dev, int64_t scratch_bytes, int32_t nodes_per_row, void* stream);
+int fctc_crf_greedy_search(fctc_handle* h, const float* post_host, int64_t n_rows, int32_t n_state, int32_t n_labels,
+                           const float* init_host, int32_t n_init, int32_t qstring, float qscale, float qbias,
+                           uint8_t* labels, uint32_t* quals, int64_t* path, int64_t capacity, int64_t* out_len);
+int fctc_crf_beam_search(fctc_handle* h, const float* post_host, int64_t n_rows, int32_t n_state, int32_t n_labels,
+                         const float* init_host, int32_t n_init, int32_t beam_size, float beam_cut_threshold,
+                         uint8_t* labels, int64_t* path, int64_t capacity, int64_t* out_len);
 
 /* ------------------------------------------------------------------------------------------
  * Synthetic posterior generator used by bench.py and the tests (no reference counterpart; it

@@ -252,7 +252,7 @@ int beam1d(const Posterior2& m, size_t beam_size, float thr, bool collapse, Deco
 int first_argmax(const float* v, int64_t n, int64_t stride, int64_t* arg, float* val) {
     if (n <= 0) return ST_PANIC;
     int64_t a = 0; float best = v[0];
-    if (!(best == best) && n > 1) return ST_PANIC;
+    if (!(best == best)) return ST_PANIC;  // indexed_iter compares element 0 with itself: NaN -> Err
     for (int64_t i = 1; i < n; ++i) {
         float x = v[i * stride];
         if (!(x == x) || !(best == best)) return ST_PANIC;

@@ -1,0 +1,114 @@
+"""GPU parity tests of the state-conditioned (crf) decoders through the C ABI and the drop-in module
+vs the CPU oracle: the reference's only crf vector (src/search.rs:431-510) plus random k-mer
+transition models, bit-exact (labels, path, quality characters)."""
+import numpy as np
+import pytest
+
+from helpers import load_kats
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def dec():
+    import fctc_b200
+    d = fctc_b200.Decoder(0)
+    yield d
+    d.close()
+
+
+def crf_posteriors(rng, T, S, C, peak=0.0):
+    x = rng.random((T, S, C), dtype=np.float32)
+    if peak:
+        x[..., 0] += peak
+    x /= x.sum(axis=2, keepdims=True, dtype=np.float32)
+    return x.astype(np.float32)
+
+
+@pytest.mark.parametrize("kat", [pytest.param(k, id=k["name"]) for k in load_kats() if k["fn"].startswith("crf_")])
+def test_reference_kats(dec, oracle, kat):
+    import fast_ctc_decode as fcd
+    post = np.asarray(kat["post"], np.float32)
+    init = np.asarray(kat["init_state"], np.float32)
+    if kat["fn"] == "crf_greedy_search":
+        st, labels, quals, path = dec.crf_greedy_search(post, init, kat["qstring"], kat["qscale"], kat["qbias"])
+        assert st == 0
+        assert oracle.to_text(kat["alphabet"], labels, quals) == kat["expect_seq"]
+        assert path.tolist() == kat["expect_path"]
+        seq, p = fcd.crf_greedy_search(post, init, kat["alphabet"], kat["qstring"], kat["qscale"], kat["qbias"])
+    else:
+        st, labels, path = dec.crf_beam_search(post, init, kat["beam_size"], kat["beam_cut_threshold"])
+        assert st == 0
+        assert oracle.to_text(kat["alphabet"], labels) == kat["expect_seq"]
+        assert path.tolist() == kat["expect_path"]
+        seq, p = fcd.crf_beam_search(post, init, kat["alphabet"], kat["beam_size"], kat["beam_cut_threshold"])
+    assert seq == kat["expect_seq"] and p == kat["expect_path"]
+
+
+@pytest.mark.parametrize("shape", [(300, 16, 5), (500, 64, 5), (200, 4, 3), (150, 25, 6), (64, 1024, 5)],
+                         ids=lambda s: "x".join(map(str, s)))
+def test_random_models_match_oracle(dec, oracle, shape):
+    T, S, C = shape
+    rng = np.random.default_rng(31 * T + S)
+    for peak in (0.0, 1.5):
+        post = crf_posteriors(rng, T, S, C, peak)
+        init = rng.random(S, dtype=np.float32)
+        st, labels, quals, path = dec.crf_greedy_search(post, init, True, 0.7, 2.0)
+        ost, ol, oq, op = oracle.crf_greedy(post, init, True, 0.7, 2.0)
+        assert st == ost == 0
+        assert np.array_equal(labels, ol) and np.array_equal(quals, oq) and np.array_equal(path, op)
+        for beam, thr in ((5, 0.0), (5, 0.05), (32, 0.0), (1, 0.0)):
+            st, labels, path = dec.crf_beam_search(post, init, beam, thr)
+            ost, ol, op = oracle.crf_beam_search(post, init, beam, thr)
+            assert st == ost, (beam, thr)
+            if st == 0:
+                assert np.array_equal(labels, ol) and np.array_equal(path, op), (beam, thr)
+
+
+def test_reference_abort_conditions_are_reported(dec, oracle):
+    import fctc_b200
+    rng = np.random.default_rng(9)
+    post = crf_posteriors(rng, 100, 16, 5)
+    init = rng.random(16, dtype=np.float32)
+    bad = post.copy()
+    bad[40] = np.nan
+    st, labels, quals, path = dec.crf_greedy_search(bad, init)
+    assert st == fctc_b200.REFERENCE_PANIC and oracle.crf_greedy(bad, init)[0] == oracle.PANIC
+    # 6 states, 4 bases: (state*4) % 6 + label can leave [0, 6)
+    post6 = crf_posteriors(rng, 100, 6, 5)
+    init6 = np.array([0, 0, 0, 0, 0, 1], np.float32)
+    st, *_ = dec.crf_greedy_search(post6, init6)
+    assert (st == fctc_b200.REFERENCE_PANIC) == (oracle.crf_greedy(post6, init6)[0] == oracle.PANIC)
+    st, labels, path = dec.crf_beam_search(bad, init, 5, 0.0)
+    assert st in (fctc_b200.INCOMPARABLE_VALUES, fctc_b200.REFERENCE_PANIC)
+    assert oracle.crf_beam_search(bad, init, 5, 0.0)[0] in (oracle.INCOMPARABLE, oracle.PANIC)
+
+
+def test_device_batch_greedy(dec, oracle):
+    import torch
+    rng = np.random.default_rng(12)
+    N, T, S, C = 200, 120, 16, 5
+    post = np.stack([crf_posteriors(rng, T, S, C, 1.0) for _ in range(N)])
+    init = rng.random((N, S), dtype=np.float32)
+    dev = torch.device("cuda:0")
+    dpost, dinit = torch.from_numpy(post).to(dev), torch.from_numpy(init).to(dev)
+    stride = (T + 31) // 32 * 32
+    labels = torch.empty(N * stride, dtype=torch.uint8, device=dev)
+    quals = torch.empty(N * stride, dtype=torch.uint8, device=dev)
+    path = torch.empty(N * stride, dtype=torch.int32, device=dev)
+    offsets = torch.empty(N, dtype=torch.int64, device=dev)
+    lens = torch.empty(N, dtype=torch.int32, device=dev)
+    status = torch.empty(N, dtype=torch.int32, device=dev)
+    rc = dec._L.fctc_crf_greedy_batch_device(dec._h, dpost.data_ptr(), dinit.data_ptr(), N, T, S, C, S, 1, 1.0, 0.0,
+                                             labels.data_ptr(), quals.data_ptr(), 1, path.data_ptr(), N * stride,
+                                             offsets.data_ptr(), lens.data_ptr(), status.data_ptr(),
+                                             torch.cuda.current_stream().cuda_stream or None)
+    assert rc == 0
+    torch.cuda.synchronize()
+    lab, q, pth, ln = labels.cpu().numpy(), quals.cpu().numpy(), path.cpu().numpy(), lens.cpu().numpy()
+    assert (status.cpu().numpy() == 0).all()
+    for n in range(N):
+        ost, ol, oq, op = oracle.crf_greedy(post[n], init[n], True)
+        o = n * stride
+        assert ln[n] == len(ol) and np.array_equal(lab[o:o + ln[n]], ol) and np.array_equal(q[o:o + ln[n]], oq)
+        assert np.array_equal(pth[o:o + ln[n]], op)
