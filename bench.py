@@ -46,6 +46,9 @@ WORKLOADS = {
                   e2e_reads=16384, label="beam_search 262,144 reads x T=4000 x C=5, beam_size=5, beam_cut_threshold=0.1"),
     "beam32": dict(reads=65_536, T=10_000, C=5, kind="beam", beam=32, thr=0.0, collapse=1, cpu_sample=128,
                    e2e_reads=4096, label="beam_search 65,536 reads x T=10,000 x C=5, beam_size=32, beam_cut_threshold=0.0"),
+    "duplex": dict(reads=16_384, T=4000, T2=4000, C=5, kind="duplex", beam=5, thr=0.0, collapse=1, band=32, exp_mode=0,
+                   cpu_sample=64, e2e_reads=1024,
+                   label="duplex 2D envelope beam search: 16,384 pairs x T1=T2=4000 x C=5, beam_size=5, band +-32, exact exp"),
 }
 
 
@@ -119,15 +122,41 @@ def cpu_rate(w, post_np, n_threads):
     if w["kind"] == "viterbi":
         oracle.viterbi_batch(post_np, bool(w["qstring"]), w["qscale"], w["qbias"], bool(w["collapse"]),
                              n_threads=n_threads, keep=False)
+    elif w["kind"] == "duplex":
+        p1, p2, env = post_np
+        t0 = time.perf_counter()
+        oracle.beam_search_duplex_batch(p1, p2, env.astype(np.uint64), w["beam"], w["thr"], bool(w["collapse"]),
+                                        w["exp_mode"], n_threads=n_threads)
+        dt = time.perf_counter() - t0
+        return p1.shape[0] * p1.shape[1] / dt, dt
     else:
         oracle.beam_search_batch(post_np, w["beam"], w["thr"], bool(w["collapse"]), n_threads=n_threads, keep=False)
     dt = time.perf_counter() - t0
     return post_np.shape[0] * post_np.shape[1] / dt, dt
 
 
+def band_envelope_np(n, T1, T2, half):
+    c = (np.arange(T1) * T2) // max(T1, 1)
+    env = np.stack([np.maximum(0, c - half), np.minimum(T2, c + half + 1)], axis=1).astype(np.int64)
+    return np.ascontiguousarray(np.broadcast_to(env, (n, T1, 2)))
+
+
 def synth_host_sample(w, n_reads, first_read=0):
     """The first n_reads reads of rank 0's shard, as host float32 (generated by the device generator
     when a GPU is present so that both arms see identical bytes; numpy restatement otherwise)."""
+    if w["kind"] == "duplex":
+        import torch
+        import fctc_b200
+        dec = fctc_b200.Decoder(0)
+        st = torch.cuda.current_stream().cuda_stream
+        a = torch.empty((n_reads, w["T"], w["C"]), dtype=torch.float32, device="cuda:0")
+        b = torch.empty((n_reads, w["T2"], w["C"]), dtype=torch.float32, device="cuda:0")
+        dec.synth_posteriors_device(a.data_ptr(), n_reads, w["T"], w["C"], 1, SEED, first_read, st)
+        dec.synth_posteriors_device(b.data_ptr(), n_reads, w["T2"], w["C"], 2, SEED, first_read, st)
+        torch.cuda.synchronize()
+        out = (a.cpu().numpy(), b.cpu().numpy(), band_envelope_np(n_reads, w["T"], w["T2"], w["band"]))
+        dec.close()
+        return out, "device generator (same bytes as the GPU arm)"
     try:
         import torch
         if torch.cuda.is_available():
@@ -161,7 +190,7 @@ def run_reference(args, w):
     post, how = synth_host_sample(w, n)
     threads = host_threads()
     for _ in range(max(args.warmup, 0)):
-        cpu_rate(w, post[: max(1, n // 8)], threads)
+        cpu_rate(w, tuple(x[: max(1, n // 8)] for x in post) if isinstance(post, tuple) else post[: max(1, n // 8)], threads)
     t_total = 0.0
     for _ in range(args.steps):
         _, dt = cpu_rate(w, post, threads)
@@ -204,7 +233,8 @@ def run_ours(args, w):
     # ---- resident synthetic input: rank r decodes reads [r*N, (r+1)*N) of the global job ----------
     post = torch.empty((N, T, Cn), dtype=torch.float32, device=dev)
     from fctc_b200.sharding import weak_shard_first_read
-    dec.synth_posteriors_device(post.data_ptr(), N, T, Cn, 0, SEED, weak_shard_first_read(N, rank), stream)
+    dec.synth_posteriors_device(post.data_ptr(), N, T, Cn, 1 if w["kind"] == "duplex" else 0, SEED,
+                                weak_shard_first_read(N, rank), stream)
     cap = N * stride
     labels = torch.empty(cap, dtype=torch.uint8, device=dev)
     path = torch.empty(cap, dtype=torch.int32, device=dev)
@@ -220,6 +250,23 @@ def run_ours(args, w):
             dec.viterbi_batch_device(post.data_ptr(), N, T, Cn, w["qstring"], w["qscale"], w["qbias"], w["collapse"],
                                      labels.data_ptr(), quals.data_ptr(), 1, path.data_ptr(), cap, offsets.data_ptr(),
                                      lens.data_ptr(), status.data_ptr(), stream)
+        launches_per_step = 1
+    elif w["kind"] == "duplex":
+        T2 = w["T2"]
+        post2 = torch.empty((N, T2, Cn), dtype=torch.float32, device=dev)
+        dec.synth_posteriors_device(post2.data_ptr(), N, T2, Cn, 2, SEED, weak_shard_first_read(N, rank), stream)
+        env = torch.from_numpy(band_envelope_np(N, T, T2, w["band"])).to(dev)
+        max_window = 2 * w["band"] + 1
+        free_b, _ = torch.cuda.mem_get_info(dev)
+        nbytes = min(dec.duplex_scratch_bytes(N, T, T2, Cn, w["beam"], max_window, 0), int(free_b * 0.8) // 256 * 256)
+        scratch = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+
+        def step():
+            used.zero_()
+            dec.beam_search_duplex_batch_device(post.data_ptr(), post2.data_ptr(), N, T, T2, Cn, env.data_ptr(), max_window,
+                                                w["beam"], w["thr"], w["collapse"], w["exp_mode"], labels.data_ptr(), cap,
+                                                offsets.data_ptr(), lens.data_ptr(), status.data_ptr(), used.data_ptr(),
+                                                scratch.data_ptr(), nbytes, 0, stream)
         launches_per_step = 1
     else:
         nbytes = dec.beam_scratch_bytes(N, T, Cn, w["beam"], 0)
@@ -268,6 +315,8 @@ def run_ours(args, w):
     ok_reads = int((status == 0).sum().item())
     out_per_label = (1 + 4 + (1 if w.get("qstring") else 0))
     alg_bytes = N * T * Cn * 4 + emitted * out_per_label + N * 16
+    if w["kind"] == "duplex":  # two posterior arrays + the envelope in, labels out
+        alg_bytes = N * (T + w["T2"]) * Cn * 4 + N * T * 16 + emitted + N * 16
     mean_launch_ms = float(np.mean(step_ms))
     peaks, peak_src = measured_peaks()
     achieved = alg_bytes / (mean_launch_ms * 1e-3) / 1e9
@@ -293,12 +342,20 @@ def run_ours(args, w):
                        "emitted_labels_per_row": emitted / (N * T), "reads_ok": ok_reads},
             "clocks": clocks, "gpu_launches": launches_per_step * args.steps, "roofline": roofline}
 
-    if rank == 0:
-        # ---- end to end through the C ABI with pinned HOST buffers (copies inside the timed region) --
-        ne = min(w["e2e_reads"], N)
-        hpost = torch.empty((ne, T, Cn), dtype=torch.float32).pin_memory()
-        hpost.copy_(post[:ne])
-        hcap = ne * stride
+    # ---- end to end through the C ABI with pinned HOST buffers (copies inside the timed region);
+    #      every rank streams its own shard, time = max over ranks ------------------------------------
+    ne = min(w["e2e_reads"], N)
+    hpost = torch.empty((ne, T, Cn), dtype=torch.float32).pin_memory()
+    hpost.copy_(post[:ne])
+    hnp = hpost.numpy()
+    hcap = ne * stride
+    if w["kind"] == "duplex":
+        hpost2 = torch.empty((ne, w["T2"], Cn), dtype=torch.float32).pin_memory()
+        hpost2.copy_(post2[:ne])
+        henv = band_envelope_np(ne, T, w["T2"], w["band"])
+        hnp2 = hpost2.numpy()
+        outd = None
+    else:
         hl = torch.empty(hcap, dtype=torch.uint8).pin_memory()
         hq = torch.empty(hcap, dtype=torch.uint8).pin_memory()
         hp = torch.empty(hcap, dtype=torch.int32).pin_memory()
@@ -307,38 +364,45 @@ def run_ours(args, w):
         hs = torch.empty(ne, dtype=torch.int32).pin_memory()
         outd = dict(labels=hl.numpy(), quals=hq.numpy(), path=hp.numpy(), offsets=ho.numpy(), lens=hn.numpy(),
                     status=hs.numpy())
-        hnp = hpost.numpy()
 
-        def e2e_step():
-            if w["kind"] == "viterbi":
-                return dec.viterbi_batch(hnp, bool(w["qstring"]), w["qscale"], w["qbias"], bool(w["collapse"]),
-                                         qual_bytes=1, out=outd)
-            return dec.beam_search_batch(hnp, w["beam"], w["thr"], bool(w["collapse"]), out=outd)
-        for _ in range(3):
-            res = e2e_step()
-        torch.cuda.synchronize()
-        reps = 5
-        t0 = time.perf_counter()
-        for _ in range(reps):
-            res = e2e_step()
-        dt = (time.perf_counter() - t0) / reps
-        h2d = ne * T * Cn * 4
+    def e2e_step():
         if w["kind"] == "viterbi":
-            d2h = hcap * (1 + 4 + (1 if w["qstring"] else 0)) + ne * 16
-        else:
-            d2h = int(res["used"]) * 5 + ne * 16 + 8
-        line["e2e"] = {"value": ne * T / dt, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                       "reads_per_step": ne, "ms_per_step": dt * 1e3,
-                       "note": "fctc_*_batch (host pointers, pinned memory), rank 0, one GPU; x n_gpus when every rank "
-                               "streams its own shard"}
-        if world > 1:
-            line["e2e"]["value"] *= 1  # rank 0's rate; ranks are independent
+            return dec.viterbi_batch(hnp, bool(w["qstring"]), w["qscale"], w["qbias"], bool(w["collapse"]),
+                                     qual_bytes=1, out=outd)
+        if w["kind"] == "duplex":
+            return dec.beam_search_duplex_batch(hnp, hnp2, henv, w["beam"], w["thr"], bool(w["collapse"]), w["exp_mode"])
+        return dec.beam_search_batch(hnp, w["beam"], w["thr"], bool(w["collapse"]), out=outd)
+    for _ in range(3):
+        res = e2e_step()
+    barrier()
+    reps = 5
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        res = e2e_step()
+    dt = (time.perf_counter() - t0) / reps
+    if world > 1:
+        tt = torch.tensor([dt], dtype=torch.float64, device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dt = float(tt.item())
+    h2d = ne * T * Cn * 4
+    if w["kind"] == "viterbi":
+        d2h = hcap * (1 + 4 + (1 if w["qstring"] else 0)) + ne * 16
+    elif w["kind"] == "duplex":
+        h2d = ne * (T + w["T2"]) * Cn * 4 + ne * T * 16
+        d2h = int(res["used"]) + ne * 16 + 8
+    else:
+        d2h = int(res["used"]) * 5 + ne * 16 + 8
+    line["e2e"] = {"value": world * ne * T / dt, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                   "reads_per_step_per_gpu": ne, "ms_per_step": dt * 1e3,
+                   "note": "fctc_*_batch (host pointers, pinned memory); every rank streams its own shard, max over ranks"}
+    if rank == 0:
         # ---- CPU baseline on a bounded sample of the same bytes ------------------------------------------
         import oracle
         oracle.build()
         nc = min(w["cpu_sample"], ne)
         threads = host_threads()
-        rate, dtc = cpu_rate(w, hnp[:nc], threads)
+        sample = (hnp[:nc], hnp2[:nc], henv[:nc]) if w["kind"] == "duplex" else hnp[:nc]
+        rate, dtc = cpu_rate(w, sample, threads)
         line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": threads, "kind": "port",
                                 "sample": f"first {nc} reads of rank 0's shard ({nc * T} rows, {dtc:.1f} s), one read per "
                                           "worker thread; C++ restatement of the reference (Rust toolchain absent)"}

@@ -22,7 +22,9 @@ __global__ void __launch_bounds__(256) synth_kernel(float* post, long long N, lo
     for (long long g = blockIdx.x * (long long)blockDim.x + threadIdx.x; g < rows;
          g += (long long)gridDim.x * blockDim.x) {
         const long long n = g / T, t = g - n * T;
-        const uint64_t key = mix64(seed ^ mix64(uint64_t(first_read + n) * 0x100000001B3ull + 0x51ull)) + uint64_t(t) * 0xD1342543DE82EF95ull;
+        // kind 2 = kind 1's hidden label track with an independent noise stream (second read of a duplex pair)
+        const uint64_t noise_seed = (kind == 2) ? (seed ^ 0x5BD1E9955BD1E995ull) : seed;
+        const uint64_t key = mix64(noise_seed ^ mix64(uint64_t(first_read + n) * 0x100000001B3ull + 0x51ull)) + uint64_t(t) * 0xD1342543DE82EF95ull;
         float* row = post + g * C;
         if (kind == 0) {
             // softmax(3 * (2u - 1)) in f32

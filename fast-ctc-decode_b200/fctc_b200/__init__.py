@@ -155,6 +155,21 @@ class Decoder:
                                                           pool_used_ptr, scratch_ptr, scratch_bytes, nodes_per_row,
                                                           stream or None))
 
+    def duplex_scratch_bytes(self, n_pairs, n_rows_1, n_rows_2, n_labels, beam_size, max_window=0, nodes_per_row=0):
+        return int(self._L.fctc_duplex_scratch_bytes(self._h, n_pairs, n_rows_1, n_rows_2, n_labels, beam_size,
+                                                     max_window, nodes_per_row))
+
+    def beam_search_duplex_batch_device(self, post1_ptr, post2_ptr, n_pairs, n_rows_1, n_rows_2, n_labels, envelope_ptr,
+                                        max_window, beam_size, beam_cut_threshold, collapse_repeats, exp_mode,
+                                        labels_ptr, pool_capacity, offsets_ptr, lens_ptr, status_ptr, pool_used_ptr,
+                                        scratch_ptr, scratch_bytes, nodes_per_row=0, stream=0):
+        self._check(self._L.fctc_beam_search_duplex_batch_device(self._h, post1_ptr, post2_ptr, n_pairs, n_rows_1,
+                                                                 n_rows_2, n_labels, envelope_ptr or None, max_window,
+                                                                 beam_size, beam_cut_threshold, int(collapse_repeats),
+                                                                 exp_mode, labels_ptr, pool_capacity, offsets_ptr,
+                                                                 lens_ptr, status_ptr, pool_used_ptr, scratch_ptr,
+                                                                 scratch_bytes, nodes_per_row, stream or None))
+
     def beam_search_batch_device_static(self, post_ptr, n_reads, n_rows, n_labels, beam_size, beam_cut_threshold,
                                         collapse_repeats, labels_ptr, path_ptr, pool_capacity, offsets_ptr, lens_ptr,
                                         status_ptr, pool_used_ptr, nodes_per_row=0, stream=0):

@@ -221,7 +221,8 @@ int fctc_crf_beam_search(fctc_handle* h, const float* post_host, int64_t n_rows,
 /* ------------------------------------------------------------------------------------------
  * Synthetic posterior generator used by bench.py and the tests (no reference counterpart; it
  * implements SURVEY.md §8d's input definition): fills post_dev[n_reads, n_rows, n_labels] with
- * kind 0: softmax(3*(2u-1)) rows, kind 1: peaked rows (dominant label, blank w.p. 0.65),
+ * kind 0: softmax(3*(2u-1)) rows, kind 1: peaked rows (dominant label, blank w.p. 0.65), kind 2: kind
+ * 1's dominant-label track with an independent noise stream (the second read of a duplex pair),
  * u from a counter-based generator keyed (seed, first_read + read, row).  Asynchronous on stream.
  * ------------------------------------------------------------------------------------------ */
 int fctc_synth_posteriors_device(fctc_handle* h, float* post_dev, int64_t n_reads, int64_t n_rows, int32_t n_labels,
