@@ -515,7 +515,10 @@ cudaStream_t handle_stream(fctc_handle* h) { return h->stream; }
 int64_t fctc_beam_scratch_bytes(const fctc_handle* h, int64_t n_reads, int64_t n_rows, int32_t n_labels,
                                 int32_t beam_size, int32_t nodes_per_row) {
     if (!h || n_labels <= 0 || beam_size <= 0) return 0;
-    return fctc::beam_scratch_bytes(h->sm_count, n_reads, n_rows, n_labels, beam_size, nodes_per_row, nullptr, nullptr);
+    // recommended size: one trie pool per resident warp, capped at 96 GiB (a smaller buffer is accepted
+    // by the device entry points: they run as many pools as fit, at least 4)
+    return fctc::beam_scratch_bytes(h->sm_count, n_reads, n_rows, n_labels, beam_size, nodes_per_row, int64_t(96) << 30,
+                                    nullptr, nullptr);
 }
 
 int fctc_beam_search_batch_device(fctc_handle* h, const float* post_dev, int64_t n_reads, int64_t n_rows,
@@ -532,7 +535,7 @@ int fctc_beam_search_batch_device(fctc_handle* h, const float* post_dev, int64_t
     FCTC_CUDA(h, cudaSetDevice(h->device));
     fctc::BeamParams p{};
     int64_t need = fctc::beam_scratch_bytes(h->sm_count, n_reads, n_rows, n_labels, beam_size, nodes_per_row,
-                                            &p.nodes_per_slot, &p.n_slots);
+                                            scratch_bytes, &p.nodes_per_slot, &p.n_slots);
     if (scratch_bytes < need)
         return fail(h, FCTC_E_CAPACITY, "beam scratch too small: %lld bytes given, %lld needed", (long long)scratch_bytes,
                     (long long)need);
@@ -553,13 +556,17 @@ int beam_host_pass(fctc_handle* h, const float* post_host, int64_t n_reads, int6
     const int64_t chunk = std::min<int64_t>(default_chunk_reads(n_rows * int64_t(n_labels) * 4), n_reads);
     int64_t nodes_per_slot = 0;
     int n_slots = 0;
-    const int64_t need = fctc::beam_scratch_bytes(h->sm_count, chunk, n_rows, n_labels, beam_size, nodes_per_row,
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) free_b = size_t(16) << 30;
+    const int64_t budget = std::max<int64_t>(int64_t(free_b / 2) + int64_t(h->slot[0].scratch.bytes + h->slot[1].scratch.bytes) / 2,
+                                             int64_t(1) << 28) / 2;  // two slots share the budget
+    const int64_t need = fctc::beam_scratch_bytes(h->sm_count, chunk, n_rows, n_labels, beam_size, nodes_per_row, budget,
                                                   &nodes_per_slot, &n_slots);
     for (int i = 0; i < 2; ++i)
         if (int rc = ensure(h, h->slot[i].scratch, size_t(need))) return rc;
     auto launch = [&](Slot& s, int64_t cnt) -> int {
         fctc::BeamParams p{};
-        fctc::beam_scratch_bytes(h->sm_count, cnt, n_rows, n_labels, beam_size, nodes_per_row, &p.nodes_per_slot, &p.n_slots);
+        fctc::beam_scratch_bytes(h->sm_count, cnt, n_rows, n_labels, beam_size, nodes_per_row, need, &p.nodes_per_slot, &p.n_slots);
         p.post = static_cast<const float*>(s.post.p); p.N = cnt; p.T = n_rows; p.C = n_labels;
         p.beam_size = beam_size; p.threshold = thr; p.collapse = collapse;
         p.labels = static_cast<uint8_t*>(s.labels.p); p.path = static_cast<int32_t*>(s.path.p);

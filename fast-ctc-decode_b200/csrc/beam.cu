@@ -25,6 +25,7 @@
 #include "kernels.h"
 
 #include <cstdio>
+#include <cstdlib>
 
 #include "../../include/fctc.h"
 
@@ -48,7 +49,7 @@ __host__ __device__ inline size_t beam_slot_bytes(long long cap, int NL) {
 
 struct BeamLayout {  // per-warp shared memory plan, in bytes from the warp's base
     int beam_stride;  // one beam buffer: 6 arrays of B words
-    int off_newcnt, off_fold, off_key, off_node, off_lp, off_gp, off_src, off_sel, off_rows, off_root;
+    int off_newcnt, off_fold, off_key, off_node, off_lp, off_gp, off_src, off_sel, off_perm, off_skey, off_slo, off_rows, off_root;
     int warp_bytes;
     int rows_per_chunk;
 };
@@ -102,6 +103,9 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
     float* clp = reinterpret_cast<float*>(ws + L.off_lp);
     float* cgp = reinterpret_cast<float*>(ws + L.off_gp);
     int* sel = reinterpret_cast<int*>(ws + L.off_sel);
+    unsigned char* cperm = ws + L.off_perm;  // per-lane rank order of a hypothesis' C candidates
+    uint32_t* skey = reinterpret_cast<uint32_t*>(ws + L.off_skey);  // the same candidates' keys, in rank order
+    uint32_t* slo = reinterpret_cast<uint32_t*>(ws + L.off_slo);
     float* rowbuf = reinterpret_cast<float*>(ws + L.off_rows);
     int* root_child = reinterpret_cast<int*>(ws + L.off_root);
 
@@ -325,27 +329,72 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
                 }
 
                 // ---- ranking: select the best min(B, n_cand) candidates in order --------------------
+                // order: score descending, equal scores by ascending node id (the oracle's tie rule)
                 const int n_slots_c = nbeam * C;
                 const int n_keep = n_cand < B ? n_cand : B;
-                uint32_t best_hi = 0, best_lo = 0;
-                int best_i = -1;
-                auto rescan = [&]() {
-                    best_hi = 0; best_lo = 0; best_i = -1;
-                    for (int i = lane; i < n_slots_c; i += 32) {
-                        const uint32_t k = ckey[i];
-                        if (k == 0u) continue;
-                        const uint32_t lo = 0x7FFFFFFFu - uint32_t(cnode[i]);  // lower node id ranks first
-                        if (k > best_hi || (k == best_hi && lo > best_lo)) { best_hi = k; best_lo = lo; best_i = i; }
+                if (nbeam <= 32 && n_slots_c > 64) {
+                    // Lane b sorts its own hypothesis' C candidates once (tiny insertion sort on an index
+                    // permutation) and lays them out in rank order; then every rank costs one REDUX.MAX (two
+                    // on a score tie) and a head advance on the winning lane.
+                    unsigned char* perm = cperm + lane * C;
+                    const int base = lane * C;
+                    auto better = [&](int a, int b2) {  // slot a ranks before slot b2
+                        const uint32_t ka = ckey[base + a], kb = ckey[base + b2];
+                        return ka > kb || (ka == kb && ka != 0u && cnode[base + a] < cnode[base + b2]);
+                    };
+                    if (lane < nbeam) {
+                        for (int j = 0; j < C; ++j) {
+                            int k = j - 1;
+                            while (k >= 0 && better(j, perm[k])) { perm[k + 1] = perm[k]; --k; }
+                            perm[k + 1] = (unsigned char)j;
+                        }
+                        for (int j = 0; j < C; ++j) {
+                            const int i = base + perm[j];
+                            const uint32_t k = ckey[i];
+                            skey[base + j] = k;
+                            slo[base + j] = k ? 0x7FFFFFFFu - uint32_t(cnode[i]) : 0u;
+                        }
                     }
-                };
-                rescan();
-                for (int r = 0; r < n_keep; ++r) {
-                    const uint32_t m1 = __reduce_max_sync(FULL, best_hi);
-                    const uint32_t m2 = __reduce_max_sync(FULL, best_hi == m1 ? best_lo : 0u);
-                    if (best_hi == m1 && best_lo == m2) {
-                        sel[r] = best_i;
-                        ckey[best_i] = 0u;
-                        rescan();
+                    int head = base;
+                    const int tail = base + C;
+                    uint32_t cur_hi = (lane < nbeam) ? skey[head] : 0u;
+                    uint32_t cur_lo = (lane < nbeam) ? slo[head] : 0u;
+                    for (int r = 0; r < n_keep; ++r) {
+                        const uint32_t m1 = __reduce_max_sync(FULL, cur_hi);
+                        unsigned who = __ballot_sync(FULL, cur_hi == m1);
+                        if (who & (who - 1)) {  // several lanes share the top score: lowest node id wins
+                            const uint32_t m2 = __reduce_max_sync(FULL, cur_hi == m1 ? cur_lo : 0u);
+                            who = __ballot_sync(FULL, cur_hi == m1 && cur_lo == m2);
+                        }
+                        const int wl = __ffs(who) - 1;
+                        if (lane == wl) {
+                            sel[r] = base + perm[head - base];
+                            ++head;
+                            cur_hi = (head < tail) ? skey[head] : 0u;
+                            cur_lo = (head < tail) ? slo[head] : 0u;
+                        }
+                    }
+                } else {
+                    uint32_t best_hi = 0, best_lo = 0;
+                    int best_i = -1;
+                    auto rescan = [&]() {
+                        best_hi = 0; best_lo = 0; best_i = -1;
+                        for (int i = lane; i < n_slots_c; i += 32) {
+                            const uint32_t k = ckey[i];
+                            if (k == 0u) continue;
+                            const uint32_t lo = 0x7FFFFFFFu - uint32_t(cnode[i]);  // lower node id ranks first
+                            if (k > best_hi || (k == best_hi && lo > best_lo)) { best_hi = k; best_lo = lo; best_i = i; }
+                        }
+                    };
+                    rescan();
+                    for (int r = 0; r < n_keep; ++r) {
+                        const uint32_t m1 = __reduce_max_sync(FULL, best_hi);
+                        const uint32_t m2 = __reduce_max_sync(FULL, best_hi == m1 ? best_lo : 0u);
+                        if (best_hi == m1 && best_lo == m2) {
+                            sel[r] = best_i;
+                            ckey[best_i] = 0u;
+                            rescan();
+                        }
                     }
                 }
                 __syncwarp();
@@ -426,6 +475,9 @@ static bool plan_beam(int B, int C, BeamLayout* L) {
     L->off_gp = int(o);     o = up(o + 4 * nc, 16);
     L->off_src = int(o);
     L->off_sel = int(o);    o = up(o + 4LL * B, 16);
+    L->off_perm = int(o);   o = up(o + 32LL * C, 16);
+    L->off_skey = int(o);   o = up(o + 4LL * 32 * C, 16);
+    L->off_slo = int(o);    o = up(o + 4LL * 32 * C, 16);
     L->off_rows = int(o);   o = up(o + 2LL * BM_ROWBUF * 4, 16);
     L->off_root = int(o);   o = up(o + 4LL * (NL > 0 ? NL : 1), 16);
     L->warp_bytes = int(up(o, 128));
@@ -448,16 +500,26 @@ static int default_nodes_per_row(int C, int B) {
 }
 
 int64_t beam_scratch_bytes(int sm_count, int64_t N, int64_t T, int C, int beam_size, int nodes_per_row,
-                           int64_t* nodes_per_slot, int* n_slots) {
+                           int64_t budget_bytes, int64_t* nodes_per_slot, int* n_slots) {
     if (nodes_per_row <= 0) nodes_per_row = default_nodes_per_row(C, beam_size);
     const long long bound = (long long)(C - 1) * beam_size;
     if (nodes_per_row > bound) nodes_per_row = int(bound > 0 ? bound : 1);
-    long long slots = (long long)sm_count * 16;
+    // The kernel is latency-bound (sequential per read), so throughput follows the number of resident
+    // warps: 24 per SM is what registers and shared memory allow.  One trie pool per resident warp.
+    int per_sm = 24;
+    if (const char* e = getenv("FCTC_BEAM_WARPS_PER_SM")) per_sm = atoi(e) > 0 ? atoi(e) : per_sm;  // tuning knob
+    long long slots = (long long)sm_count * per_sm;
     if (slots > N) slots = N;
     if (slots < 1) slots = 1;
     slots = (slots + BM_WARPS - 1) / BM_WARPS * BM_WARPS;
     const long long cap = (long long)nodes_per_row * (T > 0 ? T : 1);
     const long long per_slot = (long long)beam_slot_bytes(cap, C - 1);
+    if (budget_bytes > 0) {  // fewer reads in flight rather than more memory
+        long long fit = (budget_bytes - 256) / per_slot;
+        fit = fit / BM_WARPS * BM_WARPS;
+        if (fit < BM_WARPS) fit = BM_WARPS;
+        if (slots > fit) slots = fit;
+    }
     if (nodes_per_slot) *nodes_per_slot = cap;
     if (n_slots) *n_slots = int(slots);
     return 256 + slots * per_slot;
@@ -547,7 +609,7 @@ extern "C" int fctc_beam_search_batch_device_static(fctc_handle* h, const float*
     // Fit the launch into the fixed array: fewer resident warps (pool slots) if need be, never more bytes.
     fctc::BeamParams p{};
     const int sm_count = fctc::handle_sm_count(h);
-    fctc::beam_scratch_bytes(sm_count, n_reads, n_rows, n_labels, beam_size, nodes_per_row, &p.nodes_per_slot, &p.n_slots);
+    fctc::beam_scratch_bytes(sm_count, n_reads, n_rows, n_labels, beam_size, nodes_per_row, 0, &p.nodes_per_slot, &p.n_slots);
     const int64_t per_slot = int64_t(fctc::beam_slot_bytes(p.nodes_per_slot, n_labels - 1));
     int64_t fit = (int64_t(FCTC_BEAM_STATIC_SCRATCH_BYTES) - 256) / per_slot;
     fit = fit / fctc::BM_WARPS * fctc::BM_WARPS;

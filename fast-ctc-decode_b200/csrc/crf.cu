@@ -177,7 +177,7 @@ extern "C" int fctc_crf_beam_search_batch_device(fctc_handle* h, const float* po
     CRF_CUDA(cudaSetDevice(fctc::handle_device(h)));
     fctc::BeamParams p{};
     const int64_t need = fctc::beam_scratch_bytes(fctc::handle_sm_count(h), n_reads, n_rows, n_labels, beam_size, nodes_per_row,
-                                                  &p.nodes_per_slot, &p.n_slots);
+                                                  scratch_bytes, &p.nodes_per_slot, &p.n_slots);
     if (scratch_bytes < need) return fctc::handle_fail(h, FCTC_E_CAPACITY, "beam scratch too small (see fctc_beam_scratch_bytes)");
     p.post = post_dev; p.N = n_reads; p.T = n_rows; p.C = n_labels; p.beam_size = beam_size; p.threshold = beam_cut_threshold;
     p.collapse = 0; p.labels = labels_dev; p.path = path_dev; p.pool_cap = pool_capacity; p.offsets = offsets_dev;
@@ -266,7 +266,7 @@ extern "C" int fctc_crf_beam_search(fctc_handle* h, const float* post_host, int6
     const int32_t tries[2] = {0, std::max<int32_t>(1, (n_labels - 1) * beam_size)};
     for (int attempt = 0; attempt < 2; ++attempt) {
         const int64_t need = fctc::beam_scratch_bytes(fctc::handle_sm_count(h), 1, n_rows, n_labels, beam_size, tries[attempt],
-                                                      nullptr, nullptr);
+                                                      0, nullptr, nullptr);
         void* scratch = fctc::handle_device_buffer(h, 8, size_t(need));
         if (!scratch) return FCTC_E_NOMEM;
         CRF_CUDA(cudaMemsetAsync(dcur, 0, 8, st));

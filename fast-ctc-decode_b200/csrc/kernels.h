@@ -66,8 +66,9 @@ struct BeamParams {
     int n_init;
 };
 
+// budget_bytes > 0: use at most that much (fewer pool slots = fewer reads in flight); 0: the full plan.
 int64_t beam_scratch_bytes(int sm_count, int64_t N, int64_t T, int C, int beam_size, int nodes_per_row,
-                           int64_t* nodes_per_slot, int* n_slots);
+                           int64_t budget_bytes, int64_t* nodes_per_slot, int* n_slots);
 cudaError_t launch_beam(const BeamParams& p, int sm_count, cudaStream_t stream);
 bool beam_shape_supported(int beam_size, int C);
 

@@ -115,10 +115,12 @@ int fctc_viterbi_search(fctc_handle* h, const float* post_host, int64_t n_rows, 
  * 0 <= threshold < 1/n_labels; src/lib.rs:333-349) is the caller's, as in the reference, but is
  * re-checked here and reported as FCTC_E_ARGUMENT.
  *
- * The device API needs trie scratch: fctc_beam_scratch_bytes() bytes at scratch_dev (256-byte
- * aligned), sized for nodes_per_row proposals per posterior row per read in flight (the hard
- * bound is (n_labels-1)*beam_size; 0 selects a default that the host entry points grow on
- * FCTC_NODE_POOL_OVERFLOW).
+ * The device API needs trie scratch at scratch_dev (256-byte aligned): one pool of nodes_per_row
+ * proposals per posterior row for every read in flight (hard bound (n_labels-1)*beam_size; 0
+ * selects a default that the host entry points grow on FCTC_NODE_POOL_OVERFLOW).
+ * fctc_beam_scratch_bytes() is the recommended size (a pool per resident warp, capped at 96 GiB);
+ * a smaller buffer is accepted — the launch then keeps fewer reads in flight (at least 4 pools
+ * must fit, else FCTC_E_CAPACITY).
  * ------------------------------------------------------------------------------------------ */
 int64_t fctc_beam_scratch_bytes(const fctc_handle* h, int64_t n_reads, int64_t n_rows, int32_t n_labels,
                                 int32_t beam_size, int32_t nodes_per_row);
