@@ -73,6 +73,7 @@ struct DxBeam {
     float* lab;
     float* gap;
     float* p2;
+    int* st;  // crf transition state
 };
 __device__ __forceinline__ DxBeam dx_beam(unsigned char* base, int B) {
     DxBeam v;
@@ -83,6 +84,7 @@ __device__ __forceinline__ DxBeam dx_beam(unsigned char* base, int B) {
     v.lab = reinterpret_cast<float*>(v.dep + B);
     v.gap = v.lab + B;
     v.p2 = v.gap + B;
+    v.st = reinterpret_cast<int*>(v.p2 + B);
     return v;
 }
 
@@ -158,6 +160,11 @@ __device__ __forceinline__ DxCell dx_step(const DxCell& last, float pgap, float 
     return c;
 }
 
+// CRF = true gives duplex::crf_beam_search (src/duplex.rs:652-834): both networks are [T, S, C], every
+// hypothesis carries a transition state, rows are read at [t][state], a label moves the state to
+// (state * n_base) % n_state + label, and there is no repeat case.  Network-2 values are mapped to
+// log space on the fly there (a [T2, S, C] log table per pair would not fit the scratch).
+template <bool CRF>
 __global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexParams p, const DuplexLayout L) {
     extern __shared__ __align__(16) unsigned char smem[];
     double* s_invc = reinterpret_cast<double*>(smem);
@@ -174,7 +181,8 @@ __global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexP
     const int B = p.beam_size, C = p.C, NL = C - 1;
     const int T1 = p.T1, T2 = p.T2, W = p.W;
     const int mode = p.exp_mode;
-    const bool collapse = p.collapse != 0;
+    const bool collapse = !CRF && p.collapse != 0;
+    const int NS = CRF ? p.S : 1;
     const float NEG = dx_neg_inf();
 
     int* newcnt = reinterpret_cast<int*>(ws + L.off_newcnt);
@@ -202,13 +210,42 @@ __global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexP
         ticket = __shfl_sync(DXFULL, ticket, 0);
         if (ticket >= (unsigned long long)p.N) break;
         const long long n = (long long)ticket;
-        const float* rd1 = p.post1 + n * (long long)T1 * C;
-        const float* rd2 = p.post2 + n * (long long)T2 * C;
+        const float* rd1 = p.post1 + n * (long long)T1 * C * NS;
+        const float* rd2 = p.post2 + n * (long long)T2 * C * NS;
+        // network-2 value of row i, state s, column c in log space
+        auto lp2 = [&](int i, int s_, int c) -> float {
+            if (CRF) return glibc_logf(rd2[((size_t)i * NS + s_) * C + c], s_invc, s_logc);
+            return S.logp2[(size_t)i * C + c];
+        };
         const long long* env = p.env ? p.env + n * (long long)T1 * 2 : nullptr;
         int status = FCTC_OK;
 
         // network 2 in log space (src/duplex.rs:453)
-        for (int i = lane; i < T2 * C; i += 32) S.logp2[i] = glibc_logf(rd2[i], s_invc, s_logc);
+        if (!CRF)
+            for (int i = lane; i < T2 * C; i += 32) S.logp2[i] = glibc_logf(rd2[i], s_invc, s_logc);
+        int init_state_1 = 0, init_state_2 = 0;
+        if (CRF) {  // argmax of the initial state scores (src/duplex.rs:679, 691); NaN aborts the reference
+            bool bad = false;
+            if (lane == 0) {
+                for (int which = 0; which < 2; ++which) {
+                    const float* init = which ? p.init2 + n * p.n_init2 : p.init1 + n * p.n_init1;
+                    const int ni = which ? p.n_init2 : p.n_init1;
+                    float best = init[0];
+                    int arg = 0;
+                    bad = bad || (best != best);
+                    for (int i = 1; i < ni; ++i) {
+                        const float v = init[i];
+                        bad = bad || (v != v);
+                        if (v > best) { best = v; arg = i; }
+                    }
+                    if (arg >= NS) bad = true;
+                    if (which) init_state_2 = arg; else init_state_1 = arg;
+                }
+            }
+            init_state_1 = __shfl_sync(DXFULL, init_state_1, 0);
+            init_state_2 = __shfl_sync(DXFULL, init_state_2, 0);
+            if (__shfl_sync(DXFULL, int(bad), 0)) status = FCTC_REFERENCE_PANIC;
+        }
         // root vector over envelope[(0,1)] rows (src/duplex.rs:476-477, 389-409)
         unsigned long long ub0 = env ? (unsigned long long)env[1] : (unsigned long long)T2;
         if (ub0 > (unsigned long long)T2) status = FCTC_INVALID_ENVELOPE;  // the reference would panic on the slice
@@ -219,9 +256,11 @@ __global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexP
             if (lane == 0) {
                 float cur = 0.0f;
                 S.rootv[0] = cur;
+                int rs = init_state_2;  // crf_root_probs walks the blank transitions (src/duplex.rs:430-438)
                 for (int i = 0; i < int(ub0); ++i) {
-                    cur = __fadd_rn(cur, S.logp2[(size_t)i * C]);
+                    cur = __fadd_rn(cur, lp2(i, rs, 0));
                     S.rootv[i + 1] = cur;
+                    if (CRF) rs = int(((long long)rs * NL) % NS);
                 }
             }
         }
@@ -230,6 +269,7 @@ __global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexP
         if (lane == 0) {  // src/duplex.rs:465-473
             bv.nd[0] = DXROOT; bv.par[0] = -2; bv.tip[0] = -1; bv.dep[0] = 0;
             bv.lab[0] = NEG; bv.gap[0] = 0.0f; bv.p2[0] = 0.0f;
+            bv.st[0] = init_state_1;
         }
         for (int l = lane; l < NL; l += 32) root_child[l] = -1;
         int nbeam = 1;
@@ -251,7 +291,13 @@ __global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexP
                 status = FCTC_NODE_POOL_OVERFLOW;
                 break;
             }
-            for (int c = lane; c < C; c += 32) lp1[c] = glibc_logf(rd1[(size_t)t * C + c], s_invc, s_logc);
+            if (!CRF)
+                for (int c = lane; c < C; c += 32) lp1[c] = glibc_logf(rd1[(size_t)t * C + c], s_invc, s_logc);
+            // network-1 value of this row for a hypothesis in state s_, column c
+            auto row1 = [&](int s_, int c) -> float {
+                if (CRF) return glibc_logf(rd1[((size_t)t * NS + s_) * C + c], s_invc, s_logc);
+                return lp1[c];
+            };
 
             // ---- extend the vectors of the beam's nodes (src/duplex.rs:490-522) ----------------------
             if (hi > last_hi) {
@@ -263,6 +309,7 @@ __global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexP
                     for (int k = 0; k < nbeam; ++k) r += (bv.nd[k] < me) ? 1 : 0;
                     nb.nd[r] = me; nb.par[r] = bv.par[lane]; nb.tip[r] = bv.tip[lane]; nb.dep[r] = bv.dep[lane];
                     nb.lab[r] = bv.lab[lane]; nb.gap[r] = bv.gap[lane]; nb.p2[r] = bv.p2[lane];
+                    nb.st[r] = bv.st[lane];
                 }
                 __syncwarp();
                 cur ^= 1;
@@ -271,6 +318,7 @@ __global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexP
                 const int node = (lane < nbeam) ? bv.nd[lane] : DXROOT;
                 const bool active = node >= 0;
                 int my_par = -2, my_lab = 0, v_end = 0, par_end = 0;
+                const int my_state = (lane < nbeam) ? bv.st[lane] : 0;  // crf_extend uses the entry's own state (:728)
                 bool repeat = false;
                 float mx = NEG;
                 DxCell last{NEG, NEG, NEG};
@@ -302,7 +350,7 @@ __global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexP
                     }
                     // the parent's label decides the repeat case, independent of collapse (:511)
                     const int plab = (my_par >= 0) ? int(S.nlab[my_par]) : -1;
-                    repeat = (plab == my_lab);
+                    repeat = !CRF && (plab == my_lab);
                     bool par_in_beam = false;
                     for (int k = 0; k < nbeam; ++k) par_in_beam |= (bv.nd[k] == my_par);
                     par_end = (my_par >= 0) ? ((par_in_beam) ? hi : S.vend[my_par]) : 0;
@@ -320,8 +368,7 @@ __global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexP
                         // a parent that is in the beam has (by now) cells up to i-1; others are as stored
                         dx_parent_get(S, my_par, i - 1, root_len, (my_par >= 0 && par_end == hi) ? i : par_end, W, mode,
                                       pgap, ptot);
-                        const DxCell c = dx_step(last, pgap, ptot, S.logp2[(size_t)i * C], S.logp2[(size_t)i * C + my_lab + 1],
-                                                 repeat, mode);
+                        const DxCell c = dx_step(last, pgap, ptot, lp2(i, my_state, 0), lp2(i, my_state, my_lab + 1), repeat, mode);
                         const int sl = i % W;
                         vd[sl] = c.label; vd[W + sl] = c.gap; vd[2 * W + sl] = c.total;
                         mx = lg_max(mx, c.total);
@@ -338,7 +385,6 @@ __global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexP
             last_hi = hi;
             __syncwarp();  // lp1 row visible to every lane
 
-            const float p_blank = lp1[0];
             DxBeam nb = dx_beam(ws + (cur ^ 1) * L.beam_stride, B);
 
             // ---- phase A: own continuation (+ the parent's extension, folded in) ------------------
@@ -347,6 +393,7 @@ __global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexP
                 const int node = bv.nd[b];
                 const float lab = bv.lab[b], gap = bv.gap[b];
                 const int tip = bv.tip[b];
+                const float p_blank = row1(bv.st[b], 0);
                 bool has_self = false;
                 float s_lab = NEG, s_gap = NEG;
                 if (p_blank > thr) {  // src/duplex.rs:529-534
@@ -354,7 +401,7 @@ __global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexP
                     has_self = true;
                 }
                 if (collapse && tip >= 0) {  // :540-544
-                    const float pt = lp1[tip + 1];
+                    const float pt = row1(bv.st[b], tip + 1);
                     if (!(pt < thr)) {
                         s_lab = __fadd_rn(lab, pt);
                         has_self = true;
@@ -366,7 +413,7 @@ __global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexP
                     for (int k = 0; k < nbeam; ++k)
                         if (bv.nd[k] == mypar) r = k;
                     if (r >= 0) {
-                        const float pt = lp1[tip + 1];
+                        const float pt = row1(bv.st[r], tip + 1);  // the parent's row
                         if (!(pt < thr)) {
                             float c;
                             if (collapse && bv.tip[r] == tip) c = __fadd_rn(bv.gap[r], pt);           // :563-568
@@ -394,7 +441,7 @@ __global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexP
                 const int tip = bv.tip[b];
                 for (int l = 0; l < NL; ++l) {
                     const int s = b * C + 1 + l;
-                    const float pl = lp1[l + 1];
+                    const float pl = row1(bv.st[b], l + 1);
                     uint32_t key = 0;
                     if (!(pl < thr)) {  // :537-539
                         const bool repeat = collapse && l == tip;
@@ -446,6 +493,7 @@ __global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexP
                     const int b = newlist[j] >> 16, l = newlist[j] & 0xffff;
                     const int id = int(n_nodes) + j;
                     const int pnode = bv.nd[b];
+                    const int tstate = bv.st[b];  // crf_build uses the proposing hypothesis' state (:766)
                     const bool repeat = collapse && l == bv.tip[b];
                     const int par_end = (pnode >= 0) ? S.vend[pnode] : 0;
                     float* vd = S.vdata + (size_t)id * 3 * W;
@@ -455,7 +503,7 @@ __global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexP
                     for (int i = lo; i < hi; ++i) {
                         float pgap, ptot;
                         dx_parent_get(S, pnode, i - 1, root_len, par_end, W, mode, pgap, ptot);
-                        const DxCell c = dx_step(last, pgap, ptot, S.logp2[(size_t)i * C], S.logp2[(size_t)i * C + l + 1], repeat, mode);
+                        const DxCell c = dx_step(last, pgap, ptot, lp2(i, tstate, 0), lp2(i, tstate, l + 1), repeat, mode);
                         vd[sl] = c.label; vd[W + sl] = c.gap; vd[2 * W + sl] = c.total;
                         mx = lg_max(mx, c.total);
                         last = c;
@@ -527,8 +575,15 @@ __global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexP
                 nb.lab[lane] = clab[i];
                 nb.gap[lane] = cgap[i];
                 nb.p2[lane] = cp2[i];
-                if (sl == 0) { nb.par[lane] = bv.par[b]; nb.tip[lane] = bv.tip[b]; nb.dep[lane] = bv.dep[b]; }
-                else { nb.par[lane] = bv.nd[b]; nb.tip[lane] = sl - 1; nb.dep[lane] = bv.dep[b] + 1; }
+                if (sl == 0) { nb.par[lane] = bv.par[b]; nb.tip[lane] = bv.tip[b]; nb.dep[lane] = bv.dep[b]; nb.st[lane] = bv.st[b]; }
+                else {
+                    nb.par[lane] = bv.nd[b]; nb.tip[lane] = sl - 1; nb.dep[lane] = bv.dep[b] + 1;
+                    nb.st[lane] = CRF ? int(((long long)bv.st[b] * NL) % NS) + (sl - 1) : 0;  // src/duplex.rs:775
+                }
+            }
+            if (CRF) {
+                const bool bad_state = (lane < n_keep) && (nb.st[lane] >= NS);
+                if (__any_sync(DXFULL, bad_state)) status = FCTC_REFERENCE_PANIC;  // the reference's slice would panic
             }
             __syncwarp();
             cur ^= 1;
@@ -571,7 +626,7 @@ static bool plan_duplex(int B, int C, DuplexLayout* L) {
     if (B > DX_MAX_BEAM || B < 1 || C < 1 || C > 256) return false;
     const int NL = C - 1 > 0 ? C - 1 : 1;
     auto up = [](long long v, int a) { return (v + a - 1) / a * a; };
-    L->beam_stride = int(up(7LL * 4 * B, 16));
+    L->beam_stride = int(up(8LL * 4 * B, 16));
     long long o = 2LL * L->beam_stride;
     L->off_newcnt = int(o);  o = up(o + 4LL * B, 16);
     L->off_fold = int(o);    o = up(o + (long long)B * NL, 16);
@@ -631,11 +686,14 @@ cudaError_t launch_duplex(const DuplexParams& p, cudaStream_t stream) {
     DuplexLayout L;
     if (!plan_duplex(p.beam_size, p.C, &L)) return cudaErrorInvalidConfiguration;
     const int smem = L.cta_fixed + L.warp_bytes * DX_WARPS;
-    cudaError_t e = cudaFuncSetAttribute(duplex_search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    const bool crf = p.S > 0;
+    cudaError_t e = crf ? cudaFuncSetAttribute(duplex_search_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
+                        : cudaFuncSetAttribute(duplex_search_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
     e = cudaMemsetAsync(p.ticket, 0, sizeof(unsigned long long), stream);
     if (e != cudaSuccess) return e;
-    duplex_search_kernel<<<p.n_slots / DX_WARPS, DX_THREADS, smem, stream>>>(p, L);
+    if (crf) duplex_search_kernel<true><<<p.n_slots / DX_WARPS, DX_THREADS, smem, stream>>>(p, L);
+    else duplex_search_kernel<false><<<p.n_slots / DX_WARPS, DX_THREADS, smem, stream>>>(p, L);
     return cudaGetLastError();
 }
 
@@ -864,5 +922,123 @@ extern "C" int fctc_beam_search_duplex(fctc_handle* h, const float* post1_host, 
     for (int64_t i = 0; i < m; ++i)
         if (labels) labels[i] = pin[ol + *off1 + i];
     return *st1;
+}
+
+// ---- crf variant: replaces duplex::crf_beam_search (src/duplex.rs:652-834) as called from
+//      src/lib.rs:563-574.  The reference holds no test vector for it (parity unpinned): the check
+//      here is against this repository's CPU restatement. ---------------------------------------------
+extern "C" int fctc_crf_beam_search_duplex_batch_device(
+    fctc_handle* h, const float* post1_dev, const float* init1_dev, int32_t n_init1, const float* post2_dev,
+    const float* init2_dev, int32_t n_init2, int64_t n_pairs, int64_t n_rows_1, int64_t n_rows_2, int32_t n_state,
+    int32_t n_labels, const int64_t* envelope_dev, int32_t max_window, int32_t beam_size, float beam_cut_threshold,
+    int32_t exp_mode, uint8_t* labels_dev, int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev,
+    int32_t* status_dev, unsigned long long* pool_used_dev, void* scratch_dev, int64_t scratch_bytes,
+    int32_t nodes_per_row, void* stream) {
+    if (int rc = dx_check(h, n_pairs, n_rows_1, n_rows_2, n_labels, beam_size, beam_cut_threshold)) return rc;
+    if (n_state <= 0 || n_init1 <= 0 || n_init2 <= 0) return fctc::handle_fail(h, FCTC_E_ARGUMENT, "n_state and the init_state vectors must be non-empty");
+    if (n_rows_2 * int64_t(n_labels) * n_state >= (int64_t(1) << 40)) return fctc::handle_fail(h, FCTC_E_UNSUPPORTED, "network output too large");
+    if (!post1_dev || !post2_dev || !init1_dev || !init2_dev || !labels_dev || !offsets_dev || !lens_dev || !status_dev ||
+        !pool_used_dev || !scratch_dev)
+        return fctc::handle_fail(h, FCTC_E_ARGUMENT, "null device pointer");
+    if (reinterpret_cast<uintptr_t>(scratch_dev) & 255u) return fctc::handle_fail(h, FCTC_E_ARGUMENT, "scratch_dev must be 256-byte aligned");
+    if (exp_mode != 0 && exp_mode != 1) return fctc::handle_fail(h, FCTC_E_ARGUMENT, "exp_mode must be 0 (exact exp) or 1 (fastexp as shipped)");
+    cudaError_t e = cudaSetDevice(fctc::handle_device(h));
+    if (e != cudaSuccess) return fctc::handle_fail(h, FCTC_E_CUDA, cudaGetErrorString(e));
+    fctc::DuplexParams p{};
+    p.W = int((max_window > 0 && max_window < n_rows_2 ? max_window : n_rows_2) + 1);
+    const int64_t need = fctc::duplex_scratch_bytes(fctc::handle_sm_count(h), n_pairs, int(n_rows_1), int(n_rows_2), n_labels,
+                                                    beam_size, p.W, nodes_per_row, scratch_bytes, &p.nodes_per_slot, &p.n_slots);
+    if (need > scratch_bytes) return fctc::handle_fail(h, FCTC_E_CAPACITY, "duplex scratch too small (see fctc_duplex_scratch_bytes)");
+    p.post1 = post1_dev; p.post2 = post2_dev; p.env = reinterpret_cast<const long long*>(envelope_dev);
+    p.N = n_pairs; p.T1 = int(n_rows_1); p.T2 = int(n_rows_2); p.C = n_labels; p.beam_size = beam_size;
+    p.threshold = beam_cut_threshold; p.collapse = 0; p.exp_mode = exp_mode;
+    p.labels = labels_dev; p.pool_cap = pool_capacity; p.offsets = offsets_dev; p.lens = lens_dev; p.status = status_dev;
+    p.cursor = pool_used_dev; p.scratch = scratch_dev; p.ticket = static_cast<unsigned long long*>(scratch_dev);
+    p.S = n_state; p.init1 = init1_dev; p.init2 = init2_dev; p.n_init1 = n_init1; p.n_init2 = n_init2;
+    e = fctc::launch_duplex(p, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return fctc::handle_fail(h, FCTC_E_CUDA, cudaGetErrorString(e));
+    return 0;
+}
+
+// One pair from host memory; arrays C-contiguous: post [T, S, C], init [n_init], envelope usize [T1, 2] or NULL.
+extern "C" int fctc_crf_beam_search_duplex(fctc_handle* h, const float* post1_host, int64_t n_rows_1,
+                                           const float* init1_host, int32_t n_init1, const float* post2_host,
+                                           int64_t n_rows_2, const float* init2_host, int32_t n_init2, int32_t n_state,
+                                           int32_t n_labels, const uint64_t* envelope, int32_t beam_size,
+                                           float beam_cut_threshold, int32_t exp_mode, uint8_t* labels, int64_t capacity,
+                                           int64_t* out_len) {
+    if (int rc = dx_check(h, 1, n_rows_1, n_rows_2, n_labels, beam_size, beam_cut_threshold)) return rc;
+    if (!post1_host || !post2_host || !init1_host || !init2_host || !out_len) return fctc::handle_fail(h, FCTC_E_ARGUMENT, "null pointer");
+    if (n_state <= 0 || n_init1 <= 0 || n_init2 <= 0) return fctc::handle_fail(h, FCTC_E_ARGUMENT, "n_state and the init_state vectors must be non-empty");
+    cudaError_t e = cudaSetDevice(fctc::handle_device(h));
+    if (e != cudaSuccess) return fctc::handle_fail(h, FCTC_E_CUDA, cudaGetErrorString(e));
+    cudaStream_t st = fctc::handle_stream(h);
+    const int64_t stride = std::max<int64_t>((n_rows_1 + 31) & ~int64_t(31), 32);
+    const size_t b1 = size_t(n_rows_1) * n_state * n_labels * 4, b2 = size_t(n_rows_2) * n_state * n_labels * 4;
+    float* d1 = static_cast<float*>(fctc::handle_device_buffer(h, 0, b1));
+    float* d2 = static_cast<float*>(fctc::handle_device_buffer(h, 1, std::max<size_t>(b2, 16)));
+    long long* de = static_cast<long long*>(fctc::handle_device_buffer(h, 2, size_t(n_rows_1) * 16));
+    uint8_t* dl = static_cast<uint8_t*>(fctc::handle_device_buffer(h, 3, size_t(stride)));
+    int64_t* doff = static_cast<int64_t*>(fctc::handle_device_buffer(h, 4, 64));
+    int32_t* dlen = static_cast<int32_t*>(fctc::handle_device_buffer(h, 5, 64));
+    int32_t* dst = static_cast<int32_t*>(fctc::handle_device_buffer(h, 6, 64));
+    unsigned long long* dcur = static_cast<unsigned long long*>(fctc::handle_device_buffer(h, 7, 256));
+    float* di1 = static_cast<float*>(fctc::handle_device_buffer(h, 11, size_t(n_init1) * 4));
+    float* di2 = static_cast<float*>(fctc::handle_device_buffer(h, 12, size_t(n_init2) * 4));
+    unsigned char* pin = static_cast<unsigned char*>(fctc::handle_pinned_buffer(h, 3, size_t(stride) + size_t(n_rows_1) * 16 + 64));
+    if (!d1 || !d2 || !de || !dl || !doff || !dlen || !dst || !dcur || !di1 || !di2 || !pin) return FCTC_E_NOMEM;
+#define DXC(call)                                                                              \
+    do {                                                                                       \
+        cudaError_t e__ = (call);                                                              \
+        if (e__ != cudaSuccess) return fctc::handle_fail(h, FCTC_E_CUDA, cudaGetErrorString(e__)); \
+    } while (0)
+    int64_t wmax = n_rows_2;
+    long long* henv = reinterpret_cast<long long*>(pin + 64);
+    if (envelope) {
+        wmax = 1;
+        for (int64_t t = 0; t < n_rows_1; ++t) {
+            henv[2 * t] = (long long)envelope[2 * t];
+            henv[2 * t + 1] = (long long)envelope[2 * t + 1];
+            const uint64_t lo = envelope[2 * t], hu = envelope[2 * t + 1];
+            const int64_t hi = hu > uint64_t(n_rows_2) ? n_rows_2 : int64_t(hu);
+            if (lo < uint64_t(hi) && hi - int64_t(lo) > wmax) wmax = hi - int64_t(lo);
+        }
+        DXC(cudaMemcpyAsync(de, henv, size_t(n_rows_1) * 16, cudaMemcpyHostToDevice, st));
+    }
+    DXC(cudaMemcpyAsync(d1, post1_host, b1, cudaMemcpyHostToDevice, st));
+    if (b2) DXC(cudaMemcpyAsync(d2, post2_host, b2, cudaMemcpyHostToDevice, st));
+    DXC(cudaMemcpyAsync(di1, init1_host, size_t(n_init1) * 4, cudaMemcpyHostToDevice, st));
+    DXC(cudaMemcpyAsync(di2, init2_host, size_t(n_init2) * 4, cudaMemcpyHostToDevice, st));
+    int32_t* hlen = reinterpret_cast<int32_t*>(pin);
+    int32_t* hst = hlen + 1;
+    int64_t* hoff = reinterpret_cast<int64_t*>(pin + 8);
+    uint8_t* hl = pin + 64 + size_t(n_rows_1) * 16;
+    const int32_t tries[2] = {0, std::max<int32_t>(1, (n_labels - 1) * beam_size)};
+    for (int attempt = 0; attempt < 2; ++attempt) {
+        int64_t nps = 0;
+        int nsl = 0;
+        const int64_t need = fctc::duplex_scratch_bytes(fctc::handle_sm_count(h), 1, int(n_rows_1), int(n_rows_2), n_labels, beam_size,
+                                                        int(wmax + 1), tries[attempt], dx_free_budget(), &nps, &nsl);
+        void* scratch = fctc::handle_device_buffer(h, 8, size_t(need));
+        if (!scratch) return FCTC_E_NOMEM;
+        DXC(cudaMemsetAsync(dcur, 0, 8, st));
+        int rc = fctc_crf_beam_search_duplex_batch_device(h, d1, di1, n_init1, d2, di2, n_init2, 1, n_rows_1, n_rows_2, n_state, n_labels,
+                                                          envelope ? reinterpret_cast<const int64_t*>(de) : nullptr, int32_t(wmax),
+                                                          beam_size, beam_cut_threshold, exp_mode, dl, stride, doff, dlen, dst, dcur,
+                                                          scratch, need, tries[attempt], st);
+        if (rc < 0) return rc;
+        DXC(cudaMemcpyAsync(hlen, dlen, 4, cudaMemcpyDeviceToHost, st));
+        DXC(cudaMemcpyAsync(hst, dst, 4, cudaMemcpyDeviceToHost, st));
+        DXC(cudaMemcpyAsync(hoff, doff, 8, cudaMemcpyDeviceToHost, st));
+        DXC(cudaMemcpyAsync(hl, dl, size_t(stride), cudaMemcpyDeviceToHost, st));
+        DXC(cudaStreamSynchronize(st));
+        if (*hst != FCTC_NODE_POOL_OVERFLOW) break;
+    }
+#undef DXC
+    *out_len = *hlen;
+    const int64_t m = std::min<int64_t>(*hlen, capacity);
+    for (int64_t i = 0; i < m; ++i)
+        if (labels) labels[i] = hl[*hoff + i];
+    return *hst;
 }
 

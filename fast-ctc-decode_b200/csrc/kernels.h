@@ -93,6 +93,11 @@ struct DuplexParams {
     int64_t nodes_per_slot;
     int n_slots;
     unsigned long long* ticket;
+    // crf variant (duplex::crf_beam_search): S > 0 selects it; posts are [N, T, S, C]
+    int S;
+    const float* init1;  // [N, n_init1]
+    const float* init2;  // [N, n_init2]
+    int n_init1, n_init2;
 };
 bool duplex_shape_supported(int beam_size, int C);
 int64_t duplex_scratch_bytes(int sm_count, int64_t N, int T1, int T2, int C, int beam_size, int W, int nodes_per_row,

@@ -58,6 +58,11 @@ _SIGNATURES = {
     "fctc_crf_greedy_search": (C.c_int, [_vp, _vp, _i64, _i32, _i32, _vp, _i32, _i32, _f32, _f32, _vp, _vp, _vp, _i64,
                                          _vp]),
     "fctc_crf_beam_search": (C.c_int, [_vp, _vp, _i64, _i32, _i32, _vp, _i32, _i32, _f32, _vp, _vp, _i64, _vp]),
+    "fctc_crf_beam_search_duplex_batch_device": (C.c_int, [_vp, _vp, _vp, _i32, _vp, _vp, _i32, _i64, _i64, _i64, _i32,
+                                                           _i32, _vp, _i32, _i32, _f32, _i32, _vp, _i64, _vp, _vp, _vp,
+                                                           _vp, _vp, _i64, _i32, _vp]),
+    "fctc_crf_beam_search_duplex": (C.c_int, [_vp, _vp, _i64, _vp, _i32, _vp, _i64, _vp, _i32, _i32, _i32, _vp, _i32,
+                                              _f32, _i32, _vp, _i64, _vp]),
     "fctc_synth_posteriors_device": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _i32, _u64, _i64, _vp]),
     "fctc_host_phred": (C.c_uint32, [_f32, _f32, _f32]),
     "fctc_host_log10f": (None, [_vp, _vp, _i64]),
@@ -335,6 +340,33 @@ class Decoder:
                                                           labels.ctypes.data, path.ctypes.data, cap, C.byref(n)))
         k = n.value
         return status, labels[:k].copy(), path[:k].copy()
+
+    def crf_beam_search_duplex(self, post1, init1, post2, init2, envelope=None, beam_size=5, beam_cut_threshold=0.0,
+                               exp_mode=0):
+        post1, post2 = np.ascontiguousarray(post1), np.ascontiguousarray(post2)
+        init1, init2 = np.ascontiguousarray(init1), np.ascontiguousarray(init2)
+        for a, nd in ((post1, 3), (post2, 3), (init1, 1), (init2, 1)):
+            if a.dtype != np.float32 or a.ndim != nd:
+                raise TypeError("expected float32 arrays [T, S, C] and [n_init]")
+        T1, S, Cn = post1.shape
+        if post2.shape[2] != Cn or post2.shape[1] != S:
+            raise ValueError("inner axes of the network outputs do not match")
+        env = None
+        if envelope is not None:
+            env = np.ascontiguousarray(envelope, dtype=np.uint64)
+            if env.shape[0] != T1:
+                raise ValueError("the lengths of network_output_1 and envelope do not match")
+            if env.ndim != 2 or env.shape[1] != 2:
+                raise ValueError("the inner axis of envelope must have size 2")
+        cap = max(T1, 1)
+        labels = np.empty(cap, np.uint8)
+        n = _i64(0)
+        status = self._check(self._L.fctc_crf_beam_search_duplex(self._h, post1.ctypes.data, T1, init1.ctypes.data,
+                                                                 init1.size, post2.ctypes.data, post2.shape[0],
+                                                                 init2.ctypes.data, init2.size, S, Cn, _np_ptr(env),
+                                                                 beam_size, beam_cut_threshold, exp_mode,
+                                                                 labels.ctypes.data, cap, C.byref(n)))
+        return status, labels[:n.value].copy()
 
     def beam_search(self, post, beam_size=5, beam_cut_threshold=0.0, collapse_repeats=True):
         post = _as_f32_2d(post)

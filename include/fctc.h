@@ -220,6 +220,21 @@ int fctc_crf_beam_search(fctc_handle* h, const float* post_host, int64_t n_rows,
                          const float* init_host, int32_t n_init, int32_t beam_size, float beam_cut_threshold,
                          uint8_t* labels, int64_t* path, int64_t capacity, int64_t* out_len);
 
+int fctc_crf_beam_search_duplex_batch_device(fctc_handle* h, const float* post1_dev, const float* init1_dev,
+                                             int32_t n_init1, const float* post2_dev, const float* init2_dev,
+                                             int32_t n_init2, int64_t n_pairs, int64_t n_rows_1, int64_t n_rows_2,
+                                             int32_t n_state, int32_t n_labels, const int64_t* envelope_dev,
+                                             int32_t max_window, int32_t beam_size, float beam_cut_threshold,
+                                             int32_t exp_mode, uint8_t* labels_dev, int64_t pool_capacity,
+                                             int64_t* offsets_dev, int32_t* lens_dev, int32_t* status_dev,
+                                             unsigned long long* pool_used_dev, void* scratch_dev,
+                                             int64_t scratch_bytes, int32_t nodes_per_row, void* stream);
+int fctc_crf_beam_search_duplex(fctc_handle* h, const float* post1_host, int64_t n_rows_1, const float* init1_host,
+                                int32_t n_init1, const float* post2_host, int64_t n_rows_2, const float* init2_host,
+                                int32_t n_init2, int32_t n_state, int32_t n_labels, const uint64_t* envelope,
+                                int32_t beam_size, float beam_cut_threshold, int32_t exp_mode, uint8_t* labels,
+                                int64_t capacity, int64_t* out_len);
+
 /* ------------------------------------------------------------------------------------------
  * Synthetic posterior generator used by bench.py and the tests (no reference counterpart; it
  * implements SURVEY.md §8d's input definition): fills post_dev[n_reads, n_rows, n_labels] with

@@ -112,3 +112,34 @@ def test_device_batch_greedy(dec, oracle):
         o = n * stride
         assert ln[n] == len(ol) and np.array_equal(lab[o:o + ln[n]], ol) and np.array_equal(q[o:o + ln[n]], oq)
         assert np.array_equal(pth[o:o + ln[n]], op)
+
+
+def test_crf_duplex_matches_oracle(dec, oracle):
+    """duplex::crf_beam_search (src/duplex.rs:652-834).  The reference has no vector for it (parity
+    unpinned); compared with this repository's restatement: exactly in the max-plus mode (no
+    exp/log1p), by tolerance in the exact-exp mode."""
+    import fast_ctc_decode as fcd
+    rng = np.random.default_rng(21)
+    for (T1, T2, S, C, beam, w) in [(80, 80, 16, 5, 5, 8), (60, 70, 4, 3, 5, None), (100, 100, 64, 5, 8, 6)]:
+        hid = np.where(rng.random(T1) < 0.6, 0, rng.integers(1, C, T1))
+
+        def render(T):
+            idx = np.minimum((np.arange(T) * T1) // T, T1 - 1)
+            x = (0.1 * rng.random((T, S, C), dtype=np.float32)).astype(np.float32)
+            x[np.arange(T), :, hid[idx]] += 1.0
+            x /= x.sum(axis=2, keepdims=True, dtype=np.float32)
+            return x.astype(np.float32)
+        p1, p2 = render(T1), render(T2)
+        i1, i2 = rng.random(S, dtype=np.float32), rng.random(S, dtype=np.float32)
+        env = None
+        if w is not None:
+            c = (np.arange(T1) * T2) // T1
+            env = np.stack([np.maximum(0, c - w), np.minimum(T2, c + w + 1)], axis=1).astype(np.uint64)
+        st, labels = dec.crf_beam_search_duplex(p1, i1, p2, i2, env, beam, 0.0, exp_mode=1)
+        ost, ol = oracle.crf_beam_search_duplex(p1, i1, p2, i2, env, beam, 0.0, exp_mode=1)
+        assert st == ost == 0 and labels.tolist() == ol.tolist()
+        st, labels = dec.crf_beam_search_duplex(p1, i1, p2, i2, env, beam, 0.0, exp_mode=0)
+        ost, ol = oracle.crf_beam_search_duplex(p1, i1, p2, i2, env, beam, 0.0, exp_mode=0)
+        assert st == ost == 0 and abs(len(labels) - len(ol)) <= max(2, len(ol) // 10)
+        seq = fcd.crf_beam_search_duplex(p1, i1, p2, i2, "NACGT"[:C], envelope=env, beam_size=beam)
+        assert isinstance(seq, str) and abs(len(seq) - len(ol)) <= max(2, len(ol) // 10)
