@@ -553,7 +553,12 @@ namespace {
 int beam_host_pass(fctc_handle* h, const float* post_host, int64_t n_reads, int64_t n_rows, int32_t n_labels,
                    int32_t beam_size, float thr, int32_t collapse, int32_t nodes_per_row, HostOut& out) {
     const int64_t slot_entries = std::max<int64_t>(roundup32(n_rows), 32);
-    const int64_t chunk = std::min<int64_t>(default_chunk_reads(n_rows * int64_t(n_labels) * 4), n_reads);
+    // The search keeps one read per resident warp busy for the read's whole length, so a chunk must hold
+    // several reads per warp slot (a 64 MiB chunk would leave most of the GPU idle); capped at 2 GiB.
+    const int64_t read_bytes = std::max<int64_t>(n_rows * int64_t(n_labels) * 4, 1);
+    int64_t chunk = std::max<int64_t>(default_chunk_reads(read_bytes), int64_t(h->sm_count) * 24 * 4);
+    chunk = std::min<int64_t>(chunk, std::max<int64_t>((int64_t(2) << 30) / read_bytes, 1));
+    chunk = std::min<int64_t>(chunk, n_reads);
     int64_t nodes_per_slot = 0;
     int n_slots = 0;
     size_t free_b = 0, total_b = 0;
