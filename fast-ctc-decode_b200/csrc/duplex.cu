@@ -98,13 +98,14 @@ struct DxSlot {
     int* voff;      // [cap]  first valid network-2 index of the node's vector
     int* vend;      // [cap]  one past the last
     float* vmx;     // [cap]  max_prob
+    int* vlo;       // [cap]  lower bound that max_prob currently covers (lets update_max skip rescans)
     float* vdata;   // [cap][3][W]: label, gap, total
 };
 __host__ __device__ inline size_t dx_up256(size_t v) { return (v + 255) & ~size_t(255); }
 __host__ __device__ inline size_t dx_slot_bytes(long long cap, int T2, int C, int W) {
     const int NL = C - 1 > 0 ? C - 1 : 1;
     return dx_up256((size_t)T2 * C * 4) + dx_up256((size_t)(T2 + 1) * 4) + dx_up256((size_t)cap * 4) +
-           dx_up256((size_t)cap * NL * 4) + dx_up256((size_t)cap) + 3 * dx_up256((size_t)cap * 4) +
+           dx_up256((size_t)cap * NL * 4) + dx_up256((size_t)cap) + 4 * dx_up256((size_t)cap * 4) +
            dx_up256((size_t)cap * 3 * (size_t)W * 4);
 }
 __device__ __forceinline__ DxSlot dx_slot(unsigned char* base, long long cap, int T2, int C, int W) {
@@ -119,6 +120,7 @@ __device__ __forceinline__ DxSlot dx_slot(unsigned char* base, long long cap, in
     s.voff = reinterpret_cast<int*>(p);    p += dx_up256((size_t)cap * 4);
     s.vend = reinterpret_cast<int*>(p);    p += dx_up256((size_t)cap * 4);
     s.vmx = reinterpret_cast<float*>(p);   p += dx_up256((size_t)cap * 4);
+    s.vlo = reinterpret_cast<int*>(p);     p += dx_up256((size_t)cap * 4);
     s.vdata = reinterpret_cast<float*>(p);
     return s;
 }
@@ -129,8 +131,9 @@ struct DxCell {
 
 // SecondaryProbs::get of the parent at index `at` (src/duplex.rs:167-179); only gap and
 // probability() are ever used by the recurrences.
-__device__ __forceinline__ void dx_parent_get(const DxSlot& S, int par, int at, int root_len, int par_end, int W,
-                                              int mode, float& pgap, float& ptotal) {
+// `pslot` is at mod W, kept incrementally by the caller; `par_off` the parent's first valid index.
+__device__ __forceinline__ void dx_parent_get(const DxSlot& S, int par, const float* pv, int at, int pslot, int root_len,
+                                              int par_off, int par_end, int W, int mode, float& pgap, float& ptotal) {
     pgap = dx_neg_inf();
     ptotal = dx_neg_inf();
     if (par == DXROOT) {
@@ -139,15 +142,13 @@ __device__ __forceinline__ void dx_parent_get(const DxSlot& S, int par, int at, 
             pgap = S.rootv[idx];
             ptotal = lg_add(dx_neg_inf(), pgap, mode);
         }
-    } else {
-        const int off = S.voff[par];
-        if (at >= off && at < par_end) {
-            const int slot = at % W;
-            const float* v = S.vdata + (size_t)par * 3 * W;
-            pgap = v[W + slot];
-            ptotal = v[2 * W + slot];
-        }
+    } else if (at >= par_off && at < par_end) {
+        pgap = pv[W + pslot];
+        ptotal = pv[2 * W + pslot];
     }
+}
+__device__ __forceinline__ int dx_mod(int i, int W) {  // i mod W for i >= -1
+    return i < 0 ? i + W : i % W;
 }
 
 // One step of the forward recurrence (src/duplex.rs:234-246 and :373-385).
@@ -337,15 +338,33 @@ __global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexP
                             off = keep;
                         }
                         if (v_end == off) { off = lo; v_end = lo; }
-                        // update_max(lo, hi) (:193-204)
+                        // update_max(lo, hi) (:193-204): max over [max(lo, off), min(hi, end)).  The stored
+                        // max covers [vlo, end); it stays valid unless a cell that drops out could have
+                        // been the maximum (lg_max never picks up NaN cells, so they cannot matter).
                         const int b0 = lo > off ? lo : off;
                         const int e0 = hi < v_end ? hi : v_end;
-                        mx = NEG;
-                        for (int i = b0; i < e0; ++i) mx = lg_max(mx, vd[2 * W + (i % W)]);
+                        const int old_lo = S.vlo[node];
+                        bool rescan = (old_lo > b0) || (e0 <= b0);
+                        if (!rescan) {
+                            int sl = dx_mod(old_lo, W);
+                            for (int i = old_lo; i < b0; ++i) {
+                                if (vd[2 * W + sl] >= mx) rescan = true;
+                                if (++sl == W) sl = 0;
+                            }
+                        }
+                        if (rescan) {
+                            mx = NEG;
+                            int sl = dx_mod(b0, W);
+                            for (int i = b0; i < e0; ++i) {
+                                mx = lg_max(mx, vd[2 * W + sl]);
+                                if (++sl == W) sl = 0;
+                            }
+                        }
+                        S.vlo[node] = b0;
                         S.voff[node] = off;
                     }
                     if (v_end > off) {
-                        const int sl = (v_end - 1) % W;
+                        const int sl = dx_mod(v_end - 1, W);
                         last.label = vd[sl]; last.gap = vd[W + sl]; last.total = vd[2 * W + sl];
                     }
                     // the parent's label decides the repeat case, independent of collapse (:511)
@@ -356,24 +375,28 @@ __global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexP
                     par_end = (my_par >= 0) ? ((par_in_beam) ? hi : S.vend[my_par]) : 0;
                 }
                 __syncwarp();  // every node's new offset is visible before children read their parents
+                const int par_off = (active && my_par >= 0) ? S.voff[my_par] : 0;
+                const float* pv = (active && my_par >= 0) ? S.vdata + (size_t)my_par * 3 * W : nullptr;
                 int imin = active ? v_end : hi;
 #pragma unroll
                 for (int d = 16; d > 0; d >>= 1) {
                     const int o = __shfl_xor_sync(DXFULL, imin, d);
                     imin = o < imin ? o : imin;
                 }
+                int sl_w = dx_mod(imin, W), sl_p = dx_mod(imin - 1, W);
                 for (int i = imin; i < hi; ++i) {  // lockstep over the network-2 row index
                     if (active && v_end <= i) {
                         float pgap, ptot;
                         // a parent that is in the beam has (by now) cells up to i-1; others are as stored
-                        dx_parent_get(S, my_par, i - 1, root_len, (my_par >= 0 && par_end == hi) ? i : par_end, W, mode,
-                                      pgap, ptot);
+                        dx_parent_get(S, my_par, pv, i - 1, sl_p, root_len, par_off, (my_par >= 0 && par_end == hi) ? i : par_end, W,
+                                      mode, pgap, ptot);
                         const DxCell c = dx_step(last, pgap, ptot, lp2(i, my_state, 0), lp2(i, my_state, my_lab + 1), repeat, mode);
-                        const int sl = i % W;
-                        vd[sl] = c.label; vd[W + sl] = c.gap; vd[2 * W + sl] = c.total;
+                        vd[sl_w] = c.label; vd[W + sl_w] = c.gap; vd[2 * W + sl_w] = c.total;
                         mx = lg_max(mx, c.total);
                         last = c;
                     }
+                    if (++sl_w == W) sl_w = 0;
+                    if (++sl_p == W) sl_p = 0;
                     __syncwarp();
                 }
                 if (active) {
@@ -496,13 +519,16 @@ __global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexP
                     const int tstate = bv.st[b];  // crf_build uses the proposing hypothesis' state (:766)
                     const bool repeat = collapse && l == bv.tip[b];
                     const int par_end = (pnode >= 0) ? S.vend[pnode] : 0;
+                    const int par_off = (pnode >= 0) ? S.voff[pnode] : 0;
+                    const float* pv = (pnode >= 0) ? S.vdata + (size_t)pnode * 3 * W : nullptr;
                     float* vd = S.vdata + (size_t)id * 3 * W;
                     DxCell last{NEG, NEG, NEG};
                     float mx = NEG;
-                    int sl = lo % W;
+                    int sl = dx_mod(lo, W), sl_p = dx_mod(lo - 1, W);
                     for (int i = lo; i < hi; ++i) {
                         float pgap, ptot;
-                        dx_parent_get(S, pnode, i - 1, root_len, par_end, W, mode, pgap, ptot);
+                        dx_parent_get(S, pnode, pv, i - 1, sl_p, root_len, par_off, par_end, W, mode, pgap, ptot);
+                        if (++sl_p == W) sl_p = 0;
                         const DxCell c = dx_step(last, pgap, ptot, lp2(i, tstate, 0), lp2(i, tstate, l + 1), repeat, mode);
                         vd[sl] = c.label; vd[W + sl] = c.gap; vd[2 * W + sl] = c.total;
                         mx = lg_max(mx, c.total);
@@ -512,6 +538,7 @@ __global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexP
                     S.parent[id] = pnode;
                     S.nlab[id] = uint8_t(l);
                     S.voff[id] = lo;
+                    S.vlo[id] = lo;
                     S.vend[id] = hi;
                     S.vmx[id] = mx;
                     for (int q = 0; q < NL; ++q) S.child[(size_t)id * NL + q] = -1;
