@@ -23,6 +23,7 @@
 //     cell of the previous index only).
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 
 #include "device_utils.cuh"
 #include "kernels.h"
@@ -99,14 +100,15 @@ struct DxSlot {
     int* vend;      // [cap]  one past the last
     float* vmx;     // [cap]  max_prob
     int* vlo;       // [cap]  lower bound that max_prob currently covers (lets update_max skip rescans)
-    float* vdata;   // [cap][3][W]: label, gap, total
+    float* vlast;   // [cap]  label probability of the vector's last cell (older label cells are never read)
+    float* vdata;   // [cap][2][W]: gap, total
 };
 __host__ __device__ inline size_t dx_up256(size_t v) { return (v + 255) & ~size_t(255); }
 __host__ __device__ inline size_t dx_slot_bytes(long long cap, int T2, int C, int W) {
     const int NL = C - 1 > 0 ? C - 1 : 1;
     return dx_up256((size_t)T2 * C * 4) + dx_up256((size_t)(T2 + 1) * 4) + dx_up256((size_t)cap * 4) +
-           dx_up256((size_t)cap * NL * 4) + dx_up256((size_t)cap) + 4 * dx_up256((size_t)cap * 4) +
-           dx_up256((size_t)cap * 3 * (size_t)W * 4);
+           dx_up256((size_t)cap * NL * 4) + dx_up256((size_t)cap) + 5 * dx_up256((size_t)cap * 4) +
+           dx_up256((size_t)cap * 2 * (size_t)W * 4);
 }
 __device__ __forceinline__ DxSlot dx_slot(unsigned char* base, long long cap, int T2, int C, int W) {
     const int NL = C - 1 > 0 ? C - 1 : 1;
@@ -121,6 +123,7 @@ __device__ __forceinline__ DxSlot dx_slot(unsigned char* base, long long cap, in
     s.vend = reinterpret_cast<int*>(p);    p += dx_up256((size_t)cap * 4);
     s.vmx = reinterpret_cast<float*>(p);   p += dx_up256((size_t)cap * 4);
     s.vlo = reinterpret_cast<int*>(p);     p += dx_up256((size_t)cap * 4);
+    s.vlast = reinterpret_cast<float*>(p); p += dx_up256((size_t)cap * 4);
     s.vdata = reinterpret_cast<float*>(p);
     return s;
 }
@@ -143,8 +146,8 @@ __device__ __forceinline__ void dx_parent_get(const DxSlot& S, int par, const fl
             ptotal = lg_add(dx_neg_inf(), pgap, mode);
         }
     } else if (at >= par_off && at < par_end) {
-        pgap = pv[W + pslot];
-        ptotal = pv[2 * W + pslot];
+        pgap = pv[pslot];
+        ptotal = pv[W + pslot];
     }
 }
 __device__ __forceinline__ int dx_mod(int i, int W) {  // i mod W for i >= -1
@@ -166,7 +169,7 @@ __device__ __forceinline__ DxCell dx_step(const DxCell& last, float pgap, float 
 // (state * n_base) % n_state + label, and there is no repeat case.  Network-2 values are mapped to
 // log space on the fly there (a [T2, S, C] log table per pair would not fit the scratch).
 template <bool CRF>
-__global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexParams p, const DuplexLayout L) {
+__global__ void __launch_bounds__(DX_THREADS, 6) duplex_search_kernel(const DuplexParams p, const DuplexLayout L) {
     extern __shared__ __align__(16) unsigned char smem[];
     double* s_invc = reinterpret_cast<double*>(smem);
     double* s_logc = s_invc + 16;
@@ -327,7 +330,7 @@ __global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexP
                 if (active) {
                     my_par = bv.par[lane];
                     my_lab = bv.tip[lane];
-                    vd = S.vdata + (size_t)node * 3 * W;
+                    vd = S.vdata + (size_t)node * 2 * W;
                     int off = S.voff[node];
                     v_end = S.vend[node];
                     mx = S.vmx[node];
@@ -348,7 +351,7 @@ __global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexP
                         if (!rescan) {
                             int sl = dx_mod(old_lo, W);
                             for (int i = old_lo; i < b0; ++i) {
-                                if (vd[2 * W + sl] >= mx) rescan = true;
+                                if (vd[W + sl] >= mx) rescan = true;
                                 if (++sl == W) sl = 0;
                             }
                         }
@@ -356,7 +359,7 @@ __global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexP
                             mx = NEG;
                             int sl = dx_mod(b0, W);
                             for (int i = b0; i < e0; ++i) {
-                                mx = lg_max(mx, vd[2 * W + sl]);
+                                mx = lg_max(mx, vd[W + sl]);
                                 if (++sl == W) sl = 0;
                             }
                         }
@@ -365,7 +368,7 @@ __global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexP
                     }
                     if (v_end > off) {
                         const int sl = dx_mod(v_end - 1, W);
-                        last.label = vd[sl]; last.gap = vd[W + sl]; last.total = vd[2 * W + sl];
+                        last.label = S.vlast[node]; last.gap = vd[sl]; last.total = vd[W + sl];
                     }
                     // the parent's label decides the repeat case, independent of collapse (:511)
                     const int plab = (my_par >= 0) ? int(S.nlab[my_par]) : -1;
@@ -376,7 +379,7 @@ __global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexP
                 }
                 __syncwarp();  // every node's new offset is visible before children read their parents
                 const int par_off = (active && my_par >= 0) ? S.voff[my_par] : 0;
-                const float* pv = (active && my_par >= 0) ? S.vdata + (size_t)my_par * 3 * W : nullptr;
+                const float* pv = (active && my_par >= 0) ? S.vdata + (size_t)my_par * 2 * W : nullptr;
                 int imin = active ? v_end : hi;
 #pragma unroll
                 for (int d = 16; d > 0; d >>= 1) {
@@ -391,7 +394,7 @@ __global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexP
                         dx_parent_get(S, my_par, pv, i - 1, sl_p, root_len, par_off, (my_par >= 0 && par_end == hi) ? i : par_end, W,
                                       mode, pgap, ptot);
                         const DxCell c = dx_step(last, pgap, ptot, lp2(i, my_state, 0), lp2(i, my_state, my_lab + 1), repeat, mode);
-                        vd[sl_w] = c.label; vd[W + sl_w] = c.gap; vd[2 * W + sl_w] = c.total;
+                        vd[sl_w] = c.gap; vd[W + sl_w] = c.total;
                         mx = lg_max(mx, c.total);
                         last = c;
                     }
@@ -400,6 +403,7 @@ __global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexP
                     __syncwarp();
                 }
                 if (active) {
+                    S.vlast[node] = last.label;
                     S.vend[node] = hi;
                     S.vmx[node] = mx;
                 }
@@ -520,8 +524,8 @@ __global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexP
                     const bool repeat = collapse && l == bv.tip[b];
                     const int par_end = (pnode >= 0) ? S.vend[pnode] : 0;
                     const int par_off = (pnode >= 0) ? S.voff[pnode] : 0;
-                    const float* pv = (pnode >= 0) ? S.vdata + (size_t)pnode * 3 * W : nullptr;
-                    float* vd = S.vdata + (size_t)id * 3 * W;
+                    const float* pv = (pnode >= 0) ? S.vdata + (size_t)pnode * 2 * W : nullptr;
+                    float* vd = S.vdata + (size_t)id * 2 * W;
                     DxCell last{NEG, NEG, NEG};
                     float mx = NEG;
                     int sl = dx_mod(lo, W), sl_p = dx_mod(lo - 1, W);
@@ -530,7 +534,7 @@ __global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexP
                         dx_parent_get(S, pnode, pv, i - 1, sl_p, root_len, par_off, par_end, W, mode, pgap, ptot);
                         if (++sl_p == W) sl_p = 0;
                         const DxCell c = dx_step(last, pgap, ptot, lp2(i, tstate, 0), lp2(i, tstate, l + 1), repeat, mode);
-                        vd[sl] = c.label; vd[W + sl] = c.gap; vd[2 * W + sl] = c.total;
+                        vd[sl] = c.gap; vd[W + sl] = c.total;
                         mx = lg_max(mx, c.total);
                         last = c;
                         if (++sl == W) sl = 0;
@@ -539,6 +543,7 @@ __global__ void __launch_bounds__(DX_THREADS) duplex_search_kernel(const DuplexP
                     S.nlab[id] = uint8_t(l);
                     S.voff[id] = lo;
                     S.vlo[id] = lo;
+                    S.vlast[id] = last.label;
                     S.vend[id] = hi;
                     S.vmx[id] = mx;
                     for (int q = 0; q < NL; ++q) S.child[(size_t)id * NL + q] = -1;
@@ -693,7 +698,9 @@ int64_t duplex_scratch_bytes(int sm_count, int64_t N, int T1, int T2, int C, int
     if (nodes_per_row > bound) nodes_per_row = int(bound > 0 ? bound : 1);
     const long long cap = (long long)nodes_per_row * (T1 > 0 ? T1 : 1);
     const long long per_slot = (long long)dx_slot_bytes(cap, T2, C, W);
-    long long slots = (long long)sm_count * 16;
+    int per_sm = 24;  // latency-bound, sequential per pair: throughput follows the resident warps
+    if (const char* e = getenv("FCTC_DUPLEX_WARPS_PER_SM")) per_sm = atoi(e) > 0 ? atoi(e) : per_sm;  // tuning knob
+    long long slots = (long long)sm_count * per_sm;
     if (slots > N) slots = N;
     if (slots < 1) slots = 1;
     slots = (slots + DX_WARPS - 1) / DX_WARPS * DX_WARPS;
@@ -758,8 +765,9 @@ extern "C" int64_t fctc_duplex_scratch_bytes(const fctc_handle* h, int64_t n_pai
                                              int32_t nodes_per_row) {
     if (!h || n_labels <= 0 || beam_size <= 0 || n_rows_1 <= 0 || n_rows_2 < 0) return 0;
     const int W = int((max_window > 0 && max_window < n_rows_2 ? max_window : n_rows_2) + 1);
+    // recommended: a pool per resident warp, capped at 96 GiB (smaller buffers run fewer pairs in flight)
     return fctc::duplex_scratch_bytes(fctc::handle_sm_count(h), n_pairs, int(n_rows_1), int(n_rows_2), n_labels, beam_size, W,
-                                      nodes_per_row, 0, nullptr, nullptr);
+                                      nodes_per_row, int64_t(96) << 30, nullptr, nullptr);
 }
 
 extern "C" int fctc_beam_search_duplex_batch_device(fctc_handle* h, const float* post1_dev, const float* post2_dev,
