@@ -24,6 +24,8 @@
 //     MUFU.LG2 fast path whose result is only trusted when it is provably on the same side of
 //     every rounding boundary as glibc's log10f, else the exact binary64 re-evaluation of glibc's
 //     algorithm (phred.cuh) decides.
+#include <cstdlib>
+
 #include "device_utils.cuh"
 #include "kernels.h"
 #include "phred.cuh"
@@ -36,6 +38,9 @@ constexpr unsigned FULLMASK = 0xffffffffu;
 constexpr int VW_WARPS = 4;  // warps per CTA of the streaming kernel
 constexpr int VW_THREADS = VW_WARPS * 32;
 constexpr int VW_MAX_STAGES = 8;
+#ifndef VW_MINBLOCKS
+#define VW_MINBLOCKS 6
+#endif
 constexpr int VT_SMEM_LIMIT = 227 * 1024;
 
 __constant__ double c_logf_invc[16] = FCTC_LOGF_INVC;
@@ -134,7 +139,7 @@ __device__ __forceinline__ P* keep_in_register(P* ptr) {  // stops the compiler 
 // Streaming kernel: one warp per read, RPL rows per lane and tile.
 // ------------------------------------------------------------------------------------------
 template <typename QT, int RPL, bool COLLAPSE, bool QSTRING>
-__global__ void __launch_bounds__(VW_THREADS, 6) viterbi_stream_kernel(const ViterbiParams p, const WarpLayout L) {
+__global__ void __launch_bounds__(VW_THREADS, VW_MINBLOCKS) viterbi_stream_kernel(const ViterbiParams p, const WarpLayout L) {
     constexpr int TILE = 32 * RPL;
     extern __shared__ __align__(128) unsigned char smem[];
     double* s_invc = reinterpret_cast<double*>(smem);
@@ -538,6 +543,7 @@ static bool plan_stream(const ViterbiParams& p, WarpLayout* L) {
     if (stage > 16 * 1024) return false;
     // enough bytes in flight per warp to cover HBM latency at ~16-20 resident warps per SM
     int ns = int((8 * 1024) / stage);
+    if (const char* e = getenv("FCTC_VIT_STAGES")) ns = atoi(e) > 0 ? atoi(e) : ns;  // tuning knob
     if (ns > VW_MAX_STAGES) ns = VW_MAX_STAGES;
     if (ns < 2) ns = 2;
     L->nstage = ns;

@@ -11,7 +11,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "libfctc_b200.so")
+LIB_PATH = os.environ.get("FCTC_LIB") or os.path.join(os.path.dirname(_HERE), "libfctc_b200.so")
 
 OK, RAN_OUT_OF_BEAM, INCOMPARABLE_VALUES, INVALID_ENVELOPE, NODE_POOL_OVERFLOW, OUTPUT_OVERFLOW, INVALID_QUALITY_CHAR, \
     REFERENCE_PANIC = range(8)
