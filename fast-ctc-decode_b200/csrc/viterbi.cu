@@ -38,8 +38,15 @@ constexpr unsigned FULLMASK = 0xffffffffu;
 constexpr int VW_WARPS = 4;  // warps per CTA of the streaming kernel
 constexpr int VW_THREADS = VW_WARPS * 32;
 constexpr int VW_MAX_STAGES = 8;
-#ifndef VW_MINBLOCKS
-#define VW_MINBLOCKS 6
+// Resident CTAs per SM the compiler must allow (register budget) and bytes of posteriors each warp
+// keeps in flight.  Measured on B200 (65,536 reads x 4000 x 5): with quality strings the kernel is
+// issue-bound and wants more warps (6 CTAs, 3 stages); without, it is HBM-bound and runs best with
+// fewer, fatter warps (4 CTAs, 4 stages: 0.95 of the measured copy bandwidth).
+#ifndef VW_MINBLOCKS_Q
+#define VW_MINBLOCKS_Q 6
+#endif
+#ifndef VW_MINBLOCKS_NOQ
+#define VW_MINBLOCKS_NOQ 4
 #endif
 constexpr int VT_SMEM_LIMIT = 227 * 1024;
 
@@ -102,31 +109,28 @@ struct WarpLayout {  // shared memory plan of the streaming kernel (bytes)
     int nstage;
     int stage_bytes;
     int off_stage;   // from the warp's base
-    int off_rec;     // (TILE + 1) x {float winning probability, int label} per row + a sentinel
-    int off_orow;    // TILE bytes: tile-local row of the tile's j-th emission
-    int off_open;    // 3 words: the run left open at the end of a tile {sum, count, output index}
+    int off_queue;   // (TILE + 1) x {float run sum, int run length}: slot 0 = run carried in, slot s = s-th emission
+    int off_open;    // {sum, length} of the run left open at the end of the previous tile
     int warp_bytes;
     int cta_fixed;   // log tables at the start of the CTA's shared memory
 };
 
 // Explicit shared-space accesses on 32-bit addresses (keeps address arithmetic 32-bit and lets
 // the hot loops skip generic->shared window conversions).
-__device__ __forceinline__ void sts_rec2(uint32_t addr, float p0, int l0, float p1, int l1) {
-    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(p0), "r"(l0), "f"(p1), "r"(l1) : "memory");
+__device__ __forceinline__ void sts_run(uint32_t addr, float sum, int n) {
+    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(addr), "f"(sum), "r"(n) : "memory");
 }
-__device__ __forceinline__ void sts_rec1(uint32_t addr, float p0, int l0) {
-    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(addr), "f"(p0), "r"(l0) : "memory");
+__device__ __forceinline__ void lds_run(uint32_t addr, float& sum, int& n) {
+    asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=f"(sum), "=r"(n) : "r"(addr) : "memory");
 }
-__device__ __forceinline__ void lds_rec(uint32_t addr, float& prob, int& label) {
-    asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=f"(prob), "=r"(label) : "r"(addr) : "memory");
+
+__device__ __forceinline__ void lds_f4(uint32_t addr, float* f) {
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(f[0]), "=f"(f[1]), "=f"(f[2]), "=f"(f[3]) : "r"(addr) : "memory");
 }
-__device__ __forceinline__ int lds_u8(uint32_t addr) {
-    int v;
-    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+__device__ __forceinline__ float lds_f1(uint32_t addr) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
     return v;
-}
-__device__ __forceinline__ void sts_u8(uint32_t addr, int v) {
-    asm volatile("st.shared.u8 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
 }
 
 template <typename P>
@@ -138,24 +142,28 @@ __device__ __forceinline__ P* keep_in_register(P* ptr) {  // stops the compiler 
 // ------------------------------------------------------------------------------------------
 // Streaming kernel: one warp per read, RPL rows per lane and tile.
 // ------------------------------------------------------------------------------------------
-template <typename QT, int RPL, bool COLLAPSE, bool QSTRING>
-__global__ void __launch_bounds__(VW_THREADS, VW_MINBLOCKS) viterbi_stream_kernel(const ViterbiParams p, const WarpLayout L) {
+// FAST5: five labels, RPL == 4 and every tile 16-byte aligned (the nanopore case), so that all the
+// tile geometry is a compile-time constant.
+template <typename QT, int RPL, bool COLLAPSE, bool QSTRING, bool FAST5>
+__global__ void __launch_bounds__(VW_THREADS, QSTRING ? VW_MINBLOCKS_Q : VW_MINBLOCKS_NOQ) viterbi_stream_kernel(const ViterbiParams p, const WarpLayout L) {
+    static_assert(!FAST5 || RPL == 4, "the five-label fast path is written for four rows per lane");
     constexpr int TILE = 32 * RPL;
     extern __shared__ __align__(128) unsigned char smem[];
     double* s_invc = reinterpret_cast<double*>(smem);
     double* s_logc = s_invc + 16;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(FULLMASK, threadIdx.x >> 5, 0);  // tells the compiler it is warp-uniform
     unsigned char* ws = smem + L.cta_fixed + (size_t)warp * L.warp_bytes;
-    uint64_t* full = reinterpret_cast<uint64_t*>(ws);
-    unsigned char* stage0 = ws + L.off_stage;
-    const uint32_t rec_base = smem_u32(ws + L.off_rec);
-    const uint32_t orow_base = smem_u32(ws + L.off_orow);
-    float* s_open = reinterpret_cast<float*>(ws + L.off_open);
+    const uint32_t bar0 = smem_u32(ws);  // nstage mbarriers, then the stages (all addressed in the shared window)
+    const uint32_t stage0 = smem_u32(ws + L.off_stage);
+    const uint32_t q_base = smem_u32(ws + L.off_queue);
+    const uint32_t open_addr = smem_u32(ws + L.off_open);
     const QualityParams qp = make_quality_params(p.qscale, p.qbias);
 
-    const int C = p.C;
+    const int C = FAST5 ? 5 : p.C;
     const int T = int(p.T);
     const int ntiles = (T + TILE - 1) / TILE;
+    const int last_rows = T - (ntiles - 1) * TILE;
     const long long gw = (long long)blockIdx.x * VW_WARPS + warp;
     const long long nwarps = (long long)gridDim.x * VW_WARPS;
     const int my_reads = int((p.N > gw) ? (p.N - gw + nwarps - 1) / nwarps : 0);
@@ -165,41 +173,36 @@ __global__ void __launch_bounds__(VW_THREADS, VW_MINBLOCKS) viterbi_stream_kerne
     const long long safe_elems = safe_bytes >> 2;
     const long long stride = p.slot_stride;
     // every tile of every read starts 16-byte aligned and lies inside the bulk-copy-safe range
-    const bool aligned = ((read_elems & 3) == 0) && (((TILE * C) & 3) == 0);
-    const bool aligned5 = (RPL == 4) && (C == 5) && aligned;
+    const bool aligned = FAST5 || (((read_elems & 3) == 0) && (((TILE * C) & 3) == 0));
     const int nstage = L.nstage;
     const int stage_bytes = L.stage_bytes;
     const int tile_elems = TILE * C;
+    const int last_elems = last_rows * C;
+    const long long skip_elems = (nwarps - 1) * read_elems;  // from the end of one of my reads to my next one
 
-    // producer state (advanced by every lane so that it stays warp-uniform; lane 0 issues)
-    long long p_left = (long long)my_reads * ntiles;  // tiles not yet issued
-    long long p_n = gw;                               // read of the next tile to issue
-    int p_ti = 0;
-    long long p_e0 = gw * read_elems;  // its first element
-    int p_s = 0;
-    auto issue_next = [&]() {
-        if (p_left <= 0) return;
-        const int rows = (T - p_ti * TILE < TILE) ? (T - p_ti * TILE) : TILE;
+    // Producer state, advanced by every lane so that it stays warp-uniform; lane 0 issues.  The
+    // stage it fills is always the one the consumer has just released, so both share one ring position.
+    int p_reads = my_reads;            // reads not yet completely issued
+    int p_tl = ntiles;                 // tiles left in the read being issued
+    long long p_e0 = gw * read_elems;  // first element of the next tile to issue
+    auto issue_next = [&](uint32_t bar, uint32_t stage) {
+        if (p_reads <= 0) return;
+        const int elems = (p_tl == 1) ? last_elems : tile_elems;
         if (lane == 0) {
-            long long b0;
-            uint32_t bytes;
-            if (aligned) {
-                b0 = p_e0 * 4;
-                bytes = uint32_t(rows * C * 4);
-            } else {
-                const long long e1 = p_e0 + (long long)rows * C;
-                b0 = (p_e0 * 4) & ~15LL;
+            long long b0 = p_e0 * 4;
+            uint32_t bytes = uint32_t(elems) * 4u;
+            if (!aligned) {
+                const long long e1 = p_e0 + elems;
+                b0 &= ~15LL;
                 long long b1 = (e1 * 4 + 15) & ~15LL;
                 if (b1 > safe_bytes) b1 = safe_bytes;
                 bytes = b1 > b0 ? uint32_t(b1 - b0) : 0u;
             }
-            mbar_expect_tx(&full[p_s], bytes);
-            if (bytes) bulk_g2s(stage0 + p_s * stage_bytes, reinterpret_cast<const char*>(p.post) + b0, bytes, &full[p_s]);
+            mbar_expect_tx_a(bar, bytes);
+            if (FAST5 || bytes) bulk_g2s_a(stage, reinterpret_cast<const char*>(p.post) + b0, bytes, bar);
         }
-        --p_left;
-        if (++p_s == nstage) p_s = 0;
-        if (++p_ti == ntiles) { p_ti = 0; p_n += nwarps; p_e0 = p_n * read_elems; }
-        else p_e0 += tile_elems;
+        p_e0 += elems;
+        if (--p_tl == 0) { p_tl = ntiles; p_e0 += skip_elems; --p_reads; }
     };
 
     if (threadIdx.x < 16) {
@@ -207,47 +210,46 @@ __global__ void __launch_bounds__(VW_THREADS, VW_MINBLOCKS) viterbi_stream_kerne
         s_logc[threadIdx.x] = c_logf_logc[threadIdx.x];
     }
     if (lane == 0) {
-        for (int s = 0; s < nstage; ++s) mbar_init(&full[s], 1);
+        for (int s = 0; s < nstage; ++s) mbar_init_a(bar0 + 8 * s, 1);
         mbar_init_fence();
-        sts_rec1(rec_base + 8 * TILE, 0.0f, -3);  // sentinel row: ends every run walk at the tile edge
     }
     __syncthreads();  // the only block-level barrier: tables + barrier inits visible
-    for (int s = 0; s < nstage; ++s) issue_next();
+    for (int s = 0; s < nstage; ++s) issue_next(bar0 + 8 * s, stage0 + s * stage_bytes);
 
-    int c_s = 0;  // consumer ring position
-    uint32_t c_phase = 0;
+    int r_s = 0;  // ring position
+    uint32_t r_bar = bar0, r_stage = stage0, r_phase = 0;
     const int r_base = RPL * lane;
     for (int k = 0; k < my_reads; ++k) {
         const long long n = gw + (long long)k * nwarps;
         uint8_t* const out_lab = keep_in_register(p.labels + n * stride);
         QT* const out_qual = keep_in_register(reinterpret_cast<QT*>(p.quals) + n * stride);
         int* const out_path = keep_in_register(p.path + n * stride);
-        long long e0 = n * read_elems;
         int out_count = 0;
+        bool open_in = false;  // the previous tile ended inside a non-blank run (warp-uniform)
         int last_label = -1;  // None, src/search.rs:337
-        bool open_active = false;  // a run that reached the end of the previous tile (warp-uniform)
-        float open_sum = 0.0f;
-        int open_n = 0, open_idx = 0;
         bool bad_char = false;
 
-        for (int ti = 0; ti < ntiles; ++ti, e0 += tile_elems) {
-            const int row0 = ti * TILE;
-            const int rows = (T - row0 < TILE) ? (T - row0) : TILE;
+        for (int ti = 0, row0 = 0; ti < ntiles; ++ti, row0 += TILE) {
             const bool last_tile = (ti == ntiles - 1);
-            const unsigned char* stage = stage0 + c_s * stage_bytes;
-            mbar_wait(&full[c_s], c_phase);
+            const int rows = last_tile ? last_rows : TILE;
+            mbar_wait_a(r_bar, r_phase);
 
             float pr[RPL];
             int lab[RPL];
-            if (aligned5 && rows == TILE) {
-                const float4* s4 = reinterpret_cast<const float4*>(stage) + 5 * lane;
-                const float4 a = s4[0], b = s4[1], c = s4[2], d = s4[3], e = s4[4];
-                const float f[20] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, c.x, c.y,
-                                     c.z, c.w, d.x, d.y, d.z, d.w, e.x, e.y, e.z, e.w};
+            if (FAST5) {
+                float f[20];
+#pragma unroll
+                for (int v = 0; v < 5; ++v) lds_f4(r_stage + 80 * lane + 16 * v, f + 4 * v);
 #pragma unroll
                 for (int r = 0; r < RPL; ++r) argmax_row5(f + 5 * (r & 3), lab[r], pr[r]);
+                if (rows != TILE) {  // rows past the end of the read (stale stage contents) count as blank
+#pragma unroll
+                    for (int r = 0; r < RPL; ++r)
+                        if (r_base + r >= rows) { lab[r] = 0; pr[r] = 0.0f; }
+                }
             } else {
-                const float* stagef = reinterpret_cast<const float*>(stage) + int(e0 & 3);
+                const long long e0 = n * read_elems + (long long)ti * tile_elems;
+                const uint32_t stagef = r_stage + 4u * uint32_t(e0 & 3);
 #pragma unroll
                 for (int r = 0; r < RPL; ++r) {
                     const int row = r_base + r;
@@ -255,7 +257,7 @@ __global__ void __launch_bounds__(VW_THREADS, VW_MINBLOCKS) viterbi_stream_kerne
                     float best = 0.0f;
                     if (row < rows) {
                         const int le = row * C;
-                        auto ld = [&](int i) { return (e0 + i < safe_elems) ? stagef[i] : p.post[e0 + i]; };
+                        auto ld = [&](int i) { return (e0 + i < safe_elems) ? lds_f1(stagef + 4u * uint32_t(i)) : p.post[e0 + i]; };
                         best = ld(le);
                         for (int c = 1; c < C; ++c) {
                             const float v = ld(le + c);
@@ -266,30 +268,25 @@ __global__ void __launch_bounds__(VW_THREADS, VW_MINBLOCKS) viterbi_stream_kerne
                     lab[r] = arg;  // rows past the end of the read count as blank
                 }
             }
-            if (QSTRING) {
-                if (RPL % 2 == 0) {
-#pragma unroll
-                    for (int r = 0; r < RPL; r += 2)
-                        sts_rec2(rec_base + 8 * (r_base + r), pr[r], lab[r], pr[(r + 1) % RPL], lab[(r + 1) % RPL]);
-                } else {
-#pragma unroll
-                    for (int r = 0; r < RPL; ++r) sts_rec1(rec_base + 8 * (r_base + r), pr[r], lab[r]);
-                }
-            }
-            __syncwarp();  // stage c_s fully consumed; per-row arrays visible
-            issue_next();  // refill the stage just freed (it is the producer's next slot by construction)
-            if (++c_s == nstage) { c_s = 0; c_phase ^= 1u; }
+            __syncwarp();  // stage fully consumed (and the previous tile's queue reads are over)
+            issue_next(r_bar, r_stage);  // refill the stage just freed
+            r_bar += 8;
+            r_stage += stage_bytes;
+            if (++r_s == nstage) { r_s = 0; r_bar = bar0; r_stage = stage0; r_phase ^= 1u; }
 
             // emission flags (src/search.rs:347) and output positions
-            int prev = __shfl_up_sync(FULLMASK, lab[RPL - 1], 1);
-            if (lane == 0) prev = last_label;
+            int prev0 = __shfl_up_sync(FULLMASK, lab[RPL - 1], 1);
+            if (lane == 0) prev0 = last_label;
             bool em[RPL];
             int cnt = 0;
+            {
+                int prev = prev0;
 #pragma unroll
-            for (int r = 0; r < RPL; ++r) {
-                em[r] = lab[r] != 0 && (!COLLAPSE || lab[r] != prev);
-                prev = lab[r];
-                cnt += em[r] ? 1 : 0;
+                for (int r = 0; r < RPL; ++r) {
+                    em[r] = lab[r] != 0 && (!COLLAPSE || lab[r] != prev);
+                    prev = lab[r];
+                    cnt += em[r] ? 1 : 0;
+                }
             }
             const int incl = warp_inclusive_scan(cnt, lane);
             const int tile_total = __shfl_sync(FULLMASK, incl, 31);
@@ -303,67 +300,96 @@ __global__ void __launch_bounds__(VW_THREADS, VW_MINBLOCKS) viterbi_stream_kerne
                     if (em[r]) {
                         out_lab[out_count + li] = uint8_t(lab[r]);
                         out_path[out_count + li] = row0 + r_base + r;
-                        if (QSTRING) sts_u8(orow_base + li, r_base + r);
                     }
                     li += em[r] ? 1 : 0;
                 }
             }
+            const int new_last = COLLAPSE ? __shfl_sync(FULLMASK, lab[RPL - 1], 31) : -1;
 
             if (QSTRING) {
-                __syncwarp();
-                // Dense phase: lane j owns the tile's j-th emission (plus, as item `tile_total`, the run
-                // carried in from the previous tile): sum its run in row order, then either close it
-                // (quality character, coalesced byte stores) or hand it on as the open run.
-                const int n_items = tile_total + (open_active ? 1 : 0);
-                bool my_open = false;
-                for (int j = lane; j < n_items; j += 32) {
-                    int r2, nn, gidx, label;
-                    float sum;
-                    if (COLLAPSE && j == tile_total) {
-                        r2 = 0; nn = open_n; sum = open_sum; label = last_label; gidx = open_idx;
-                    } else {
-                        const int row = lds_u8(orow_base + j);
-                        float pv;
-                        lds_rec(rec_base + 8 * row, pv, label);
-                        sum = __fadd_rn(0.0f, pv);  // label_prob_total starts at 0.0 (src/search.rs:339,354)
-                        nn = 1;
-                        r2 = row + 1;
-                        gidx = out_count + j;
+                // Run sums, always in row order (src/search.rs:362-365).  S[r] = sum of the run that
+                // starts at this lane's row r over the lane's own rows; a run that reaches the lane's
+                // last row is finished by the NEXT lane (which adds its leading rows that continue it,
+                // possibly none) and lands in the queue slot of its emission: slot s (1-based) holds the
+                // tile's s-th emission, slot 0 the run left open by the previous tile.
+                float S[RPL];
+                int nr[RPL];
+                bool reach[RPL];
+#pragma unroll
+                for (int r = 0; r < RPL; ++r) {
+                    S[r] = __fadd_rn(0.0f, pr[r]);  // label_prob_total starts at 0.0 (src/search.rs:339,354)
+                    nr[r] = 1;
+                    bool alive = COLLAPSE;
+#pragma unroll
+                    for (int k = r + 1; k < RPL; ++k) {
+                        alive = alive && (lab[k] == lab[k - 1]);
+                        if (alive) { S[r] = __fadd_rn(S[r], pr[k]); nr[r] = k - r + 1; }
                     }
-                    bool open = false;
-                    if (COLLAPSE) {  // without collapse every non-blank row is its own run
-                        for (;;) {   // the sentinel at row TILE (and blank padding rows) stop the walk
-                            float p2;
-                            int l2;
-                            lds_rec(rec_base + 8 * r2, p2, l2);
-                            if (l2 != label) break;
-                            sum = __fadd_rn(sum, p2);
-                            ++nn;
-                            ++r2;
-                        }
-                        open = (r2 == TILE) && !last_tile;
-                    }
-                    if (open) {
-                        my_open = true;
-                        s_open[0] = sum;
-                        s_open[1] = __int_as_float(nn);
-                        s_open[2] = __int_as_float(gidx);
-                    } else {
-                        out_qual[gidx] = quality_char<QT>(sum, nn, qp, s_invc, s_logc, bad_char);
+                    reach[r] = alive;  // without collapse every non-blank row is a finished run of its own
+                }
+                {
+                    uint32_t slot = q_base + 8 * (li0 + 1);
+#pragma unroll
+                    for (int r = 0; r < RPL; ++r) {
+                        if (em[r] && !reach[r]) sts_run(slot, S[r], nr[r]);
+                        if (em[r]) slot += 8;
                     }
                 }
+                bool open_out = false;
                 if (COLLAPSE) {
-                    open_active = __any_sync(FULLMASK, my_open);  // at most one item touches the tile end
-                    if (open_active) {
-                        __syncwarp();  // orders the owner lane's s_open stores before these loads
-                        open_sum = s_open[0];
-                        open_n = __float_as_int(s_open[1]);
-                        open_idx = __float_as_int(s_open[2]);
+                    const bool c0 = lab[0] == prev0;
+                    float tS = S[RPL - 1];  // the run holding the lane's last row, from its first row in this lane
+                    int tn = 1;
+#pragma unroll
+                    for (int r = RPL - 2; r >= 0; --r)
+                        if (reach[r]) { tS = S[r]; tn = nr[r]; }
+                    const bool whole = c0 && reach[0];  // every row continues the run carried in
+                    if (whole && prev0 != 0) tn = -1;   // its tail is unknown until the carry arrives
+                    float o_S = 0.0f;
+                    int o_n = 0;
+                    if (lane == 0) lds_run(open_addr, o_S, o_n);
+                    float in_S;
+                    int in_n;
+                    for (;;) {
+                        in_S = __shfl_up_sync(FULLMASK, tS, 1);
+                        in_n = __shfl_up_sync(FULLMASK, tn, 1);
+                        if (lane == 0) { in_S = o_S; in_n = o_n; }
+                        if (tn == -1 && in_n != -1) {
+                            tS = in_S;
+#pragma unroll
+                            for (int r = 0; r < RPL; ++r) tS = __fadd_rn(tS, pr[r]);
+                            tn = in_n + RPL;
+                        }
+                        if (!__any_sync(FULLMASK, in_n == -1)) break;
                     }
+                    if (!whole && prev0 > 0) {  // finish the run carried in: it is the emission before this lane's first
+                        float hs = in_S;
+                        int hn = in_n;
+                        bool alive = c0;
+#pragma unroll
+                        for (int r = 0; r + 1 < RPL; ++r) {
+                            if (alive) { hs = __fadd_rn(hs, pr[r]); ++hn; }
+                            alive = alive && (lab[r + 1] == lab[r]);
+                        }
+                        sts_run(q_base + 8 * li0, hs, hn);
+                    }
+                    open_out = new_last != 0 && !last_tile;
+                    if (lane == 31 && new_last != 0)  // the tile's last run: closed at the end of the read
+                        sts_run(last_tile ? q_base + 8 * tile_total : open_addr, tS, tn);  // (src/search.rs:367-373)
+                } else {
+                    (void)prev0;
                 }
-                __syncwarp();  // dense reads done before the next tile rewrites the per-row arrays
+                __syncwarp();  // queue complete
+                const int hi = tile_total + (open_out ? 0 : 1);
+                for (int j = (open_in ? 0 : 1) + lane; j < hi; j += 32) {
+                    float sum;
+                    int nn;
+                    lds_run(q_base + 8 * j, sum, nn);
+                    out_qual[out_count + j - 1] = quality_char<QT>(sum, nn, qp, s_invc, s_logc, bad_char);
+                }
+                open_in = open_out;
             }
-            if (COLLAPSE) last_label = __shfl_sync(FULLMASK, lab[RPL - 1], 31);
+            if (COLLAPSE) last_label = new_last;
             out_count += tile_total;
         }
         if (sizeof(QT) == 4) bad_char = __any_sync(FULLMASK, bad_char);
@@ -541,25 +567,24 @@ static bool plan_stream(const ViterbiParams& p, WarpLayout* L) {
     const long long rows = p.T < TILE ? p.T : TILE;
     const long long stage = ((rows * p.C * 4 + 15) & ~15LL) + 32;
     if (stage > 16 * 1024) return false;
-    // enough bytes in flight per warp to cover HBM latency at ~16-20 resident warps per SM
-    int ns = int((8 * 1024) / stage);
+    // enough bytes in flight per warp to cover HBM latency at the variant's resident warps per SM
+    int ns = int(((p.qstring ? 8 : 11) * 1024) / stage);
     if (const char* e = getenv("FCTC_VIT_STAGES")) ns = atoi(e) > 0 ? atoi(e) : ns;  // tuning knob
     if (ns > VW_MAX_STAGES) ns = VW_MAX_STAGES;
     if (ns < 2) ns = 2;
     L->nstage = ns;
     L->stage_bytes = int(stage);
     L->off_stage = 64;
-    L->off_rec = int(L->off_stage + ns * stage);
-    L->off_orow = L->off_rec + (TILE + 2) * 8;
-    L->off_open = L->off_orow + ((TILE + 15) & ~15);
+    L->off_queue = int(L->off_stage + ns * stage);
+    L->off_open = L->off_queue + (TILE + 1) * 8;
     L->warp_bytes = (L->off_open + 16 + 127) & ~127;
     L->cta_fixed = 256;
     return L->cta_fixed + VW_WARPS * L->warp_bytes <= VT_SMEM_LIMIT;
 }
 
-template <typename QT, int RPL, bool COLLAPSE, bool QSTRING>
+template <typename QT, int RPL, bool COLLAPSE, bool QSTRING, bool FAST5>
 static cudaError_t launch_stream(const ViterbiParams& p, const WarpLayout& L, int sm_count, cudaStream_t stream) {
-    auto kernel = viterbi_stream_kernel<QT, RPL, COLLAPSE, QSTRING>;
+    auto kernel = viterbi_stream_kernel<QT, RPL, COLLAPSE, QSTRING, FAST5>;
     const int smem = L.cta_fixed + VW_WARPS * L.warp_bytes;
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
@@ -574,14 +599,14 @@ static cudaError_t launch_stream(const ViterbiParams& p, const WarpLayout& L, in
     return cudaGetLastError();
 }
 
-template <typename QT, int RPL>
+template <typename QT, int RPL, bool FAST5>
 static cudaError_t launch_stream_flags(const ViterbiParams& p, const WarpLayout& L, int sm_count, cudaStream_t stream) {
     if (p.collapse) {
-        return p.qstring ? launch_stream<QT, RPL, true, true>(p, L, sm_count, stream)
-                         : launch_stream<QT, RPL, true, false>(p, L, sm_count, stream);
+        return p.qstring ? launch_stream<QT, RPL, true, true, FAST5>(p, L, sm_count, stream)
+                         : launch_stream<QT, RPL, true, false, FAST5>(p, L, sm_count, stream);
     }
-    return p.qstring ? launch_stream<QT, RPL, false, true>(p, L, sm_count, stream)
-                     : launch_stream<QT, RPL, false, false>(p, L, sm_count, stream);
+    return p.qstring ? launch_stream<QT, RPL, false, true, FAST5>(p, L, sm_count, stream)
+                     : launch_stream<QT, RPL, false, false, FAST5>(p, L, sm_count, stream);
 }
 
 template <typename QT>
@@ -589,11 +614,13 @@ static cudaError_t launch_viterbi_t(const ViterbiParams& p, int sm_count, cudaSt
     WarpLayout L;
     if (p.C <= 16 && plan_stream<4>(p, &L)) {
         if (which) *which = 0;
-        return launch_stream_flags<QT, 4>(p, L, sm_count, stream);
+        const bool fast5 = p.C == 5 && ((p.T * 5) & 3) == 0;  // every read (hence every tile) starts 16-byte aligned
+        return fast5 ? launch_stream_flags<QT, 4, true>(p, L, sm_count, stream)
+                     : launch_stream_flags<QT, 4, false>(p, L, sm_count, stream);
     }
     if (p.C <= 64 && plan_stream<1>(p, &L)) {
         if (which) *which = 0;
-        return launch_stream_flags<QT, 1>(p, L, sm_count, stream);
+        return launch_stream_flags<QT, 1, false>(p, L, sm_count, stream);
     }
     long long grid = (long long)sm_count * 8;
     if (grid > p.N) grid = p.N;
