@@ -86,7 +86,8 @@ __device__ __forceinline__ BeamView beam_view(unsigned char* base, int B) {
 template <bool CRF>
 __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParams p, const BeamLayout L) {
     extern __shared__ __align__(16) unsigned char smem[];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);  // tells the compiler it is warp-uniform
     const int slot = blockIdx.x * BM_WARPS + warp;
     if (slot >= p.n_slots) return;
     unsigned char* ws = smem + (size_t)warp * L.warp_bytes;

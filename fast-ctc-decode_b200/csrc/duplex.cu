@@ -173,7 +173,8 @@ __global__ void __launch_bounds__(DX_THREADS, 6) duplex_search_kernel(const Dupl
     extern __shared__ __align__(16) unsigned char smem[];
     double* s_invc = reinterpret_cast<double*>(smem);
     double* s_logc = s_invc + 16;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);  // tells the compiler it is warp-uniform
     if (threadIdx.x < 16) {
         s_invc[threadIdx.x] = c_dx_invc[threadIdx.x];
         s_logc[threadIdx.x] = c_dx_logc[threadIdx.x];
