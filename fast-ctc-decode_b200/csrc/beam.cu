@@ -49,7 +49,7 @@ __host__ __device__ inline size_t beam_slot_bytes(long long cap, int NL) {
 
 struct BeamLayout {  // per-warp shared memory plan, in bytes from the warp's base
     int beam_stride;  // one beam buffer: 6 arrays of B words
-    int off_newcnt, off_fold, off_key, off_node, off_lp, off_gp, off_src, off_sel, off_perm, off_skey, off_slo, off_rows, off_root;
+    int off_newcnt, off_fold, off_key, off_node, off_lp, off_gp, off_src, off_sel, off_srec, off_slo, off_rows, off_root;
     int warp_bytes;
     int rows_per_chunk;
 };
@@ -104,8 +104,8 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
     float* clp = reinterpret_cast<float*>(ws + L.off_lp);
     float* cgp = reinterpret_cast<float*>(ws + L.off_gp);
     int* sel = reinterpret_cast<int*>(ws + L.off_sel);
-    unsigned char* cperm = ws + L.off_perm;  // per-lane rank order of a hypothesis' C candidates
-    uint32_t* skey = reinterpret_cast<uint32_t*>(ws + L.off_skey);  // the same candidates' keys, in rank order
+    // per-lane ranked candidate lists: (C + 1) x {score key, candidate slot}, and the node-id tie keys
+    const uint32_t srec_base = smem_u32(ws + L.off_srec);
     uint32_t* slo = reinterpret_cast<uint32_t*>(ws + L.off_slo);
     float* rowbuf = reinterpret_cast<float*>(ws + L.off_rows);
     int* root_child = reinterpret_cast<int*>(ws + L.off_root);
@@ -334,45 +334,69 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
                 const int n_slots_c = nbeam * C;
                 const int n_keep = n_cand < B ? n_cand : B;
                 if (nbeam <= 32 && n_slots_c > 64) {
-                    // Lane b sorts its own hypothesis' C candidates once (tiny insertion sort on an index
-                    // permutation) and lays them out in rank order; then every rank costs one REDUX.MAX (two
-                    // on a score tie) and a head advance on the winning lane.
-                    unsigned char* perm = cperm + lane * C;
+                    // Lane b ranks its own hypothesis' C candidates once (pairwise counting, no data-dependent
+                    // moves) and lays them out in rank order as {score key, slot} records closed by a zero
+                    // sentinel; then every output rank costs one REDUX.MAX (two on a score tie, which reads
+                    // the node-id keys) and a head advance on the winning lane.
                     const int base = lane * C;
-                    auto better = [&](int a, int b2) {  // slot a ranks before slot b2
-                        const uint32_t ka = ckey[base + a], kb = ckey[base + b2];
-                        return ka > kb || (ka == kb && ka != 0u && cnode[base + a] < cnode[base + b2]);
-                    };
+                    const uint32_t list0 = srec_base + uint32_t(lane) * uint32_t(C + 1) * 8u;
                     if (lane < nbeam) {
-                        for (int j = 0; j < C; ++j) {
-                            int k = j - 1;
-                            while (k >= 0 && better(j, perm[k])) { perm[k + 1] = perm[k]; --k; }
-                            perm[k + 1] = (unsigned char)j;
+                        if (C == 5) {
+                            uint32_t hi[5], lo[5];
+                            int rank[5] = {0, 0, 0, 0, 0};
+#pragma unroll
+                            for (int j = 0; j < 5; ++j) {
+                                hi[j] = ckey[base + j];
+                                lo[j] = hi[j] ? 0x7FFFFFFFu - uint32_t(cnode[base + j]) : 0u;
+                            }
+#pragma unroll
+                            for (int x = 0; x < 5; ++x)
+#pragma unroll
+                                for (int y = x + 1; y < 5; ++y) {
+                                    const bool x_first = hi[x] > hi[y] || (hi[x] == hi[y] && lo[x] >= lo[y]);
+                                    rank[y] += x_first ? 1 : 0;
+                                    rank[x] += x_first ? 0 : 1;
+                                }
+#pragma unroll
+                            for (int j = 0; j < 5; ++j) {
+                                sts_v2(list0 + 8u * uint32_t(rank[j]), hi[j], uint32_t(base + j));
+                                slo[lane * (C + 1) + rank[j]] = lo[j];
+                            }
+                        } else {
+                            for (int j = 0; j < C; ++j) {
+                                const uint32_t hj = ckey[base + j];
+                                const uint32_t lj = hj ? 0x7FFFFFFFu - uint32_t(cnode[base + j]) : 0u;
+                                int rk = 0;
+                                for (int y = 0; y < C; ++y) {
+                                    if (y == j) continue;
+                                    const uint32_t hy = ckey[base + y];
+                                    const uint32_t ly = hy ? 0x7FFFFFFFu - uint32_t(cnode[base + y]) : 0u;
+                                    const bool y_first = hy > hj || (hy == hj && (ly > lj || (ly == lj && y < j)));
+                                    rk += y_first ? 1 : 0;
+                                }
+                                sts_v2(list0 + 8u * uint32_t(rk), hj, uint32_t(base + j));
+                                slo[lane * (C + 1) + rk] = lj;
+                            }
                         }
-                        for (int j = 0; j < C; ++j) {
-                            const int i = base + perm[j];
-                            const uint32_t k = ckey[i];
-                            skey[base + j] = k;
-                            slo[base + j] = k ? 0x7FFFFFFFu - uint32_t(cnode[i]) : 0u;
-                        }
+                        sts_v2(list0 + 8u * uint32_t(C), 0u, 0u);
+                        slo[lane * (C + 1) + C] = 0u;
                     }
-                    int head = base;
-                    const int tail = base + C;
-                    uint32_t cur_hi = (lane < nbeam) ? skey[head] : 0u;
-                    uint32_t cur_lo = (lane < nbeam) ? slo[head] : 0u;
+                    uint32_t head = list0;
+                    uint32_t cur_hi = 0u, cur_idx = 0u;
+                    if (lane < nbeam) lds_v2(head, cur_hi, cur_idx);
                     for (int r = 0; r < n_keep; ++r) {
                         const uint32_t m1 = __reduce_max_sync(FULL, cur_hi);
                         unsigned who = __ballot_sync(FULL, cur_hi == m1);
                         if (who & (who - 1)) {  // several lanes share the top score: lowest node id wins
-                            const uint32_t m2 = __reduce_max_sync(FULL, cur_hi == m1 ? cur_lo : 0u);
-                            who = __ballot_sync(FULL, cur_hi == m1 && cur_lo == m2);
+                            const uint32_t my_lo = (cur_hi == m1) ? slo[(head - srec_base) >> 3] : 0u;
+                            const uint32_t m2 = __reduce_max_sync(FULL, my_lo);
+                            who = __ballot_sync(FULL, cur_hi == m1 && my_lo == m2);
                         }
                         const int wl = __ffs(who) - 1;
                         if (lane == wl) {
-                            sel[r] = base + perm[head - base];
-                            ++head;
-                            cur_hi = (head < tail) ? skey[head] : 0u;
-                            cur_lo = (head < tail) ? slo[head] : 0u;
+                            sel[r] = int(cur_idx);
+                            head += 8;
+                            lds_v2(head, cur_hi, cur_idx);
                         }
                     }
                 } else {
@@ -476,9 +500,8 @@ static bool plan_beam(int B, int C, BeamLayout* L) {
     L->off_gp = int(o);     o = up(o + 4 * nc, 16);
     L->off_src = int(o);
     L->off_sel = int(o);    o = up(o + 4LL * B, 16);
-    L->off_perm = int(o);   o = up(o + 32LL * C, 16);
-    L->off_skey = int(o);   o = up(o + 4LL * 32 * C, 16);
-    L->off_slo = int(o);    o = up(o + 4LL * 32 * C, 16);
+    L->off_srec = int(o);   o = up(o + 8LL * 32 * (C + 1), 16);
+    L->off_slo = int(o);    o = up(o + 4LL * 32 * (C + 1), 16);
     L->off_rows = int(o);   o = up(o + 2LL * BM_ROWBUF * 4, 16);
     L->off_root = int(o);   o = up(o + 4LL * (NL > 0 ? NL : 1), 16);
     L->warp_bytes = int(up(o, 128));
