@@ -83,7 +83,9 @@ __device__ __forceinline__ BeamView beam_view(unsigned char* base, int B) {
 // CRF = true gives search::crf_beam_search (src/search.rs:38-157): posteriors are [T, S, C], every
 // hypothesis carries a transition state and reads row probs[t][state][:], a label moves it to
 // (state * n_base) % n_state + label, and there is no repeat-collapse case.
-template <bool CRF>
+// CT = compile-time label count (0 = read it from the parameters): with CT = 5, the nanopore
+// alphabet, every per-label loop unrolls and the slot arithmetic becomes constant.
+template <bool CRF, int CT>
 __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParams p, const BeamLayout L) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int lane = threadIdx.x & 31;
@@ -91,7 +93,7 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
     const int slot = blockIdx.x * BM_WARPS + warp;
     if (slot >= p.n_slots) return;
     unsigned char* ws = smem + (size_t)warp * L.warp_bytes;
-    const int B = p.beam_size, C = p.C, NL = C - 1;
+    const int B = p.beam_size, C = CT ? CT : p.C, NL = C - 1;
     const long long T = p.T;
     const float thr = p.threshold;
     const bool collapse = !CRF && p.collapse != 0;
@@ -306,7 +308,11 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
                             cnode[s] = id;
                             rec[id] = make_int2(node, int(t));  // src/tree.rs:138-142, data = idx
                             nlab[id] = uint8_t(l);
-                            for (int j = 0; j < NL; ++j) child[(size_t)id * NL + j] = -1;  // src/tree.rs:143
+                            if (CT == 5) {  // four children: one 16-byte store (the child table is 16-byte aligned)
+                                *reinterpret_cast<int4*>(child + (size_t)id * 4) = make_int4(-1, -1, -1, -1);
+                            } else {
+                                for (int j = 0; j < NL; ++j) child[(size_t)id * NL + j] = -1;  // src/tree.rs:143
+                            }
                             if (node == ROOT) root_child[l] = id;
                             else child[(size_t)node * NL + l] = id;
                         }
@@ -556,14 +562,14 @@ cudaError_t launch_beam(const BeamParams& p, int sm_count, cudaStream_t stream) 
     if (!plan_beam(p.beam_size, p.C, &L)) return cudaErrorInvalidConfiguration;
     const int smem = L.warp_bytes * BM_WARPS;
     const bool crf = p.S > 0;
-    cudaError_t e = crf ? cudaFuncSetAttribute(beam_search_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
-                        : cudaFuncSetAttribute(beam_search_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    auto kernel = crf ? (p.C == 5 ? beam_search_kernel<true, 5> : beam_search_kernel<true, 0>)
+                      : (p.C == 5 ? beam_search_kernel<false, 5> : beam_search_kernel<false, 0>);
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
     e = cudaMemsetAsync(p.ticket, 0, sizeof(unsigned long long), stream);
     if (e != cudaSuccess) return e;
     const int grid = p.n_slots / BM_WARPS;
-    if (crf) beam_search_kernel<true><<<grid, BM_THREADS, smem, stream>>>(p, L);
-    else beam_search_kernel<false><<<grid, BM_THREADS, smem, stream>>>(p, L);
+    kernel<<<grid, BM_THREADS, smem, stream>>>(p, L);
     return cudaGetLastError();
 }
 
