@@ -538,16 +538,18 @@ int64_t beam_scratch_bytes(int sm_count, int64_t N, int64_t T, int C, int beam_s
     // warps: 24 per SM is what registers and shared memory allow.  One trie pool per resident warp.
     int per_sm = 24;
     if (const char* e = getenv("FCTC_BEAM_WARPS_PER_SM")) per_sm = atoi(e) > 0 ? atoi(e) : per_sm;  // tuning knob
+    if (beam_small_eligible(beam_size, C, T)) per_sm = beam_small_warps_per_sm();  // narrow beams: lighter warps
+    const int wpc = beam_warps_per_cta(beam_size, C, T);
     long long slots = (long long)sm_count * per_sm;
     if (slots > N) slots = N;
     if (slots < 1) slots = 1;
-    slots = (slots + BM_WARPS - 1) / BM_WARPS * BM_WARPS;
+    slots = (slots + wpc - 1) / wpc * wpc;
     const long long cap = (long long)nodes_per_row * (T > 0 ? T : 1);
-    const long long per_slot = (long long)beam_slot_bytes(cap, C - 1);
+    const long long per_slot = (long long)beam_pool_bytes(cap, beam_size, C, T);
     if (budget_bytes > 0) {  // fewer reads in flight rather than more memory
         long long fit = (budget_bytes - 256) / per_slot;
-        fit = fit / BM_WARPS * BM_WARPS;
-        if (fit < BM_WARPS) fit = BM_WARPS;
+        fit = fit / wpc * wpc;
+        if (fit < wpc) fit = wpc;
         if (slots > fit) slots = fit;
     }
     if (nodes_per_slot) *nodes_per_slot = cap;
@@ -555,9 +557,18 @@ int64_t beam_scratch_bytes(int sm_count, int64_t N, int64_t T, int C, int beam_s
     return 256 + slots * per_slot;
 }
 
+int64_t beam_pool_bytes(int64_t cap, int beam_size, int C, int64_t T) {
+    return beam_small_eligible(beam_size, C, T) ? beam_small_slot_bytes(cap) : int64_t(beam_slot_bytes(cap, C - 1));
+}
+
+int beam_warps_per_cta(int beam_size, int C, int64_t T) {
+    return beam_small_eligible(beam_size, C, T) ? beam_small_warps_per_cta() : BM_WARPS;
+}
+
 cudaError_t launch_beam(const BeamParams& p, int sm_count, cudaStream_t stream) {
     (void)sm_count;
     if (p.N <= 0) return cudaSuccess;
+    if (beam_small_eligible(p.beam_size, p.C, p.T)) return launch_beam_small(p, stream);
     BeamLayout L;
     if (!plan_beam(p.beam_size, p.C, &L)) return cudaErrorInvalidConfiguration;
     const int smem = L.warp_bytes * BM_WARPS;
@@ -640,16 +651,17 @@ extern "C" int fctc_beam_search_batch_device_static(fctc_handle* h, const float*
     fctc::BeamParams p{};
     const int sm_count = fctc::handle_sm_count(h);
     fctc::beam_scratch_bytes(sm_count, n_reads, n_rows, n_labels, beam_size, nodes_per_row, 0, &p.nodes_per_slot, &p.n_slots);
-    const int64_t per_slot = int64_t(fctc::beam_slot_bytes(p.nodes_per_slot, n_labels - 1));
+    const int64_t per_slot = fctc::beam_pool_bytes(p.nodes_per_slot, beam_size, n_labels, n_rows);
+    const int wpc = fctc::beam_warps_per_cta(beam_size, n_labels, n_rows);
     int64_t fit = (int64_t(FCTC_BEAM_STATIC_SCRATCH_BYTES) - 256) / per_slot;
-    fit = fit / fctc::BM_WARPS * fctc::BM_WARPS;
-    if (fit < fctc::BM_WARPS) {
+    fit = fit / wpc * wpc;
+    if (fit < wpc) {
         char msg[256];
         snprintf(msg, sizeof msg,
                  "static scratch too small: one trie pool for %lld rows x %d proposals needs %lld bytes and at least %d "
                  "are required, the built-in array holds %lld; use fctc_beam_search_batch_device with caller scratch",
                  (long long)n_rows, int(p.nodes_per_slot / (n_rows > 0 ? n_rows : 1)), (long long)per_slot,
-                 fctc::BM_WARPS, (long long)FCTC_BEAM_STATIC_SCRATCH_BYTES);
+                 wpc, (long long)FCTC_BEAM_STATIC_SCRATCH_BYTES);
         return fctc::handle_fail(h, FCTC_E_CAPACITY, msg);
     }
     if (p.n_slots > fit) p.n_slots = int(fit);

@@ -71,6 +71,15 @@ int64_t beam_scratch_bytes(int sm_count, int64_t N, int64_t T, int C, int beam_s
                            int64_t budget_bytes, int64_t* nodes_per_slot, int* n_slots);
 cudaError_t launch_beam(const BeamParams& p, int sm_count, cudaStream_t stream);
 bool beam_shape_supported(int beam_size, int C);
+// bytes of one warp's trie pool for `cap` nodes, for the kernel that (beam_size, C, T) selects
+int64_t beam_pool_bytes(int64_t cap, int beam_size, int C, int64_t T);
+int beam_warps_per_cta(int beam_size, int C, int64_t T);
+// narrow-beam kernel (beam_small.cu): one lane per candidate, beam_size * C <= 32
+bool beam_small_eligible(int beam_size, int C, int64_t T);
+int64_t beam_small_slot_bytes(int64_t cap);
+int beam_small_warps_per_cta();
+int beam_small_warps_per_sm();
+cudaError_t launch_beam_small(const BeamParams& p, cudaStream_t stream);
 
 struct DuplexParams {
     const float* post1;    // [N, T1, C]
