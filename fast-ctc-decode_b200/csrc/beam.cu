@@ -437,8 +437,8 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
                     const int i = sel[r];
                     const int b = i / C, sl = i - b * C;
                     nb.nd[r] = cnode[i];
-                    nb.lp[r] = clp[i] / top;
-                    nb.gp[r] = cgp[i] / top;
+                    nb.lp[r] = div_keep_zero(clp[i], top);
+                    nb.gp[r] = div_keep_zero(cgp[i], top);
                     if (sl == 0) { nb.par[r] = bv.par[b]; nb.dep[r] = bv.dep[b]; nb.tip[r] = bv.tip[b]; nb.st[r] = bv.st[b]; }
                     else {
                         nb.par[r] = bv.nd[b]; nb.dep[r] = bv.dep[b] + 1; nb.tip[r] = sl - 1;

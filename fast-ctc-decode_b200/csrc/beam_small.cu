@@ -257,8 +257,8 @@ __global__ void __launch_bounds__(BS_THREADS, 8) beam_small_kernel(const BeamPar
                 const int g_st = CRF ? __shfl_sync(FULL, st, my_src) : 0;
                 const int s_sl = my_src - (my_src / C) * C;
                 nd = g_x;
-                lp = g_lp / top;
-                gp = g_gp / top;
+                lp = div_keep_zero(g_lp, top);
+                gp = div_keep_zero(g_gp, top);
                 if (s_sl == 0) {
                     par = g_par; dep = g_dep; tip = g_tip; skp = g_skp; st = g_st;
                 } else {

@@ -72,6 +72,17 @@ __device__ __forceinline__ void lds_v2(uint32_t addr, uint32_t& a, uint32_t& b) 
     asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(a), "=r"(b) : "r"(addr) : "memory");
 }
 
+// IEEE a / b that keeps a zero numerator away from the division's out-of-line special-case code:
+// (+-0) / b is the same zero for any finite b > 0, and in the beam searches most quotients are of
+// that kind (the gap probability of a freshly extended hypothesis is 0).
+__device__ __forceinline__ float div_keep_zero(float a, float b) {
+    const bool zero_over_finite = a == 0.0f && b > 0.0f && b <= 3.402823466e+38f;
+    float num = zero_over_finite ? 1.0f : a;  // the divider itself never sees the zero (no branch to rely on)
+    asm volatile("" : "+f"(num));            // ... and the compiler may not fold the select back into a / b
+    const float q = num / b;
+    return zero_over_finite ? a : q;
+}
+
 __device__ __forceinline__ int warp_inclusive_scan(int v, int lane) {
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
