@@ -390,19 +390,41 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
                     uint32_t head = list0;
                     uint32_t cur_hi = 0u, cur_idx = 0u;
                     if (lane < nbeam) lds_v2(head, cur_hi, cur_idx);
+                    // Fast rounds: the lane whose list head is the maximum takes the next rank (one REDUX and a
+                    // compare).  Equal scores on two lanes would both take it; the winner count then exceeds
+                    // n_keep and the exact rounds below (score, then lowest node id) rank the row again.
+                    // (A double win can also exhaust the candidates early: then the last maximum is 0.)
+                    int won = 0;
+                    uint32_t last_max = 0u;  // maxima never increase from round to round
                     for (int r = 0; r < n_keep; ++r) {
                         const uint32_t m1 = __reduce_max_sync(FULL, cur_hi);
-                        unsigned who = __ballot_sync(FULL, cur_hi == m1);
-                        if (who & (who - 1)) {  // several lanes share the top score: lowest node id wins
-                            const uint32_t my_lo = (cur_hi == m1) ? slo[(head - srec_base) >> 3] : 0u;
-                            const uint32_t m2 = __reduce_max_sync(FULL, my_lo);
-                            who = __ballot_sync(FULL, cur_hi == m1 && my_lo == m2);
-                        }
-                        const int wl = __ffs(who) - 1;
-                        if (lane == wl) {
+                        last_max = m1;
+                        if (cur_hi == m1 && m1 != 0u) {
                             sel[r] = int(cur_idx);
                             head += 8;
                             lds_v2(head, cur_hi, cur_idx);
+                            ++won;
+                        }
+                    }
+                    if (last_max == 0u || __reduce_add_sync(FULL, won) != n_keep) {
+                        __syncwarp();
+                        head = list0;
+                        cur_hi = 0u;
+                        if (lane < nbeam) lds_v2(head, cur_hi, cur_idx);
+                        for (int r = 0; r < n_keep; ++r) {
+                            const uint32_t m1 = __reduce_max_sync(FULL, cur_hi);
+                            unsigned who = __ballot_sync(FULL, cur_hi == m1);
+                            if (who & (who - 1)) {  // several lanes share the top score: lowest node id wins
+                                const uint32_t my_lo = (cur_hi == m1) ? slo[(head - srec_base) >> 3] : 0u;
+                                const uint32_t m2 = __reduce_max_sync(FULL, my_lo);
+                                who = __ballot_sync(FULL, cur_hi == m1 && my_lo == m2);
+                            }
+                            const int wl = __ffs(who) - 1;
+                            if (lane == wl) {
+                                sel[r] = int(cur_idx);
+                                head += 8;
+                                lds_v2(head, cur_hi, cur_idx);
+                            }
                         }
                     }
                 } else {

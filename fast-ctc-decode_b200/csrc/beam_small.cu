@@ -43,8 +43,11 @@ __device__ __forceinline__ uint32_t order_key(float v) {  // monotone map f32 ->
     return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
 }
 
+#ifndef BS_MINBLOCKS
+#define BS_MINBLOCKS 8
+#endif
 template <bool CRF, int CT>
-__global__ void __launch_bounds__(BS_THREADS, 8) beam_small_kernel(const BeamParams p) {
+__global__ void __launch_bounds__(BS_THREADS, BS_MINBLOCKS) beam_small_kernel(const BeamParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int lane = threadIdx.x & 31;
     const int warp = __shfl_sync(FULL, threadIdx.x >> 5, 0);  // tells the compiler it is warp-uniform
@@ -54,6 +57,7 @@ __global__ void __launch_bounds__(BS_THREADS, 8) beam_small_kernel(const BeamPar
     float* rowbuf = reinterpret_cast<float*>(ws);
     int* root_child = reinterpret_cast<int*>(ws + 2 * BS_ROWBUF * 4);
     int* heads = root_child + 4;
+    int* sel = heads;  // winning lane of every rank; shares the traceback's block-head array
 
     const int B = p.beam_size, C = CT ? CT : p.C, NL = C - 1;
     const long long T = p.T;
@@ -232,20 +236,30 @@ __global__ void __launch_bounds__(BS_THREADS, 8) beam_small_kernel(const BeamPar
                     break;
                 }
                 const int n_keep = n_cand < B ? n_cand : B;
-                int my_src = lane, src0 = 0;
+                // Each round the lane holding the maximum takes the next rank: one REDUX and a compare.  Two
+                // candidates with the same score would both take it; that shows up as a winner count above
+                // n_keep and the row is ranked again by the exact loop (score, then lowest node id).
+                // (A double win can also exhaust the candidates early: then the last maximum is 0.)
+                const uint32_t hi0 = hi;
+                int won = 0;
+                uint32_t m1 = 0u;  // maxima never increase from round to round
                 for (int r = 0; r < n_keep; ++r) {
-                    const uint32_t m1 = __reduce_max_sync(FULL, hi);
-                    unsigned who = __ballot_sync(FULL, hi == m1);
-                    if (who & (who - 1)) {  // several candidates share the top score: lowest node id wins
-                        const uint32_t my_lo = (hi == m1) ? lo : 0u;
-                        const uint32_t m2 = __reduce_max_sync(FULL, my_lo);
-                        who = __ballot_sync(FULL, hi == m1 && my_lo == m2);
-                    }
-                    const int wl = __ffs(who) - 1;
-                    if (myb == r) my_src = wl;
-                    if (lane == wl) hi = 0u;
-                    if (r == 0) src0 = wl;
+                    m1 = __reduce_max_sync(FULL, hi);
+                    if (hi == m1 && m1 != 0u) { sel[r] = lane; hi = 0u; ++won; }
                 }
+                if (m1 == 0u || __reduce_add_sync(FULL, won) != n_keep) {
+                    hi = hi0;
+                    __syncwarp();
+                    for (int r = 0; r < n_keep; ++r) {
+                        const uint32_t x1 = __reduce_max_sync(FULL, hi);
+                        const uint32_t my_lo = (hi == x1) ? lo : 0u;
+                        const uint32_t x2 = __reduce_max_sync(FULL, my_lo);
+                        if (hi == x1 && my_lo == x2) { sel[r] = lane; hi = 0u; }
+                    }
+                }
+                __syncwarp();
+                const int my_src = (myb < n_keep) ? sel[myb] : lane;
+                const int src0 = sel[0];
 
                 // ---- new beam, renormalised by the top score (src/search.rs:278-282) -----------------
                 const float top = __shfl_sync(FULL, __fadd_rn(c_lp, c_gp), src0);
