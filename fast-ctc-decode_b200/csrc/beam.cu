@@ -394,19 +394,24 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
                     // compare).  Equal scores on two lanes would both take it; the winner count then exceeds
                     // n_keep and the exact rounds below (score, then lowest node id) rank the row again.
                     // (A double win can also exhaust the candidates early: then the last maximum is 0.)
-                    int won = 0;
                     uint32_t last_max = 0u;  // maxima never increase from round to round
-                    for (int r = 0; r < n_keep; ++r) {
-                        const uint32_t m1 = __reduce_max_sync(FULL, cur_hi);
-                        last_max = m1;
-                        if (cur_hi == m1 && m1 != 0u) {
-                            sel[r] = int(cur_idx);
-                            head += 8;
-                            lds_v2(head, cur_hi, cur_idx);
-                            ++won;
-                        }
+                    uint32_t sel_addr = smem_u32(sel);
+                    for (int r = 0; r < n_keep; ++r, sel_addr += 4) {
+                        last_max = __reduce_max_sync(FULL, cur_hi);
+                        asm volatile(  // if (cur_hi == max) { sel[r] = cur_idx; head += 8; load the next record } without a branch
+                            "{\n\t.reg .pred p;\n\t"
+                            "setp.eq.u32 p, %0, %3;\n\t"
+                            "@p st.shared.b32 [%4], %1;\n\t"
+                            "@p add.u32 %2, %2, 8;\n\t"
+                            "@p ld.shared.v2.b32 {%0, %1}, [%2];\n\t}"
+                            : "+r"(cur_hi), "+r"(cur_idx), "+r"(head)
+                            : "r"(last_max), "r"(sel_addr)
+                            : "memory");
                     }
-                    if (last_max == 0u || __reduce_add_sync(FULL, won) != n_keep) {
+                    // every win moved a list head by one record (lists end in a zero sentinel; a lane that
+                    // "wins" with a zero only happens when the maximum itself is 0, which forces the re-rank)
+                    const int won = __reduce_add_sync(FULL, int(head - list0) >> 3);
+                    if (last_max == 0u || won != n_keep) {
                         __syncwarp();
                         head = list0;
                         cur_hi = 0u;

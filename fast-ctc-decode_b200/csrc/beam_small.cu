@@ -58,6 +58,7 @@ __global__ void __launch_bounds__(BS_THREADS, BS_MINBLOCKS) beam_small_kernel(co
     int* root_child = reinterpret_cast<int*>(ws + 2 * BS_ROWBUF * 4);
     int* heads = root_child + 4;
     int* sel = heads;  // winning lane of every rank; shares the traceback's block-head array
+    const uint32_t sel_base = smem_u32(sel);
 
     const int B = p.beam_size, C = CT ? CT : p.C, NL = C - 1;
     const long long T = p.T;
@@ -241,13 +242,21 @@ __global__ void __launch_bounds__(BS_THREADS, BS_MINBLOCKS) beam_small_kernel(co
                 // n_keep and the row is ranked again by the exact loop (score, then lowest node id).
                 // (A double win can also exhaust the candidates early: then the last maximum is 0.)
                 const uint32_t hi0 = hi;
-                int won = 0;
                 uint32_t m1 = 0u;  // maxima never increase from round to round
-                for (int r = 0; r < n_keep; ++r) {
+                uint32_t sel_addr = sel_base;
+                for (int r = 0; r < n_keep; ++r, sel_addr += 4) {
                     m1 = __reduce_max_sync(FULL, hi);
-                    if (hi == m1 && m1 != 0u) { sel[r] = lane; hi = 0u; ++won; }
+                    asm volatile(  // if (hi == m1) { sel[r] = lane; hi = 0; } without a branch
+                        "{\n\t.reg .pred p;\n\t"
+                        "setp.eq.u32 p, %0, %1;\n\t"
+                        "@p st.shared.b32 [%2], %3;\n\t"
+                        "@p mov.u32 %0, 0;\n\t}"
+                        : "+r"(hi)
+                        : "r"(m1), "r"(sel_addr), "r"(lane)
+                        : "memory");
                 }
-                if (m1 == 0u || __reduce_add_sync(FULL, won) != n_keep) {
+                const int won = __popc(__ballot_sync(FULL, hi0 != 0u && hi == 0u));
+                if (m1 == 0u || won != n_keep) {
                     hi = hi0;
                     __syncwarp();
                     for (int r = 0; r < n_keep; ++r) {
