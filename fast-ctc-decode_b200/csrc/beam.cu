@@ -195,6 +195,13 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
                 const float* pr_time = rd + t * S * C;  // crf: [S][C] block of this time step
                 BeamView nb = beam_view(ws + (cur ^ 1) * L.beam_stride, B);
 
+                // The child rows of the beam's nodes are needed in phase B1; with four labels a row is one
+                // 16-byte load, issued here so that its latency hides behind phase A (beams of <= 32).
+                int4 kids = make_int4(-1, -1, -1, -1);
+                if (CT == 5 && B <= 32 && lane < nbeam) {
+                    const int node = bv.nd[lane];
+                    if (node != ROOT) kids = *reinterpret_cast<const int4*>(child + (size_t)node * 4);
+                }
                 // ---- phase A: each hypothesis' own continuation, plus its parent's extension -------
                 for (int b = lane; b < nbeam; b += 32) {
                     const int node = bv.nd[b];
@@ -255,7 +262,10 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
                         uint32_t key = 0;
                         if (!(pl < thr)) {  // src/search.rs:201-203
                             const bool repeat = collapse && l == tip;
-                            int x = (node == ROOT) ? root_child[l] : child[(size_t)node * NL + l];
+                            int x;
+                            if (node == ROOT) x = root_child[l];
+                            else if (CT == 5 && B <= 32) x = (l == 0) ? kids.x : (l == 1) ? kids.y : (l == 2) ? kids.z : kids.w;
+                            else x = child[(size_t)node * NL + l];
                             bool take = true;
                             if (x < 0) {
                                 if (repeat && !(gp > 0.0f)) take = false;  // src/search.rs:212-218
