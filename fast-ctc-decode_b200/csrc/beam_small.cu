@@ -139,6 +139,10 @@ __global__ void __launch_bounds__(BS_THREADS, BS_MINBLOCKS) beam_small_kernel(co
                 const float* pr = CRF ? rd + t * S * C + (size_t)st * C : rows + rr * C;  // my hypothesis' row
                 const float p_mine = active ? pr[sl] : 0.0f;                               // blank for s = 0
                 const float p_tip = (active && sl == 0 && tip >= 0) ? pr[tip + 1] : 0.0f;
+                // my node's child for my label, asked for now so that the load overlaps the steps below
+                int x_child = -1;
+                if (active && sl > 0)
+                    x_child = (nd == ROOT) ? root_child[sl - 1] : reinterpret_cast<const int*>(nodes + 2 * (size_t)nd + 1)[sl - 1];
 
                 // ---- my own continuation (s = 0 lanes) -------------------------------------------------
                 bool has_self = false;
@@ -189,7 +193,7 @@ __global__ void __launch_bounds__(BS_THREADS, BS_MINBLOCKS) beam_small_kernel(co
                         c_gp = 0.0f;
                         if (!(p_mine < thr)) {  // src/search.rs:201-203
                             const bool repeat = collapse && l == tip;
-                            x = (nd == ROOT) ? root_child[l] : reinterpret_cast<const int*>(nodes + 2 * (size_t)nd + 1)[l];
+                            x = x_child;
                             bool take = true;
                             if (x < 0) {
                                 if (repeat && !(gp > 0.0f)) take = false;  // src/search.rs:212-218
