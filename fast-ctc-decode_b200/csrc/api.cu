@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <cstdlib>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -290,30 +291,65 @@ int host_pipeline(fctc_handle* h, const float* post_host, int64_t n_reads, int64
         if (int rc = ensure(h, s.cursor, 256)) return rc;
         s.busy = false;
     }
+    // FCTC_TRACE_PIPELINE=1 prints, per chunk, when its copy-in started / ended and when its kernel ended
+    // (milliseconds on the device clock since the first chunk was queued): a development aid.
+    const bool trace = getenv("FCTC_TRACE_PIPELINE") != nullptr;
+    std::vector<cudaEvent_t> tev;
+    auto mark = [&](cudaStream_t st) {
+        if (!trace) return;
+        cudaEvent_t e;
+        cudaEventCreate(&e);
+        cudaEventRecord(e, st);
+        tev.push_back(e);
+    };
+    // Queue order matters: the copy engines take work in submission order, so the read-back of chunk i
+    // (which has to wait for kernel i) is only queued after the copy-in of chunk i+1 — otherwise that
+    // copy-in sits behind it and the transfer never overlaps the kernel (measured: fully serial).
+    auto queue_readback = [&](Slot& s, int64_t first, int64_t cnt) -> int {
+        FCTC_CUDA(h, cudaMemcpyAsync(s.cursor_host, s.cursor.p, 8, cudaMemcpyDeviceToHost, s.stream));
+        FCTC_CUDA(h, cudaMemcpyAsync(out.offsets + first, s.offsets.p, size_t(cnt) * 8, cudaMemcpyDeviceToHost, s.stream));
+        FCTC_CUDA(h, cudaMemcpyAsync(out.lens + first, s.lens.p, size_t(cnt) * 4, cudaMemcpyDeviceToHost, s.stream));
+        FCTC_CUDA(h, cudaMemcpyAsync(out.status + first, s.status.p, size_t(cnt) * 4, cudaMemcpyDeviceToHost, s.stream));
+        FCTC_CUDA(h, cudaEventRecord(s.done, s.stream));
+        return 0;
+    };
     int which = 0;
+    int64_t prev_first = -1, prev_cnt = 0;
     for (int64_t first = 0; first < n_reads; first += chunk, which ^= 1) {
         Slot& s = h->slot[which];
         if (int rc = drain_slot(h, s, out)) return rc;
         const int64_t cnt = std::min(chunk, n_reads - first);
         s.dst_first = first;
         s.count = cnt;
+        mark(s.stream);
         if (read_bytes > 0)
             FCTC_CUDA(h, cudaMemcpyAsync(s.post.p, post_host + first * n_rows * n_labels, size_t(cnt * read_bytes),
                                          cudaMemcpyHostToDevice, s.stream));
+        mark(s.stream);
         FCTC_CUDA(h, cudaMemsetAsync(s.cursor.p, 0, 8, s.stream));
         if (int rc = launch(s, cnt)) return rc;
-        FCTC_CUDA(h, cudaMemcpyAsync(s.cursor_host, s.cursor.p, 8, cudaMemcpyDeviceToHost, s.stream));
-        FCTC_CUDA(h, cudaMemcpyAsync(out.offsets + first, s.offsets.p, size_t(cnt) * 8, cudaMemcpyDeviceToHost, s.stream));
-        FCTC_CUDA(h, cudaMemcpyAsync(out.lens + first, s.lens.p, size_t(cnt) * 4, cudaMemcpyDeviceToHost, s.stream));
-        FCTC_CUDA(h, cudaMemcpyAsync(out.status + first, s.status.p, size_t(cnt) * 4, cudaMemcpyDeviceToHost, s.stream));
-        FCTC_CUDA(h, cudaEventRecord(s.done, s.stream));
+        mark(s.stream);
         s.busy = true;
+        if (prev_first >= 0)
+            if (int rc = queue_readback(h->slot[which ^ 1], prev_first, prev_cnt)) return rc;
+        prev_first = first;
+        prev_cnt = cnt;
     }
+    if (prev_first >= 0)
+        if (int rc = queue_readback(h->slot[which ^ 1], prev_first, prev_cnt)) return rc;
     // drain in submission order: the slot used before the last one first
     if (int rc = drain_slot(h, h->slot[which], out)) return rc;
     if (int rc = drain_slot(h, h->slot[which ^ 1], out)) return rc;
     FCTC_CUDA(h, cudaStreamSynchronize(h->slot[0].stream));
     FCTC_CUDA(h, cudaStreamSynchronize(h->slot[1].stream));
+    for (size_t i = 0; i + 2 < tev.size() + 0 && trace; i += 3) {
+        float a = 0, b = 0, c = 0;
+        cudaEventElapsedTime(&a, tev[0], tev[i]);
+        cudaEventElapsedTime(&b, tev[0], tev[i + 1]);
+        cudaEventElapsedTime(&c, tev[0], tev[i + 2]);
+        fprintf(stderr, "[fctc pipeline] chunk %zu: copy-in %.2f..%.2f ms, kernel done %.2f ms\n", i / 3, a, b, c);
+    }
+    for (cudaEvent_t e : tev) cudaEventDestroy(e);
     return 0;
 }
 
@@ -558,6 +594,7 @@ int beam_host_pass(fctc_handle* h, const float* post_host, int64_t n_reads, int6
     const int64_t read_bytes = std::max<int64_t>(n_rows * int64_t(n_labels) * 4, 1);
     int64_t chunk = std::max<int64_t>(default_chunk_reads(read_bytes), int64_t(h->sm_count) * 24 * 4);
     chunk = std::min<int64_t>(chunk, std::max<int64_t>((int64_t(2) << 30) / read_bytes, 1));
+    if (const char* e = getenv("FCTC_BEAM_CHUNK_READS")) chunk = atoll(e) > 0 ? atoll(e) : chunk;  // tuning knob
     chunk = std::min<int64_t>(chunk, n_reads);
     int64_t nodes_per_slot = 0;
     int n_slots = 0;
