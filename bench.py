@@ -224,6 +224,8 @@ def run_ours(args, w):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
+        # stdout carries exactly one JSON line: NCCL's own banner / debug lines go to stderr
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
     dec = fctc_b200.Decoder(local_rank)
     N, T, Cn = args.reads or w["reads"], w["T"], w["C"]
