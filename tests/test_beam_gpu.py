@@ -54,6 +54,9 @@ CASES = [
     (6, 300, 5, 40, 0.0, True), (4, 200, 5, 64, 0.0, True), (6, 500, 3, 5, 0.1, True), (4, 400, 12, 5, 0.0, True),
     (4, 300, 12, 16, 0.01, True), (6, 700, 4, 7, 0.0, True), (5, 33, 5, 5, 0.1, True), (3, 1, 5, 5, 0.0, True),
     (3, 250, 2, 5, 0.0, True), (2, 4000, 5, 5, 0.1, True), (2, 2000, 5, 32, 0.0, True),
+    # the narrow-beam kernel's corners (beam * C <= 32) and the first shapes past it
+    (6, 300, 2, 16, 0.0, True), (6, 300, 3, 10, 0.02, True), (6, 300, 4, 8, 0.0, False), (6, 300, 5, 6, 0.0, True),
+    (6, 300, 5, 7, 0.0, True), (6, 300, 3, 11, 0.0, True),
 ]
 
 
@@ -66,6 +69,24 @@ def test_batch_host_parity(dec, oracle, case, kind):
         else peaked_posteriors(rng, (N, T, Cn))
     res = dec.beam_search_batch(post, beam, thr, collapse)
     check_batch(oracle, post, res, beam, thr, collapse)
+
+
+@pytest.mark.parametrize("beam", [3, 5, 6, 16, 32])
+@pytest.mark.parametrize("collapse", [True, False])
+def test_score_ties_follow_the_oracle_rule(dec, oracle, beam, collapse):
+    """Rows of equal or few distinct probabilities make many candidates tie exactly: the ranking's
+    fast rounds must notice and the exact rounds must apply "equal score -> lower node id"."""
+    rng = np.random.default_rng(100 + beam)
+    T, Cn = 60, 5
+    flat = np.full((T, Cn), 0.2, np.float32)
+    coarse = rng.choice(np.array([0.125, 0.25, 0.5], np.float32), size=(T, Cn))
+    half = flat.copy()
+    half[::2] = coarse[::2]
+    for post in (flat, coarse, half):
+        st, labels, path = dec.beam_search(post, beam, 0.0, collapse)
+        ost, ol, op = oracle.beam_search(post, beam, 0.0, collapse)
+        assert st == ost == 0
+        assert np.array_equal(labels, ol) and np.array_equal(path, op)
 
 
 def test_unnormalised_readme_input(dec, oracle):
