@@ -201,11 +201,12 @@ void fctc_destroy(fctc_handle* h) {
 // ---------------------------------------------------------------------------------------------
 // Viterbi
 // ---------------------------------------------------------------------------------------------
-int fctc_viterbi_batch_device(fctc_handle* h, const float* post_dev, int64_t n_reads, int64_t n_rows,
-                              int32_t n_labels, int32_t qstring, float qscale, float qbias,
-                              int32_t collapse_repeats, uint8_t* labels_dev, void* quals_dev, int32_t qual_bytes,
-                              int32_t* path_dev, int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev,
-                              int32_t* status_dev, void* stream) {
+namespace {
+int viterbi_batch_device_any(fctc_handle* h, const void* post_dev, int in_f16, int64_t n_reads, int64_t n_rows,
+                             int32_t n_labels, int32_t qstring, float qscale, float qbias,
+                             int32_t collapse_repeats, uint8_t* labels_dev, void* quals_dev, int32_t qual_bytes,
+                             int32_t* path_dev, int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev,
+                             int32_t* status_dev, void* stream) {
     if (int rc = check_common(h, n_reads, n_rows, n_labels)) return rc;
     if (n_rows == 0) return fail(h, FCTC_E_ARGUMENT, "n_rows must be >= 1 (the reference asserts a non-empty matrix)");
     if (!post_dev || !labels_dev || !path_dev || !offsets_dev || !lens_dev || !status_dev)
@@ -221,12 +222,33 @@ int fctc_viterbi_batch_device(fctc_handle* h, const float* post_dev, int64_t n_r
                     (long long)pool_capacity, (long long)(n_reads * stride));
     FCTC_CUDA(h, cudaSetDevice(h->device));
     fctc::ViterbiParams p{};
-    p.post = post_dev; p.N = n_reads; p.T = n_rows; p.C = n_labels;
+    p.post = static_cast<const float*>(post_dev); p.in_f16 = in_f16; p.N = n_reads; p.T = n_rows; p.C = n_labels;
     p.qstring = qstring; p.qscale = qscale; p.qbias = qbias; p.collapse = collapse_repeats;
     p.labels = labels_dev; p.quals = quals_dev; p.qual_bytes = qual_bytes; p.path = path_dev;
     p.slot_stride = stride; p.offset_base = 0; p.offsets = offsets_dev; p.lens = lens_dev; p.status = status_dev;
     FCTC_CUDA(h, fctc::launch_viterbi(p, h->sm_count, static_cast<cudaStream_t>(stream), nullptr));
     return 0;
+}
+}  // namespace
+
+int fctc_viterbi_batch_device(fctc_handle* h, const float* post_dev, int64_t n_reads, int64_t n_rows,
+                              int32_t n_labels, int32_t qstring, float qscale, float qbias,
+                              int32_t collapse_repeats, uint8_t* labels_dev, void* quals_dev, int32_t qual_bytes,
+                              int32_t* path_dev, int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev,
+                              int32_t* status_dev, void* stream) {
+    return viterbi_batch_device_any(h, post_dev, 0, n_reads, n_rows, n_labels, qstring, qscale, qbias, collapse_repeats,
+                                    labels_dev, quals_dev, qual_bytes, path_dev, pool_capacity, offsets_dev, lens_dev,
+                                    status_dev, stream);
+}
+
+int fctc_viterbi_batch_device_f16(fctc_handle* h, const void* post_dev_f16, int64_t n_reads, int64_t n_rows,
+                                  int32_t n_labels, int32_t qstring, float qscale, float qbias,
+                                  int32_t collapse_repeats, uint8_t* labels_dev, void* quals_dev, int32_t qual_bytes,
+                                  int32_t* path_dev, int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev,
+                                  int32_t* status_dev, void* stream) {
+    return viterbi_batch_device_any(h, post_dev_f16, 1, n_reads, n_rows, n_labels, qstring, qscale, qbias,
+                                    collapse_repeats, labels_dev, quals_dev, qual_bytes, path_dev, pool_capacity,
+                                    offsets_dev, lens_dev, status_dev, stream);
 }
 
 namespace {
@@ -359,10 +381,13 @@ int64_t default_chunk_reads(int64_t read_bytes) {  // ~64 MiB of posteriors per 
 
 }  // namespace
 
-int fctc_viterbi_batch(fctc_handle* h, const float* post_host, int64_t n_reads, int64_t n_rows, int32_t n_labels,
-                       int32_t qstring, float qscale, float qbias, int32_t collapse_repeats, uint8_t* labels,
-                       void* quals, int32_t qual_bytes, int32_t* path, int64_t pool_capacity, int64_t* offsets,
-                       int32_t* lens, int32_t* status, int64_t* pool_used) {
+namespace {
+int viterbi_batch_any(fctc_handle* h, const void* post_host_any, int in_f16, int64_t n_reads, int64_t n_rows,
+                      int32_t n_labels, int32_t qstring, float qscale, float qbias, int32_t collapse_repeats,
+                      uint8_t* labels, void* quals, int32_t qual_bytes, int32_t* path, int64_t pool_capacity,
+                      int64_t* offsets, int32_t* lens, int32_t* status, int64_t* pool_used) {
+    const unsigned char* post_host = static_cast<const unsigned char*>(post_host_any);
+    const int elem_bytes = in_f16 ? 2 : 4;
     if (int rc = check_common(h, n_reads, n_rows, n_labels)) return rc;
     if (n_rows == 0) return fail(h, FCTC_E_ARGUMENT, "n_rows must be >= 1 (the reference asserts a non-empty matrix)");
     if (!post_host || !labels || !path || !offsets || !lens || !status)
@@ -382,7 +407,7 @@ int fctc_viterbi_batch(fctc_handle* h, const float* post_host, int64_t n_reads, 
 
     // Slot-form results need no cursor, so the whole pipeline is asynchronous: per chunk
     // H2D posteriors -> kernel -> D2H of the chunk's slots, alternating between two streams.
-    const int64_t read_bytes = n_rows * int64_t(n_labels) * 4;
+    const int64_t read_bytes = n_rows * int64_t(n_labels) * elem_bytes;
     const int64_t chunk = std::min(default_chunk_reads(read_bytes), n_reads);
     for (int i = 0; i < 2; ++i) {
         Slot& s = h->slot[i];
@@ -399,10 +424,10 @@ int fctc_viterbi_batch(fctc_handle* h, const float* post_host, int64_t n_reads, 
     for (int64_t first = 0; first < n_reads; first += chunk, which ^= 1) {
         Slot& s = h->slot[which];
         const int64_t cnt = std::min(chunk, n_reads - first);
-        FCTC_CUDA(h, cudaMemcpyAsync(s.post.p, post_host + first * n_rows * n_labels, size_t(cnt * read_bytes),
+        FCTC_CUDA(h, cudaMemcpyAsync(s.post.p, post_host + first * read_bytes, size_t(cnt * read_bytes),
                                      cudaMemcpyHostToDevice, s.stream));
         fctc::ViterbiParams p{};
-        p.post = static_cast<const float*>(s.post.p); p.N = cnt; p.T = n_rows; p.C = n_labels;
+        p.post = static_cast<const float*>(s.post.p); p.in_f16 = in_f16; p.N = cnt; p.T = n_rows; p.C = n_labels;
         p.qstring = qstring; p.qscale = qscale; p.qbias = qbias; p.collapse = collapse_repeats;
         p.labels = static_cast<uint8_t*>(s.labels.p); p.quals = s.quals.p; p.qual_bytes = qual_bytes;
         p.path = static_cast<int32_t*>(s.path.p); p.slot_stride = stride; p.offset_base = first * stride;
@@ -423,6 +448,23 @@ int fctc_viterbi_batch(fctc_handle* h, const float* post_host, int64_t n_reads, 
     FCTC_CUDA(h, cudaStreamSynchronize(h->slot[1].stream));
     if (pool_used) *pool_used = n_reads * stride;
     return 0;
+}
+}  // namespace
+
+int fctc_viterbi_batch(fctc_handle* h, const float* post_host, int64_t n_reads, int64_t n_rows, int32_t n_labels,
+                       int32_t qstring, float qscale, float qbias, int32_t collapse_repeats, uint8_t* labels,
+                       void* quals, int32_t qual_bytes, int32_t* path, int64_t pool_capacity, int64_t* offsets,
+                       int32_t* lens, int32_t* status, int64_t* pool_used) {
+    return viterbi_batch_any(h, post_host, 0, n_reads, n_rows, n_labels, qstring, qscale, qbias, collapse_repeats, labels,
+                             quals, qual_bytes, path, pool_capacity, offsets, lens, status, pool_used);
+}
+
+int fctc_viterbi_batch_f16(fctc_handle* h, const void* post_host_f16, int64_t n_reads, int64_t n_rows, int32_t n_labels,
+                           int32_t qstring, float qscale, float qbias, int32_t collapse_repeats, uint8_t* labels,
+                           void* quals, int32_t qual_bytes, int32_t* path, int64_t pool_capacity, int64_t* offsets,
+                           int32_t* lens, int32_t* status, int64_t* pool_used) {
+    return viterbi_batch_any(h, post_host_f16, 1, n_reads, n_rows, n_labels, qstring, qscale, qbias, collapse_repeats,
+                             labels, quals, qual_bytes, path, pool_capacity, offsets, lens, status, pool_used);
 }
 
 namespace {

@@ -190,7 +190,6 @@ __global__ void __launch_bounds__(DX_THREADS, 6) duplex_search_kernel(const Dupl
     const int NS = CRF ? p.S : 1;
     const float NEG = dx_neg_inf();
 
-    int* newcnt = reinterpret_cast<int*>(ws + L.off_newcnt);
     unsigned char* fold = ws + L.off_fold;
     uint32_t* ckey = reinterpret_cast<uint32_t*>(ws + L.off_key);
     int* cnode = reinterpret_cast<int*>(ws + L.off_node);

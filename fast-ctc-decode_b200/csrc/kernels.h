@@ -19,7 +19,8 @@ void* handle_pinned_buffer(fctc_handle* h, int index, size_t bytes);
 cudaStream_t handle_stream(fctc_handle* h);
 
 struct ViterbiParams {
-    const float* post;  // [N, T, C] contiguous, device
+    const float* post;  // [N, T, C] contiguous, device (binary16 values behind the same pointer when in_f16)
+    int in_f16;         // 1: the posteriors are IEEE binary16; every value is widened exactly to f32 before use
     int64_t N, T;
     int C;
     int qstring;

@@ -24,6 +24,8 @@
 //     MUFU.LG2 fast path whose result is only trusted when it is provably on the same side of
 //     every rounding boundary as glibc's log10f, else the exact binary64 re-evaluation of glibc's
 //     algorithm (phred.cuh) decides.
+#include <cuda_fp16.h>
+
 #include <cstdlib>
 
 #include "device_utils.cuh"
@@ -37,7 +39,7 @@ namespace fctc {
 constexpr unsigned FULLMASK = 0xffffffffu;
 constexpr int VW_WARPS = 4;  // warps per CTA of the streaming kernel
 constexpr int VW_THREADS = VW_WARPS * 32;
-constexpr int VW_MAX_STAGES = 8;
+constexpr int VW_MAX_STAGES = 16;
 // Resident CTAs per SM the compiler must allow (register budget) and bytes of posteriors each warp
 // keeps in flight.  Measured on B200 (65,536 reads x 4000 x 5): with quality strings the kernel is
 // issue-bound and wants more warps (6 CTAs, 3 stages); without, it is HBM-bound and runs best with
@@ -144,9 +146,13 @@ __device__ __forceinline__ P* keep_in_register(P* ptr) {  // stops the compiler 
 // ------------------------------------------------------------------------------------------
 // FAST5: five labels, RPL == 4 and every tile 16-byte aligned (the nanopore case), so that all the
 // tile geometry is a compile-time constant.
-template <typename QT, int RPL, bool COLLAPSE, bool QSTRING, bool FAST5>
+// HALF (with FAST5 only): the posteriors are binary16, 10 bytes per row; a lane's four rows are five
+// 8-byte shared loads, widened to f32 in registers.  Everything after the load is the f32 code.
+template <typename QT, int RPL, bool COLLAPSE, bool QSTRING, bool FAST5, bool HALF>
 __global__ void __launch_bounds__(VW_THREADS, QSTRING ? VW_MINBLOCKS_Q : VW_MINBLOCKS_NOQ) viterbi_stream_kernel(const ViterbiParams p, const WarpLayout L) {
     static_assert(!FAST5 || RPL == 4, "the five-label fast path is written for four rows per lane");
+    static_assert(!HALF || FAST5, "binary16 input is only staged by the five-label fast path");
+    constexpr int EB = HALF ? 2 : 4;  // bytes per posterior
     constexpr int TILE = 32 * RPL;
     extern __shared__ __align__(128) unsigned char smem[];
     double* s_invc = reinterpret_cast<double*>(smem);
@@ -169,7 +175,7 @@ __global__ void __launch_bounds__(VW_THREADS, QSTRING ? VW_MINBLOCKS_Q : VW_MINB
     const int my_reads = int((p.N > gw) ? (p.N - gw + nwarps - 1) / nwarps : 0);
     const long long read_elems = (long long)T * C;
     const long long total_elems = p.N * read_elems;
-    const long long safe_bytes = (total_elems * 4) & ~15LL;  // bulk copies never read past this
+    const long long safe_bytes = (total_elems * EB) & ~15LL;  // bulk copies never read past this
     const long long safe_elems = safe_bytes >> 2;
     const long long stride = p.slot_stride;
     // every tile of every read starts 16-byte aligned and lies inside the bulk-copy-safe range
@@ -189,8 +195,8 @@ __global__ void __launch_bounds__(VW_THREADS, QSTRING ? VW_MINBLOCKS_Q : VW_MINB
         if (p_reads <= 0) return;
         const int elems = (p_tl == 1) ? last_elems : tile_elems;
         if (lane == 0) {
-            long long b0 = p_e0 * 4;
-            uint32_t bytes = uint32_t(elems) * 4u;
+            long long b0 = p_e0 * EB;
+            uint32_t bytes = uint32_t(elems) * uint32_t(EB);
             if (!aligned) {
                 const long long e1 = p_e0 + elems;
                 b0 &= ~15LL;
@@ -238,8 +244,20 @@ __global__ void __launch_bounds__(VW_THREADS, QSTRING ? VW_MINBLOCKS_Q : VW_MINB
             int lab[RPL];
             if (FAST5) {
                 float f[20];
+                if (HALF) {
+                    uint32_t hw[10];
 #pragma unroll
-                for (int v = 0; v < 5; ++v) lds_f4(r_stage + 80 * lane + 16 * v, f + 4 * v);
+                    for (int v = 0; v < 5; ++v) lds_v2(r_stage + 40 * lane + 8 * v, hw[2 * v], hw[2 * v + 1]);
+#pragma unroll
+                    for (int j = 0; j < 10; ++j) {
+                        const float2 w = __half22float2(*reinterpret_cast<const __half2*>(&hw[j]));
+                        f[2 * j] = w.x;
+                        f[2 * j + 1] = w.y;
+                    }
+                } else {
+#pragma unroll
+                    for (int v = 0; v < 5; ++v) lds_f4(r_stage + 80 * lane + 16 * v, f + 4 * v);
+                }
 #pragma unroll
                 for (int r = 0; r < RPL; ++r) argmax_row5(f + 5 * (r & 3), lab[r], pr[r]);
                 if (rows != TILE) {  // rows past the end of the read (stale stage contents) count as blank
@@ -429,16 +447,20 @@ struct TileShared {  // double-buffered by tile parity so that one tile needs on
     int flag;
 };
 
-__device__ __forceinline__ void argmax_global(const float* row, int C, int& arg, float& best) {
-    best = row[0];
+__device__ __forceinline__ float widen(float v) { return v; }
+__device__ __forceinline__ float widen(__half v) { return __half2float(v); }
+
+template <typename IN>
+__device__ __forceinline__ void argmax_global(const IN* row, int C, int& arg, float& best) {
+    best = widen(row[0]);
     arg = 0;
     for (int c = 1; c < C; ++c) {
-        const float v = row[c];
+        const float v = widen(row[c]);
         if (v > best) { best = v; arg = c; }
     }
 }
 
-template <typename QT>
+template <typename QT, typename IN>
 __global__ void __launch_bounds__(VG_THREADS) viterbi_generic_kernel(const ViterbiParams p) {
     __shared__ TileShared S;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -454,7 +476,7 @@ __global__ void __launch_bounds__(VG_THREADS) viterbi_generic_kernel(const Viter
     __syncthreads();
     int buf = 0;
     for (long long n = blockIdx.x; n < p.N; n += gridDim.x) {
-        const float* rd = p.post + n * T * C;
+        const IN* rd = reinterpret_cast<const IN*>(p.post) + n * T * C;
         uint8_t* out_lab = p.labels + n * p.slot_stride;
         QT* out_qual = reinterpret_cast<QT*>(p.quals) + n * p.slot_stride;
         int* out_path = p.path + n * p.slot_stride;
@@ -565,16 +587,17 @@ static bool plan_stream(const ViterbiParams& p, WarpLayout* L) {
     if (p.T >= (1LL << 30) / (p.C > 0 ? p.C : 1)) return false;  // 32-bit row arithmetic in the kernel
     constexpr int TILE = 32 * RPL;
     const long long rows = p.T < TILE ? p.T : TILE;
-    const long long stage = ((rows * p.C * 4 + 15) & ~15LL) + 32;
+    const long long stage = ((rows * p.C * (p.in_f16 ? 2 : 4) + 15) & ~15LL) + 32;
     if (stage > 16 * 1024) return false;
     // enough bytes in flight per warp to cover HBM latency at the variant's resident warps per SM
     int ns = int(((p.qstring ? 8 : 11) * 1024) / stage);
+    if (p.in_f16) ns = p.qstring ? 6 : 10;  // half-size tiles: deeper rings (measured: 3 stages 1.43 ms, 10 stages 0.58 ms)
     if (const char* e = getenv("FCTC_VIT_STAGES")) ns = atoi(e) > 0 ? atoi(e) : ns;  // tuning knob
     if (ns > VW_MAX_STAGES) ns = VW_MAX_STAGES;
     if (ns < 2) ns = 2;
     L->nstage = ns;
     L->stage_bytes = int(stage);
-    L->off_stage = 64;
+    L->off_stage = (ns * 8 + 63) & ~63;  // ns mbarriers come first
     L->off_queue = int(L->off_stage + ns * stage);
     L->off_open = L->off_queue + (TILE + 1) * 8;
     L->warp_bytes = (L->off_open + 16 + 127) & ~127;
@@ -582,9 +605,9 @@ static bool plan_stream(const ViterbiParams& p, WarpLayout* L) {
     return L->cta_fixed + VW_WARPS * L->warp_bytes <= VT_SMEM_LIMIT;
 }
 
-template <typename QT, int RPL, bool COLLAPSE, bool QSTRING, bool FAST5>
+template <typename QT, int RPL, bool COLLAPSE, bool QSTRING, bool FAST5, bool HALF>
 static cudaError_t launch_stream(const ViterbiParams& p, const WarpLayout& L, int sm_count, cudaStream_t stream) {
-    auto kernel = viterbi_stream_kernel<QT, RPL, COLLAPSE, QSTRING, FAST5>;
+    auto kernel = viterbi_stream_kernel<QT, RPL, COLLAPSE, QSTRING, FAST5, HALF>;
     const int smem = L.cta_fixed + VW_WARPS * L.warp_bytes;
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
@@ -599,33 +622,43 @@ static cudaError_t launch_stream(const ViterbiParams& p, const WarpLayout& L, in
     return cudaGetLastError();
 }
 
-template <typename QT, int RPL, bool FAST5>
+template <typename QT, int RPL, bool FAST5, bool HALF>
 static cudaError_t launch_stream_flags(const ViterbiParams& p, const WarpLayout& L, int sm_count, cudaStream_t stream) {
     if (p.collapse) {
-        return p.qstring ? launch_stream<QT, RPL, true, true, FAST5>(p, L, sm_count, stream)
-                         : launch_stream<QT, RPL, true, false, FAST5>(p, L, sm_count, stream);
+        return p.qstring ? launch_stream<QT, RPL, true, true, FAST5, HALF>(p, L, sm_count, stream)
+                         : launch_stream<QT, RPL, true, false, FAST5, HALF>(p, L, sm_count, stream);
     }
-    return p.qstring ? launch_stream<QT, RPL, false, true, FAST5>(p, L, sm_count, stream)
-                     : launch_stream<QT, RPL, false, false, FAST5>(p, L, sm_count, stream);
+    return p.qstring ? launch_stream<QT, RPL, false, true, FAST5, HALF>(p, L, sm_count, stream)
+                     : launch_stream<QT, RPL, false, false, FAST5, HALF>(p, L, sm_count, stream);
 }
 
 template <typename QT>
 static cudaError_t launch_viterbi_t(const ViterbiParams& p, int sm_count, cudaStream_t stream, int* which) {
     WarpLayout L;
+    long long grid = (long long)sm_count * 8;
+    if (grid > p.N) grid = p.N;
+    if (p.in_f16) {
+        // binary16 rows are 10 bytes at five labels: reads (and so every 128-row tile) start 16-byte aligned when T % 8 == 0
+        if (p.C == 5 && (p.T & 7) == 0 && plan_stream<4>(p, &L)) {
+            if (which) *which = 0;
+            return launch_stream_flags<QT, 4, true, true>(p, L, sm_count, stream);
+        }
+        if (which) *which = 1;
+        viterbi_generic_kernel<QT, __half><<<dim3((unsigned)grid), VG_THREADS, 0, stream>>>(p);
+        return cudaGetLastError();
+    }
     if (p.C <= 16 && plan_stream<4>(p, &L)) {
         if (which) *which = 0;
         const bool fast5 = p.C == 5 && ((p.T * 5) & 3) == 0;  // every read (hence every tile) starts 16-byte aligned
-        return fast5 ? launch_stream_flags<QT, 4, true>(p, L, sm_count, stream)
-                     : launch_stream_flags<QT, 4, false>(p, L, sm_count, stream);
+        return fast5 ? launch_stream_flags<QT, 4, true, false>(p, L, sm_count, stream)
+                     : launch_stream_flags<QT, 4, false, false>(p, L, sm_count, stream);
     }
     if (p.C <= 64 && plan_stream<1>(p, &L)) {
         if (which) *which = 0;
-        return launch_stream_flags<QT, 1, false>(p, L, sm_count, stream);
+        return launch_stream_flags<QT, 1, false, false>(p, L, sm_count, stream);
     }
-    long long grid = (long long)sm_count * 8;
-    if (grid > p.N) grid = p.N;
     if (which) *which = 1;
-    viterbi_generic_kernel<QT><<<dim3((unsigned)grid), VG_THREADS, 0, stream>>>(p);
+    viterbi_generic_kernel<QT, float><<<dim3((unsigned)grid), VG_THREADS, 0, stream>>>(p);
     return cudaGetLastError();
 }
 

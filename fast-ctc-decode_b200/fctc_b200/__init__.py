@@ -33,6 +33,10 @@ _SIGNATURES = {
                                             _i64, _vp, _vp, _vp, _vp]),
     "fctc_viterbi_batch": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _i32, _f32, _f32, _i32, _vp, _vp, _i32, _vp, _i64,
                                      _vp, _vp, _vp, _vp]),
+    "fctc_viterbi_batch_device_f16": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _i32, _f32, _f32, _i32, _vp, _vp, _i32,
+                                                _vp, _i64, _vp, _vp, _vp, _vp]),
+    "fctc_viterbi_batch_f16": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _i32, _f32, _f32, _i32, _vp, _vp, _i32, _vp, _i64,
+                                         _vp, _vp, _vp, _vp]),
     "fctc_viterbi_search": (C.c_int, [_vp, _vp, _i64, _i32, _i64, _i64, _i32, _f32, _f32, _i32, _vp, _vp, _vp, _i64,
                                       _vp]),
     "fctc_beam_scratch_bytes": (_i64, [_vp, _i64, _i64, _i32, _i32, _i32]),
@@ -142,11 +146,12 @@ class Decoder:
 
     def viterbi_batch_device(self, post_ptr, n_reads, n_rows, n_labels, qstring, qscale, qbias, collapse_repeats,
                              labels_ptr, quals_ptr, qual_bytes, path_ptr, pool_capacity, offsets_ptr, lens_ptr,
-                             status_ptr, stream=0):
-        self._check(self._L.fctc_viterbi_batch_device(self._h, post_ptr, n_reads, n_rows, n_labels, int(qstring),
-                                                      qscale, qbias, int(collapse_repeats), labels_ptr,
-                                                      quals_ptr or None, qual_bytes, path_ptr, pool_capacity,
-                                                      offsets_ptr, lens_ptr, status_ptr, stream or None))
+                             status_ptr, stream=0, f16=False):
+        """f16=True: post_ptr addresses binary16 posteriors (fctc_viterbi_batch_device_f16)."""
+        fn = self._L.fctc_viterbi_batch_device_f16 if f16 else self._L.fctc_viterbi_batch_device
+        self._check(fn(self._h, post_ptr, n_reads, n_rows, n_labels, int(qstring), qscale, qbias, int(collapse_repeats),
+                       labels_ptr, quals_ptr or None, qual_bytes, path_ptr, pool_capacity, offsets_ptr, lens_ptr,
+                       status_ptr, stream or None))
 
     def beam_scratch_bytes(self, n_reads, n_rows, n_labels, beam_size, nodes_per_row=0):
         return int(self._L.fctc_beam_scratch_bytes(self._h, n_reads, n_rows, n_labels, beam_size, nodes_per_row))
@@ -190,9 +195,13 @@ class Decoder:
     # ---- host-memory batch API ------------------------------------------------------------------
     def viterbi_batch(self, post, qstring=False, qscale=1.0, qbias=0.0, collapse_repeats=True, qual_bytes=1,
                       out=None):
-        """post: C-contiguous float32 [N, T, C] (numpy; pinned memory gives full copy overlap).
+        """post: C-contiguous float32 — or float16, decoded as the exactly widened float32 values —
+        [N, T, C] (numpy; pinned memory gives full copy overlap).
         Returns dict(labels, quals, path, offsets, lens, status, used)."""
-        post = _as_f32_3d(post)
+        f16 = getattr(post, "dtype", None) == np.float16
+        post = np.ascontiguousarray(post) if f16 else _as_f32_3d(post)
+        if post.ndim != 3:
+            raise ValueError("posteriors must be [N, T, C]")
         N, T, Cn = post.shape
         cap = N * round_up32(T)
         o = out or {}
@@ -210,11 +219,10 @@ class Decoder:
         status = o.get("status", None)
         status = np.empty(N, np.int32) if status is None else status
         used = _i64(0)
-        self._check(self._L.fctc_viterbi_batch(self._h, post.ctypes.data, N, T, Cn, int(qstring), qscale, qbias,
-                                               int(collapse_repeats), labels.ctypes.data,
-                                               _np_ptr(quals) if qstring else None, qual_bytes, path.ctypes.data,
-                                               labels.size, offsets.ctypes.data, lens.ctypes.data,
-                                               status.ctypes.data, C.byref(used)))
+        fn = self._L.fctc_viterbi_batch_f16 if f16 else self._L.fctc_viterbi_batch
+        self._check(fn(self._h, post.ctypes.data, N, T, Cn, int(qstring), qscale, qbias, int(collapse_repeats),
+                       labels.ctypes.data, _np_ptr(quals) if qstring else None, qual_bytes, path.ctypes.data,
+                       labels.size, offsets.ctypes.data, lens.ctypes.data, status.ctypes.data, C.byref(used)))
         return dict(labels=labels, quals=quals if qstring else None, path=path, offsets=offsets, lens=lens,
                     status=status, used=used.value)
 

@@ -99,6 +99,23 @@ int fctc_viterbi_batch(fctc_handle* h, const float* post_host, int64_t n_reads, 
                        void* quals, int32_t qual_bytes, int32_t* path, int64_t pool_capacity, int64_t* offsets,
                        int32_t* lens, int32_t* status, int64_t* pool_used);
 
+/* fctc_viterbi_batch_device_f16 / fctc_viterbi_batch_f16: the same two calls for posteriors stored as
+ *   IEEE binary16 (the precision basecallers compute their scores in) — SURVEY.md section 8(f) rank 2,
+ *   no counterpart in the reference, whose functions take float32 arrays only (src/lib.rs:171).  Every
+ *   value is widened exactly to float32 before use, so the result is, bit for bit, what the reference
+ *   returns for the widened array; what changes is the traffic: 10 instead of 20 bytes per row over
+ *   PCIe and HBM.  Five labels with n_rows % 8 == 0 take the streaming kernel, other shapes a
+ *   slower generic one. */
+int fctc_viterbi_batch_device_f16(fctc_handle* h, const void* post_dev_f16, int64_t n_reads, int64_t n_rows,
+                                  int32_t n_labels, int32_t qstring, float qscale, float qbias,
+                                  int32_t collapse_repeats, uint8_t* labels_dev, void* quals_dev, int32_t qual_bytes,
+                                  int32_t* path_dev, int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev,
+                                  int32_t* status_dev, void* stream);
+int fctc_viterbi_batch_f16(fctc_handle* h, const void* post_host_f16, int64_t n_reads, int64_t n_rows, int32_t n_labels,
+                           int32_t qstring, float qscale, float qbias, int32_t collapse_repeats, uint8_t* labels,
+                           void* quals, int32_t qual_bytes, int32_t* path, int64_t pool_capacity, int64_t* offsets,
+                           int32_t* lens, int32_t* status, int64_t* pool_used);
+
 /* fctc_viterbi_search: one read, any strides (in elements) — the shape of the pyo3 entry point
  *   src/lib.rs:171-212.  labels/quals/path hold `capacity` entries (n_rows always suffices).
  *   Returns the decode status; n_rows == 0 or n_labels == 0 gives FCTC_E_ARGUMENT (the reference

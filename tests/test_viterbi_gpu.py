@@ -193,3 +193,50 @@ def test_device_batch_synthetic_large(dec, oracle):
         emitted = ((arg != 0) & (arg != prev)).sum(dim=1).cpu().numpy()
         assert np.array_equal(emitted, lens_np)
         del post
+
+
+# ---- binary16 posteriors: decoded as the exactly widened float32 values ----
+F16_CASES = [
+    # N, T, C, qstring, collapse
+    (40, 4000, 5, True, True), (33, 1024, 5, True, False), (17, 8, 5, True, True), (9, 4008, 5, False, True),
+    (12, 999, 5, True, True),   # T % 8 != 0: generic kernel
+    (6, 640, 4, True, True), (5, 300, 12, True, True), (3, 1, 5, True, True),
+]
+
+
+@pytest.mark.parametrize("case", F16_CASES, ids=lambda c: "N{}_T{}_C{}_q{}_c{}".format(*c))
+@pytest.mark.parametrize("kind", ["softmax", "peaked"])
+def test_f16_posteriors_host_batch(dec, oracle, case, kind):
+    N, T, Cn, qstring, collapse = case
+    rng = np.random.default_rng(1000 + N + T + Cn)
+    post = softmax_posteriors(rng, (N, T, Cn)) if kind == "softmax" else peaked_posteriors(rng, (N, T, Cn))
+    half = post.astype(np.float16)
+    half[0, T // 2] = np.float16(np.nan)      # non-finite rows travel through the widening unchanged
+    half[-1, 0] = np.float16(np.inf)
+    res = dec.viterbi_batch(half, qstring, 0.7, 2.0, collapse)
+    check_batch(oracle, half.astype(np.float32), res, qstring, 0.7, 2.0, collapse)
+
+
+def test_f16_posteriors_device_batch(dec, oracle):
+    import torch
+    N, T, Cn = 3000, 4000, 5
+    dev = torch.device("cuda:0")
+    st = torch.cuda.current_stream().cuda_stream
+    post = torch.empty((N, T, Cn), dtype=torch.float32, device=dev)
+    dec.synth_posteriors_device(post.data_ptr(), N, T, Cn, 0, 77, 0, st)
+    half = post.half()
+    stride = (T + 31) // 32 * 32
+    cap = N * stride
+    labels = torch.empty(cap, dtype=torch.uint8, device=dev)
+    quals = torch.empty(cap, dtype=torch.uint8, device=dev)
+    path = torch.empty(cap, dtype=torch.int32, device=dev)
+    offsets = torch.empty(N, dtype=torch.int64, device=dev)
+    lens = torch.empty(N, dtype=torch.int32, device=dev)
+    status = torch.empty(N, dtype=torch.int32, device=dev)
+    dec.viterbi_batch_device(half.data_ptr(), N, T, Cn, True, 1.0, 0.0, True, labels.data_ptr(), quals.data_ptr(), 1,
+                             path.data_ptr(), cap, offsets.data_ptr(), lens.data_ptr(), status.data_ptr(), st, f16=True)
+    torch.cuda.synchronize()
+    res = dict(labels=labels.cpu().numpy(), quals=quals.cpu().numpy(), path=path.cpu().numpy(),
+               offsets=offsets.cpu().numpy(), lens=lens.cpu().numpy(), status=status.cpu().numpy())
+    reads = list(range(0, N, 37))
+    check_batch(oracle, half.float().cpu().numpy(), res, True, 1.0, 0.0, True, reads=reads)
