@@ -42,6 +42,11 @@ WORKLOADS = {
     "viterbi": dict(reads=1_000_000, T=4000, C=5, kind="viterbi", qstring=1, qscale=0.7, qbias=2.0, collapse=1,
                     cpu_sample=32768, e2e_reads=32768,
                     label="viterbi 1M reads x T=4000 x C=5 f32, qstring qscale=0.7 qbias=2.0, collapse_repeats"),
+    # the same decode over binary16 posteriors (10 B/row); not the headline metric
+    "viterbi_f16": dict(reads=1_000_000, T=4000, C=5, kind="viterbi", qstring=1, qscale=0.7, qbias=2.0, collapse=1,
+                        cpu_sample=32768, e2e_reads=32768, f16=1,
+                        label="viterbi 1M reads x T=4000 x C=5 binary16 posteriors (widened exactly to f32), qstring "
+                              "qscale=0.7 qbias=2.0, collapse_repeats"),
     "beam5": dict(reads=262_144, T=4000, C=5, kind="beam", beam=5, thr=0.1, collapse=1, cpu_sample=2048,
                   e2e_reads=65536, label="beam_search 262,144 reads x T=4000 x C=5, beam_size=5, beam_cut_threshold=0.1"),
     "beam32": dict(reads=65_536, T=10_000, C=5, kind="beam", beam=32, thr=0.0, collapse=1, cpu_sample=128,
@@ -233,10 +238,22 @@ def run_ours(args, w):
     stride = (T + 31) // 32 * 32
 
     # ---- resident synthetic input: rank r decodes reads [r*N, (r+1)*N) of the global job ----------
-    post = torch.empty((N, T, Cn), dtype=torch.float32, device=dev)
     from fctc_b200.sharding import weak_shard_first_read
-    dec.synth_posteriors_device(post.data_ptr(), N, T, Cn, 1 if w["kind"] == "duplex" else 0, SEED,
-                                weak_shard_first_read(N, rank), stream)
+    f16 = bool(w.get("f16"))
+    eb = 2 if f16 else 4  # bytes per posterior
+    if f16:  # generate in float32 chunk by chunk, keep the binary16 rounding of every value
+        post = torch.empty((N, T, Cn), dtype=torch.float16, device=dev)
+        chunk = 65536
+        tmp = torch.empty((min(chunk, N), T, Cn), dtype=torch.float32, device=dev)
+        for lo in range(0, N, chunk):
+            cnt = min(chunk, N - lo)
+            dec.synth_posteriors_device(tmp.data_ptr(), cnt, T, Cn, 0, SEED, weak_shard_first_read(N, rank) + lo, stream)
+            post[lo:lo + cnt].copy_(tmp[:cnt])
+        del tmp
+    else:
+        post = torch.empty((N, T, Cn), dtype=torch.float32, device=dev)
+        dec.synth_posteriors_device(post.data_ptr(), N, T, Cn, 1 if w["kind"] == "duplex" else 0, SEED,
+                                    weak_shard_first_read(N, rank), stream)
     cap = N * stride
     labels = torch.empty(cap, dtype=torch.uint8, device=dev)
     path = torch.empty(cap, dtype=torch.int32, device=dev)
@@ -251,7 +268,7 @@ def run_ours(args, w):
         def step():
             dec.viterbi_batch_device(post.data_ptr(), N, T, Cn, w["qstring"], w["qscale"], w["qbias"], w["collapse"],
                                      labels.data_ptr(), quals.data_ptr(), 1, path.data_ptr(), cap, offsets.data_ptr(),
-                                     lens.data_ptr(), status.data_ptr(), stream)
+                                     lens.data_ptr(), status.data_ptr(), stream, f16=f16)
         launches_per_step = 1
     elif w["kind"] == "duplex":
         T2 = w["T2"]
@@ -316,7 +333,7 @@ def run_ours(args, w):
     emitted = int(lens.sum(dtype=torch.int64).item())
     ok_reads = int((status == 0).sum().item())
     out_per_label = (1 + 4 + (1 if w.get("qstring") else 0))
-    alg_bytes = N * T * Cn * 4 + emitted * out_per_label + N * 16
+    alg_bytes = N * T * Cn * eb + emitted * out_per_label + N * 16
     if w["kind"] == "duplex":  # two posterior arrays + the envelope in, labels out
         alg_bytes = N * (T + w["T2"]) * Cn * 4 + N * T * 16 + emitted + N * 16
     mean_launch_ms = float(np.mean(step_ms))
@@ -332,14 +349,15 @@ def run_ours(args, w):
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                 "frac": achieved / peaks["hbm_gbs"], "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg_bytes, "mean_launch_ms": mean_launch_ms,
-                "input_stream_gbs": N * T * Cn * 4 / (mean_launch_ms * 1e-3) / 1e9}
+                "input_stream_gbs": N * T * Cn * eb / (mean_launch_ms * 1e-3) / 1e9}
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32 (binary16 input widened exactly)" if f16 else "f32",
             "data": "synthetic",
             "config": {"workload": w["label"], "reads_per_gpu": N, "rows_per_read": T, "labels": Cn,
                        "input": "device generator, softmax(3(2u-1)) rows, seed 0xC7C00001",
-                       "l2": f"input {N * T * Cn * 4 / 1e9:.1f} GB per GPU is larger than the 126 MB L2 (no flush needed)",
+                       "l2": f"input {N * T * Cn * eb / 1e9:.1f} GB per GPU is larger than the 126 MB L2 (no flush needed)",
                        "parallelism": f"reads sharded over {world} GPU(s), no collective",
                        "emitted_labels_per_row": emitted / (N * T), "reads_ok": ok_reads},
             "clocks": clocks, "gpu_launches": launches_per_step * args.steps, "roofline": roofline}
@@ -347,7 +365,7 @@ def run_ours(args, w):
     # ---- end to end through the C ABI with pinned HOST buffers (copies inside the timed region);
     #      every rank streams its own shard, time = max over ranks ------------------------------------
     ne = min(w["e2e_reads"], N)
-    hpost = torch.empty((ne, T, Cn), dtype=torch.float32).pin_memory()
+    hpost = torch.empty((ne, T, Cn), dtype=post.dtype).pin_memory()
     hpost.copy_(post[:ne])
     hnp = hpost.numpy()
     hcap = ne * stride
@@ -386,7 +404,7 @@ def run_ours(args, w):
         tt = torch.tensor([dt], dtype=torch.float64, device=dev)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         dt = float(tt.item())
-    h2d = ne * T * Cn * 4
+    h2d = ne * T * Cn * eb
     if w["kind"] == "viterbi":
         d2h = hcap * (1 + 4 + (1 if w["qstring"] else 0)) + ne * 16
     elif w["kind"] == "duplex":
@@ -404,6 +422,8 @@ def run_ours(args, w):
         nc = min(w["cpu_sample"], ne)
         threads = host_threads()
         sample = (hnp[:nc], hnp2[:nc], henv[:nc]) if w["kind"] == "duplex" else hnp[:nc]
+        if f16:  # the CPU path only takes float32: it decodes the widened sample (widening outside its timed region)
+            sample = sample.astype(np.float32)
         rate, dtc = cpu_rate(w, sample, threads)
         line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": threads, "kind": "port",
                                 "sample": f"first {nc} reads of rank 0's shard ({nc * T} rows, {dtc:.1f} s), one read per "
