@@ -340,16 +340,24 @@ def run_ours(args, w):
     peaks, peak_src = measured_peaks()
     achieved = alg_bytes / (mean_launch_ms * 1e-3) / 1e9
     traffic = None
+    tj = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
         with open(tpath) as f:
             tj = json.load(f).get(args.workload)
-        if tj:
+        if tj and "dram_bytes_per_read" in tj:
             traffic = tj["dram_bytes_per_read"] * N
+        elif tj and "dram_bytes_per_row" in tj:
+            traffic = tj["dram_bytes_per_row"] * N * T
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                 "frac": achieved / peaks["hbm_gbs"], "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg_bytes, "mean_launch_ms": mean_launch_ms,
                 "input_stream_gbs": N * T * Cn * eb / (mean_launch_ms * 1e-3) / 1e9}
+    if tj and "issue_slots_busy" in tj:
+        # the searches are bound by instruction issue, not by HBM: the ncu capture's issue-slot utilisation and
+        # warp-instructions per row say how far the kernel is from that limit (profiles/, not measured live)
+        roofline["sm_issue_slots_busy_ncu"] = tj["issue_slots_busy"]
+        roofline["warp_instructions_per_row_ncu"] = tj["warp_instructions_per_row"]
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,

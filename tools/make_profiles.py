@@ -22,6 +22,9 @@ REPORTS = [
     ("beam5_i.ncu-rep", "beam_small_b5", 18944 * 2000, "posterior row (18,944 reads x 2000 rows, beam 5, threshold 0.1)"),
     ("duplex_b.ncu-rep", "duplex", 3552 * 1000, "network-1 row (3,552 pairs x 1000 rows, band +-32, beam 5, exact exp)"),
 ]
+# profile name -> (bench.py workload, posterior rows of the profiled launch)
+WORKLOAD_OF = {"viterbi_stream": ("viterbi", 65536 * 4000), "beam_wide_b32": ("beam32", 3552 * 2000),
+               "beam_small_b5": ("beam5", 18944 * 2000), "duplex": ("duplex", 3552 * 1000)}
 
 
 def run(cmd):
@@ -44,12 +47,20 @@ for rep, name, units, what in REPORTS:
         for h, u, v in sorted(zip(rows[0], rows[1], rows[2])):
             if "__" in h and v not in ("", "n/a"):
                 f.write(f"{h},{u},{v}\n")
+    h = rows[0]
+    val = lambda k: float(rows[2][h.index(k)].replace(",", "")) * {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1}.get(rows[1][h.index(k)], 1)
+    traffic = val("dram__bytes_read.sum") + val("dram__bytes_write.sum")
+    tj = os.path.join(OUT, "traffic.json")
+    d = json.load(open(tj))
+    wl, wrows = WORKLOAD_OF[name]
+    e = d.setdefault(wl, {})
+    e["issue_slots_busy"] = val("smsp__issue_active.avg.pct_of_peak_sustained_active") / 100
+    e["warp_instructions_per_row"] = val("smsp__inst_executed.sum") / wrows
+    if name != "viterbi_stream":
+        e["dram_bytes_per_row"] = traffic / wrows
+        e["source"] = f"profiles/{tag}_{name}_ncu_raw_metrics.csv: one launch, {what} (ncu --set full)"
+    json.dump(d, open(tj, "w"), indent=1)
     if name == "viterbi_stream":
-        h = rows[0]
-        val = lambda k: float(rows[2][h.index(k)].replace(",", "")) * {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1}[rows[1][h.index(k)]]
-        traffic = val("dram__bytes_read.sum") + val("dram__bytes_write.sum")
-        tj = os.path.join(OUT, "traffic.json")
-        d = json.load(open(tj))
         d["viterbi"]["dram_bytes_per_read"] = traffic / 65536
         d["viterbi"]["source"] = (f"profiles/{tag}_viterbi_stream_ncu_raw_metrics.csv: dram__bytes_read.sum + dram__bytes_write.sum of one "
                                   "launch over 65,536 reads x 4000 x 5 (ncu --set full, bench.py --reads 65536); traffic is linear in "
