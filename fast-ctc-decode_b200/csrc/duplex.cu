@@ -168,8 +168,11 @@ __device__ __forceinline__ DxCell dx_step(const DxCell& last, float pgap, float 
 // hypothesis carries a transition state, rows are read at [t][state], a label moves the state to
 // (state * n_base) % n_state + label, and there is no repeat case.  Network-2 values are mapped to
 // log space on the fly there (a [T2, S, C] log table per pair would not fit the scratch).
+#ifndef DX_MINBLOCKS
+#define DX_MINBLOCKS 6
+#endif
 template <bool CRF>
-__global__ void __launch_bounds__(DX_THREADS, 6) duplex_search_kernel(const DuplexParams p, const DuplexLayout L) {
+__global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel(const DuplexParams p, const DuplexLayout L) {
     extern __shared__ __align__(16) unsigned char smem[];
     double* s_invc = reinterpret_cast<double*>(smem);
     double* s_logc = s_invc + 16;
