@@ -229,9 +229,19 @@ def run_ours(args, w):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
-        # stdout carries exactly one JSON line: NCCL's own banner / debug lines go to stderr
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
-        dist.init_process_group("nccl", device_id=dev)
+        # stdout carries exactly one JSON line: while the communicator comes up (NCCL prints its version
+        # banner and any NCCL_DEBUG output to stdout) file descriptor 1 points at stderr
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=dev)
+            dist.barrier()
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved_stdout, 1)
+            os.close(saved_stdout)
     dec = fctc_b200.Decoder(local_rank)
     N, T, Cn = args.reads or w["reads"], w["T"], w["C"]
     stream = torch.cuda.current_stream().cuda_stream
