@@ -49,7 +49,7 @@ __host__ __device__ inline size_t beam_slot_bytes(long long cap, int NL) {
 
 struct BeamLayout {  // per-warp shared memory plan, in bytes from the warp's base
     int beam_stride;  // one beam buffer: 6 arrays of B words
-    int off_newcnt, off_fold, off_key, off_node, off_lp, off_gp, off_src, off_sel, off_srec, off_slo, off_rows, off_root;
+    int off_newcnt, off_fold, off_key, off_node, off_lp, off_gp, off_src, off_sel, off_srec, off_rows, off_root;
     int warp_bytes;
     int rows_per_chunk;
 };
@@ -106,9 +106,8 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
     float* clp = reinterpret_cast<float*>(ws + L.off_lp);
     float* cgp = reinterpret_cast<float*>(ws + L.off_gp);
     int* sel = reinterpret_cast<int*>(ws + L.off_sel);
-    // per-lane ranked candidate lists: (C + 1) x {score key, candidate slot}, and the node-id tie keys
+    // per-lane ranked candidate lists: (C + 1) x {score key, candidate slot}
     const uint32_t srec_base = smem_u32(ws + L.off_srec);
-    uint32_t* slo = reinterpret_cast<uint32_t*>(ws + L.off_slo);
     float* rowbuf = reinterpret_cast<float*>(ws + L.off_rows);
     int* root_child = reinterpret_cast<int*>(ws + L.off_root);
 
@@ -376,7 +375,6 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
 #pragma unroll
                             for (int j = 0; j < 5; ++j) {
                                 sts_v2(list0 + 8u * uint32_t(rank[j]), hi[j], uint32_t(base + j));
-                                slo[lane * (C + 1) + rank[j]] = lo[j];
                             }
                         } else {
                             for (int j = 0; j < C; ++j) {
@@ -391,11 +389,9 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
                                     rk += y_first ? 1 : 0;
                                 }
                                 sts_v2(list0 + 8u * uint32_t(rk), hj, uint32_t(base + j));
-                                slo[lane * (C + 1) + rk] = lj;
                             }
                         }
                         sts_v2(list0 + 8u * uint32_t(C), 0u, 0u);
-                        slo[lane * (C + 1) + C] = 0u;
                     }
                     uint32_t head = list0;
                     uint32_t cur_hi = 0u, cur_idx = 0u;
@@ -430,7 +426,8 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
                             const uint32_t m1 = __reduce_max_sync(FULL, cur_hi);
                             unsigned who = __ballot_sync(FULL, cur_hi == m1);
                             if (who & (who - 1)) {  // several lanes share the top score: lowest node id wins
-                                const uint32_t my_lo = (cur_hi == m1) ? slo[(head - srec_base) >> 3] : 0u;
+                                // the tie key: lower node id ranks first (list heads carry the candidate's slot)
+                                const uint32_t my_lo = (cur_hi == m1 && cur_hi != 0u) ? 0x7FFFFFFFu - uint32_t(cnode[cur_idx]) : 0u;
                                 const uint32_t m2 = __reduce_max_sync(FULL, my_lo);
                                 who = __ballot_sync(FULL, cur_hi == m1 && my_lo == m2);
                             }
@@ -544,7 +541,6 @@ static bool plan_beam(int B, int C, BeamLayout* L) {
     L->off_src = int(o);
     L->off_sel = int(o);    o = up(o + 4LL * B, 16);
     L->off_srec = int(o);   o = up(o + 8LL * 32 * (C + 1), 16);
-    L->off_slo = int(o);    o = up(o + 4LL * 32 * (C + 1), 16);
     L->off_rows = int(o);   o = up(o + 2LL * BM_ROWBUF * 4, 16);
     L->off_root = int(o);   o = up(o + 4LL * (NL > 0 ? NL : 1), 16);
     L->warp_bytes = int(up(o, 128));
