@@ -295,9 +295,10 @@ int drain_slot(fctc_handle* h, Slot& s, HostOut& out) {
 // slot.stream, writing slot.{labels,quals,path,offsets,lens,status,cursor}.
 // Reads [src_first, src_first + n) of post_host go to result rows [dst_first, ...).
 template <class Launch>
-int host_pipeline(fctc_handle* h, const float* post_host, int64_t n_reads, int64_t n_rows, int32_t n_labels,
-                  HostOut& out, int64_t chunk, Launch&& launch) {
-    const int64_t read_bytes = n_rows * int64_t(n_labels) * 4;
+int host_pipeline(fctc_handle* h, const void* post_host_any, int elem_bytes, int64_t n_reads, int64_t n_rows,
+                  int32_t n_labels, HostOut& out, int64_t chunk, Launch&& launch) {
+    const unsigned char* post_host = static_cast<const unsigned char*>(post_host_any);
+    const int64_t read_bytes = n_rows * int64_t(n_labels) * elem_bytes;
     const int64_t slot_entries = roundup32(n_rows);
     chunk = std::max<int64_t>(1, std::min(chunk, n_reads));
     for (int i = 0; i < 2; ++i) {
@@ -345,7 +346,7 @@ int host_pipeline(fctc_handle* h, const float* post_host, int64_t n_reads, int64
         s.count = cnt;
         mark(s.stream);
         if (read_bytes > 0)
-            FCTC_CUDA(h, cudaMemcpyAsync(s.post.p, post_host + first * n_rows * n_labels, size_t(cnt * read_bytes),
+            FCTC_CUDA(h, cudaMemcpyAsync(s.post.p, post_host + first * read_bytes, size_t(cnt * read_bytes),
                                          cudaMemcpyHostToDevice, s.stream));
         mark(s.stream);
         FCTC_CUDA(h, cudaMemsetAsync(s.cursor.p, 0, 8, s.stream));
@@ -599,12 +600,13 @@ int64_t fctc_beam_scratch_bytes(const fctc_handle* h, int64_t n_reads, int64_t n
                                     nullptr, nullptr);
 }
 
-int fctc_beam_search_batch_device(fctc_handle* h, const float* post_dev, int64_t n_reads, int64_t n_rows,
-                                  int32_t n_labels, int32_t beam_size, float beam_cut_threshold,
-                                  int32_t collapse_repeats, uint8_t* labels_dev, int32_t* path_dev,
-                                  int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev, int32_t* status_dev,
-                                  unsigned long long* pool_used_dev, void* scratch_dev, int64_t scratch_bytes,
-                                  int32_t nodes_per_row, void* stream) {
+namespace {
+int beam_search_batch_device_any(fctc_handle* h, const void* post_dev, int in_f16, int64_t n_reads, int64_t n_rows,
+                                 int32_t n_labels, int32_t beam_size, float beam_cut_threshold,
+                                 int32_t collapse_repeats, uint8_t* labels_dev, int32_t* path_dev,
+                                 int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev, int32_t* status_dev,
+                                 unsigned long long* pool_used_dev, void* scratch_dev, int64_t scratch_bytes,
+                                 int32_t nodes_per_row, void* stream) {
     if (int rc = check_common(h, n_reads, n_rows, n_labels)) return rc;
     if (int rc = check_beam(h, n_labels, beam_size, beam_cut_threshold)) return rc;
     if (!post_dev || !labels_dev || !path_dev || !offsets_dev || !lens_dev || !status_dev || !pool_used_dev || !scratch_dev)
@@ -617,7 +619,8 @@ int fctc_beam_search_batch_device(fctc_handle* h, const float* post_dev, int64_t
     if (scratch_bytes < need)
         return fail(h, FCTC_E_CAPACITY, "beam scratch too small: %lld bytes given, %lld needed", (long long)scratch_bytes,
                     (long long)need);
-    p.post = post_dev; p.N = n_reads; p.T = n_rows; p.C = n_labels; p.beam_size = beam_size;
+    p.post = static_cast<const float*>(post_dev); p.in_f16 = in_f16; p.N = n_reads; p.T = n_rows; p.C = n_labels;
+    p.beam_size = beam_size;
     p.threshold = beam_cut_threshold; p.collapse = collapse_repeats; p.labels = labels_dev; p.path = path_dev;
     p.pool_cap = pool_capacity; p.offsets = offsets_dev; p.lens = lens_dev; p.status = status_dev;
     p.cursor = pool_used_dev; p.scratch = scratch_dev; p.scratch_bytes = scratch_bytes;
@@ -625,15 +628,39 @@ int fctc_beam_search_batch_device(fctc_handle* h, const float* post_dev, int64_t
     FCTC_CUDA(h, fctc::launch_beam(p, h->sm_count, static_cast<cudaStream_t>(stream)));
     return 0;
 }
+}  // namespace
+
+int fctc_beam_search_batch_device(fctc_handle* h, const float* post_dev, int64_t n_reads, int64_t n_rows,
+                                  int32_t n_labels, int32_t beam_size, float beam_cut_threshold,
+                                  int32_t collapse_repeats, uint8_t* labels_dev, int32_t* path_dev,
+                                  int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev, int32_t* status_dev,
+                                  unsigned long long* pool_used_dev, void* scratch_dev, int64_t scratch_bytes,
+                                  int32_t nodes_per_row, void* stream) {
+    return beam_search_batch_device_any(h, post_dev, 0, n_reads, n_rows, n_labels, beam_size, beam_cut_threshold,
+                                        collapse_repeats, labels_dev, path_dev, pool_capacity, offsets_dev, lens_dev,
+                                        status_dev, pool_used_dev, scratch_dev, scratch_bytes, nodes_per_row, stream);
+}
+
+int fctc_beam_search_batch_device_f16(fctc_handle* h, const void* post_dev_f16, int64_t n_reads, int64_t n_rows,
+                                      int32_t n_labels, int32_t beam_size, float beam_cut_threshold,
+                                      int32_t collapse_repeats, uint8_t* labels_dev, int32_t* path_dev,
+                                      int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev,
+                                      int32_t* status_dev, unsigned long long* pool_used_dev, void* scratch_dev,
+                                      int64_t scratch_bytes, int32_t nodes_per_row, void* stream) {
+    return beam_search_batch_device_any(h, post_dev_f16, 1, n_reads, n_rows, n_labels, beam_size, beam_cut_threshold,
+                                        collapse_repeats, labels_dev, path_dev, pool_capacity, offsets_dev, lens_dev,
+                                        status_dev, pool_used_dev, scratch_dev, scratch_bytes, nodes_per_row, stream);
+}
 
 namespace {
 
-int beam_host_pass(fctc_handle* h, const float* post_host, int64_t n_reads, int64_t n_rows, int32_t n_labels,
+int beam_host_pass(fctc_handle* h, const void* post_host, int in_f16, int64_t n_reads, int64_t n_rows, int32_t n_labels,
                    int32_t beam_size, float thr, int32_t collapse, int32_t nodes_per_row, HostOut& out) {
+    const int elem_bytes = in_f16 ? 2 : 4;
     const int64_t slot_entries = std::max<int64_t>(roundup32(n_rows), 32);
     // The search keeps one read per resident warp busy for the read's whole length, so a chunk must hold
     // several reads per warp slot (a 64 MiB chunk would leave most of the GPU idle); capped at 2 GiB.
-    const int64_t read_bytes = std::max<int64_t>(n_rows * int64_t(n_labels) * 4, 1);
+    const int64_t read_bytes = std::max<int64_t>(n_rows * int64_t(n_labels) * elem_bytes, 1);
     int64_t chunk = std::max<int64_t>(default_chunk_reads(read_bytes), int64_t(h->sm_count) * 24 * 4);
     chunk = std::min<int64_t>(chunk, std::max<int64_t>((int64_t(2) << 30) / read_bytes, 1));
     if (const char* e = getenv("FCTC_BEAM_CHUNK_READS")) chunk = atoll(e) > 0 ? atoll(e) : chunk;  // tuning knob
@@ -651,7 +678,7 @@ int beam_host_pass(fctc_handle* h, const float* post_host, int64_t n_reads, int6
     auto launch = [&](Slot& s, int64_t cnt) -> int {
         fctc::BeamParams p{};
         fctc::beam_scratch_bytes(h->sm_count, cnt, n_rows, n_labels, beam_size, nodes_per_row, need, &p.nodes_per_slot, &p.n_slots);
-        p.post = static_cast<const float*>(s.post.p); p.N = cnt; p.T = n_rows; p.C = n_labels;
+        p.post = static_cast<const float*>(s.post.p); p.in_f16 = in_f16; p.N = cnt; p.T = n_rows; p.C = n_labels;
         p.beam_size = beam_size; p.threshold = thr; p.collapse = collapse;
         p.labels = static_cast<uint8_t*>(s.labels.p); p.path = static_cast<int32_t*>(s.path.p);
         p.pool_cap = cnt * slot_entries; p.offsets = static_cast<int64_t*>(s.offsets.p);
@@ -661,15 +688,14 @@ int beam_host_pass(fctc_handle* h, const float* post_host, int64_t n_reads, int6
         FCTC_CUDA(h, fctc::launch_beam(p, h->sm_count, s.stream));
         return 0;
     };
-    return host_pipeline(h, post_host, n_reads, n_rows, n_labels, out, chunk, launch);
+    return host_pipeline(h, post_host, elem_bytes, n_reads, n_rows, n_labels, out, chunk, launch);
 }
 
-}  // namespace
-
-int fctc_beam_search_batch(fctc_handle* h, const float* post_host, int64_t n_reads, int64_t n_rows, int32_t n_labels,
-                           int32_t beam_size, float beam_cut_threshold, int32_t collapse_repeats, uint8_t* labels,
-                           int32_t* path, int64_t pool_capacity, int64_t* offsets, int32_t* lens, int32_t* status,
-                           int64_t* pool_used) {
+int beam_search_batch_any(fctc_handle* h, const void* post_host_any, int in_f16, int64_t n_reads, int64_t n_rows,
+                          int32_t n_labels, int32_t beam_size, float beam_cut_threshold, int32_t collapse_repeats,
+                          uint8_t* labels, int32_t* path, int64_t pool_capacity, int64_t* offsets, int32_t* lens,
+                          int32_t* status, int64_t* pool_used) {
+    const unsigned char* post_host = static_cast<const unsigned char*>(post_host_any);
     if (int rc = check_common(h, n_reads, n_rows, n_labels)) return rc;
     if (int rc = check_beam(h, n_labels, beam_size, beam_cut_threshold)) return rc;
     if ((!post_host && n_rows > 0) || !labels || !path || !offsets || !lens || !status)
@@ -678,8 +704,8 @@ int fctc_beam_search_batch(fctc_handle* h, const float* post_host, int64_t n_rea
     if (pool_used) *pool_used = 0;
     if (n_reads == 0) return 0;
     HostOut out{labels, nullptr, 1, path, pool_capacity, offsets, lens, status};
-    if (int rc = beam_host_pass(h, post_host, n_reads, n_rows, n_labels, beam_size, beam_cut_threshold, collapse_repeats,
-                                0, out))
+    if (int rc = beam_host_pass(h, post_host, in_f16, n_reads, n_rows, n_labels, beam_size, beam_cut_threshold,
+                                collapse_repeats, 0, out))
         return rc;
     if (!out.overflow) {
         // reads whose trie outgrew the default pool: decode again, one at a time, with the hard
@@ -689,8 +715,8 @@ int fctc_beam_search_batch(fctc_handle* h, const float* post_host, int64_t n_rea
             if (status[n] != FCTC_NODE_POOL_OVERFLOW) continue;
             HostOut one{labels, nullptr, 1, path, pool_capacity, offsets + n, lens + n, status + n};
             one.used = out.used;
-            if (int rc = beam_host_pass(h, post_host + n * n_rows * n_labels, 1, n_rows, n_labels, beam_size,
-                                        beam_cut_threshold, collapse_repeats, bound, one))
+            if (int rc = beam_host_pass(h, post_host + n * n_rows * n_labels * (in_f16 ? 2 : 4), in_f16, 1, n_rows, n_labels,
+                                        beam_size, beam_cut_threshold, collapse_repeats, bound, one))
                 return rc;
             out.used = one.used;
             out.overflow = one.overflow;
@@ -701,6 +727,24 @@ int fctc_beam_search_batch(fctc_handle* h, const float* post_host, int64_t n_rea
         return fail(h, FCTC_E_CAPACITY, "result pool too small: %lld entries given (n_reads*round_up(n_rows,32) always suffices)",
                     (long long)pool_capacity);
     return 0;
+}
+
+}  // namespace
+
+int fctc_beam_search_batch(fctc_handle* h, const float* post_host, int64_t n_reads, int64_t n_rows, int32_t n_labels,
+                           int32_t beam_size, float beam_cut_threshold, int32_t collapse_repeats, uint8_t* labels,
+                           int32_t* path, int64_t pool_capacity, int64_t* offsets, int32_t* lens, int32_t* status,
+                           int64_t* pool_used) {
+    return beam_search_batch_any(h, post_host, 0, n_reads, n_rows, n_labels, beam_size, beam_cut_threshold, collapse_repeats,
+                                 labels, path, pool_capacity, offsets, lens, status, pool_used);
+}
+
+int fctc_beam_search_batch_f16(fctc_handle* h, const void* post_host_f16, int64_t n_reads, int64_t n_rows,
+                               int32_t n_labels, int32_t beam_size, float beam_cut_threshold, int32_t collapse_repeats,
+                               uint8_t* labels, int32_t* path, int64_t pool_capacity, int64_t* offsets, int32_t* lens,
+                               int32_t* status, int64_t* pool_used) {
+    return beam_search_batch_any(h, post_host_f16, 1, n_reads, n_rows, n_labels, beam_size, beam_cut_threshold,
+                                 collapse_repeats, labels, path, pool_capacity, offsets, lens, status, pool_used);
 }
 
 int fctc_beam_search(fctc_handle* h, const float* post_host, int64_t n_rows, int32_t n_labels, int64_t stride_row,

@@ -21,6 +21,8 @@
 //     each hypothesis looks up its parent in the beam and folds that term in itself;
 //   * ranking is a warp-level selection: lanes keep their best unselected candidate, two
 //     REDUX.MAX per rank pick (score, then lowest node id) — no comparison sort.
+#include <cuda_fp16.h>
+
 #include "device_utils.cuh"
 #include "kernels.h"
 
@@ -85,7 +87,8 @@ __device__ __forceinline__ BeamView beam_view(unsigned char* base, int B) {
 // (state * n_base) % n_state + label, and there is no repeat-collapse case.
 // CT = compile-time label count (0 = read it from the parameters): with CT = 5, the nanopore
 // alphabet, every per-label loop unrolls and the slot arithmetic becomes constant.
-template <bool CRF, int CT>
+// HALF (plain search only): the posteriors are binary16, widened exactly to f32 as they are fetched.
+template <bool CRF, int CT, bool HALF>
 __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParams p, const BeamLayout L) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int lane = threadIdx.x & 31;
@@ -130,6 +133,8 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
         if (ticket >= (unsigned long long)p.N) break;
         const long long n = (long long)ticket;
         const float* rd = p.post + n * T * C * S;
+        const __half* rdh = reinterpret_cast<const __half*>(p.post) + n * T * C;  // the same rows when HALF
+        auto fetch = [&](long long e) -> float { return HALF ? __half2float(__ldg(rdh + e)) : __ldg(rd + e); };
 
         int cur = 0;
         BeamView bv = beam_view(ws, B);
@@ -163,7 +168,7 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
 #pragma unroll
             for (int j = 0; j < BM_ROWBUF / 32; ++j) {
                 const int e = lane + 32 * j;
-                pre[j] = (e < chunk_elems && e < total) ? __ldg(rd + e) : 0.0f;
+                pre[j] = (e < chunk_elems && e < total) ? fetch(e) : 0.0f;
             }
         }
         __syncwarp();
@@ -182,7 +187,7 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
 #pragma unroll
                 for (int j = 0; j < BM_ROWBUF / 32; ++j) {
                     const long long e = base + lane + 32 * j;
-                    pre[j] = (lane + 32 * j < chunk_elems && e < total) ? __ldg(rd + e) : 0.0f;
+                    pre[j] = (lane + 32 * j < chunk_elems && e < total) ? fetch(e) : 0.0f;
                 }
             }
             __syncwarp();
@@ -606,8 +611,10 @@ cudaError_t launch_beam(const BeamParams& p, int sm_count, cudaStream_t stream) 
     if (!plan_beam(p.beam_size, p.C, &L)) return cudaErrorInvalidConfiguration;
     const int smem = L.warp_bytes * BM_WARPS;
     const bool crf = p.S > 0;
-    auto kernel = crf ? (p.C == 5 ? beam_search_kernel<true, 5> : beam_search_kernel<true, 0>)
-                      : (p.C == 5 ? beam_search_kernel<false, 5> : beam_search_kernel<false, 0>);
+    if (crf && p.in_f16) return cudaErrorInvalidValue;  // the crf search reads its state-dependent rows directly: f32 only
+    auto kernel = crf ? (p.C == 5 ? beam_search_kernel<true, 5, false> : beam_search_kernel<true, 0, false>)
+                      : p.in_f16 ? (p.C == 5 ? beam_search_kernel<false, 5, true> : beam_search_kernel<false, 0, true>)
+                                 : (p.C == 5 ? beam_search_kernel<false, 5, false> : beam_search_kernel<false, 0, false>);
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
     e = cudaMemsetAsync(p.ticket, 0, sizeof(unsigned long long), stream);

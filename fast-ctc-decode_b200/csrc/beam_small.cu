@@ -19,6 +19,8 @@
 // child[4]}; `skip` points to the nearest proper ancestor whose depth is a multiple of 32, which
 // turns the final traceback from one dependent load per label into len/32 + 32 of them (lane j
 // walks the j-th block of 32 labels).
+#include <cuda_fp16.h>
+
 #include "device_utils.cuh"
 #include "kernels.h"
 
@@ -46,7 +48,8 @@ __device__ __forceinline__ uint32_t order_key(float v) {  // monotone map f32 ->
 #ifndef BS_MINBLOCKS
 #define BS_MINBLOCKS 8
 #endif
-template <bool CRF, int CT>
+// HALF (plain search only): the posteriors are binary16, widened exactly to f32 as they are fetched.
+template <bool CRF, int CT, bool HALF>
 __global__ void __launch_bounds__(BS_THREADS, BS_MINBLOCKS) beam_small_kernel(const BeamParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int lane = threadIdx.x & 31;
@@ -82,6 +85,8 @@ __global__ void __launch_bounds__(BS_THREADS, BS_MINBLOCKS) beam_small_kernel(co
         if (ticket >= (unsigned long long)p.N) break;
         const long long n = (long long)ticket;
         const float* rd = p.post + n * T * C * S;
+        const __half* rdh = reinterpret_cast<const __half*>(p.post) + n * T * C;  // the same rows when HALF
+        auto fetch = [&](long long e) -> float { return HALF ? __half2float(__ldg(rdh + e)) : __ldg(rd + e); };
 
         // the hypothesis of my lane group (src/search.rs:170-175: one root hypothesis, gap_prob 1)
         int nd = ROOT, par = -2, dep = 0, tip = -1, skp = ROOT, st = 0;
@@ -110,7 +115,7 @@ __global__ void __launch_bounds__(BS_THREADS, BS_MINBLOCKS) beam_small_kernel(co
 #pragma unroll
             for (int j = 0; j < BS_ROWBUF / 32; ++j) {
                 const int e = lane + 32 * j;
-                pre[j] = (e < chunk_elems && e < total) ? __ldg(rd + e) : 0.0f;
+                pre[j] = (e < chunk_elems && e < total) ? fetch(e) : 0.0f;
             }
         }
         __syncwarp();
@@ -127,7 +132,7 @@ __global__ void __launch_bounds__(BS_THREADS, BS_MINBLOCKS) beam_small_kernel(co
 #pragma unroll
                 for (int j = 0; j < BS_ROWBUF / 32; ++j) {
                     const long long e = base + lane + 32 * j;
-                    pre[j] = (lane + 32 * j < chunk_elems && e < total) ? __ldg(rd + e) : 0.0f;
+                    pre[j] = (lane + 32 * j < chunk_elems && e < total) ? fetch(e) : 0.0f;
                 }
             }
             __syncwarp();
@@ -381,8 +386,10 @@ int beam_small_warps_per_sm() {
 
 cudaError_t launch_beam_small(const BeamParams& p, cudaStream_t stream) {
     const bool crf = p.S > 0;
-    auto kernel = crf ? (p.C == 5 ? beam_small_kernel<true, 5> : beam_small_kernel<true, 0>)
-                      : (p.C == 5 ? beam_small_kernel<false, 5> : beam_small_kernel<false, 0>);
+    if (crf && p.in_f16) return cudaErrorInvalidValue;  // the crf search reads its state-dependent rows directly: f32 only
+    auto kernel = crf ? (p.C == 5 ? beam_small_kernel<true, 5, false> : beam_small_kernel<true, 0, false>)
+                      : p.in_f16 ? (p.C == 5 ? beam_small_kernel<false, 5, true> : beam_small_kernel<false, 0, true>)
+                                 : (p.C == 5 ? beam_small_kernel<false, 5, false> : beam_small_kernel<false, 0, false>);
     const int smem = BS_WARP_SMEM * BS_WARPS;
     cudaError_t e = cudaMemsetAsync(p.ticket, 0, sizeof(unsigned long long), stream);
     if (e != cudaSuccess) return e;

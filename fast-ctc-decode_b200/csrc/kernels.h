@@ -43,7 +43,8 @@ struct ViterbiParams {
 cudaError_t launch_viterbi(const ViterbiParams& p, int sm_count, cudaStream_t stream, int* which);
 
 struct BeamParams {
-    const float* post;  // [N, T, C]
+    const float* post;  // [N, T, C] (binary16 values behind the same pointer when in_f16)
+    int in_f16;         // 1: binary16 posteriors, widened exactly to f32 as they are fetched (plain search only)
     int64_t N, T;
     int C;
     int beam_size;

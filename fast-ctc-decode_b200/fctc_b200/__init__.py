@@ -46,6 +46,10 @@ _SIGNATURES = {
                                                        _vp, _vp, _vp, _vp, _i32, _vp]),
     "fctc_beam_search_batch": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _i32, _f32, _i32, _vp, _vp, _i64, _vp, _vp, _vp,
                                          _vp]),
+    "fctc_beam_search_batch_device_f16": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _i32, _f32, _i32, _vp, _vp, _i64, _vp,
+                                                    _vp, _vp, _vp, _vp, _i64, _i32, _vp]),
+    "fctc_beam_search_batch_f16": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _i32, _f32, _i32, _vp, _vp, _i64, _vp, _vp,
+                                             _vp, _vp]),
     "fctc_beam_search": (C.c_int, [_vp, _vp, _i64, _i32, _i64, _i64, _i32, _f32, _i32, _vp, _vp, _i64, _vp]),
     "fctc_duplex_scratch_bytes": (_i64, [_vp, _i64, _i64, _i64, _i32, _i32, _i32, _i32]),
     "fctc_beam_search_duplex_batch_device": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i64, _i32, _vp, _i32, _i32, _f32,
@@ -158,12 +162,13 @@ class Decoder:
 
     def beam_search_batch_device(self, post_ptr, n_reads, n_rows, n_labels, beam_size, beam_cut_threshold,
                                  collapse_repeats, labels_ptr, path_ptr, pool_capacity, offsets_ptr, lens_ptr,
-                                 status_ptr, pool_used_ptr, scratch_ptr, scratch_bytes, nodes_per_row=0, stream=0):
-        self._check(self._L.fctc_beam_search_batch_device(self._h, post_ptr, n_reads, n_rows, n_labels, beam_size,
-                                                          beam_cut_threshold, int(collapse_repeats), labels_ptr,
-                                                          path_ptr, pool_capacity, offsets_ptr, lens_ptr, status_ptr,
-                                                          pool_used_ptr, scratch_ptr, scratch_bytes, nodes_per_row,
-                                                          stream or None))
+                                 status_ptr, pool_used_ptr, scratch_ptr, scratch_bytes, nodes_per_row=0, stream=0,
+                                 f16=False):
+        """f16=True: post_ptr addresses binary16 posteriors (fctc_beam_search_batch_device_f16)."""
+        fn = self._L.fctc_beam_search_batch_device_f16 if f16 else self._L.fctc_beam_search_batch_device
+        self._check(fn(self._h, post_ptr, n_reads, n_rows, n_labels, beam_size, beam_cut_threshold, int(collapse_repeats),
+                       labels_ptr, path_ptr, pool_capacity, offsets_ptr, lens_ptr, status_ptr, pool_used_ptr, scratch_ptr,
+                       scratch_bytes, nodes_per_row, stream or None))
 
     def duplex_scratch_bytes(self, n_pairs, n_rows_1, n_rows_2, n_labels, beam_size, max_window=0, nodes_per_row=0):
         return int(self._L.fctc_duplex_scratch_bytes(self._h, n_pairs, n_rows_1, n_rows_2, n_labels, beam_size,
@@ -227,22 +232,26 @@ class Decoder:
                     status=status, used=used.value)
 
     def beam_search_batch(self, post, beam_size=5, beam_cut_threshold=0.0, collapse_repeats=True, out=None):
-        post = _as_f32_3d(post)
+        """post: C-contiguous float32 — or float16, decoded as the exactly widened float32 values — [N, T, C].
+        `out` may carry preallocated (ideally pinned) labels / path / offsets / lens / status arrays."""
+        f16 = getattr(post, "dtype", None) == np.float16
+        post = np.ascontiguousarray(post) if f16 else _as_f32_3d(post)
+        if post.ndim != 3:
+            raise ValueError("posteriors must be [N, T, C]")
         N, T, Cn = post.shape
         cap = N * round_up32(T)
         o = out or {}
-        labels = o.get("labels", None)
-        labels = np.empty(cap, np.uint8) if labels is None else labels
-        path = o.get("path", None)
-        path = np.empty(cap, np.int32) if path is None else path
-        offsets = np.empty(N, np.int64)
-        lens = np.empty(N, np.int32)
-        status = np.empty(N, np.int32)
+
+        def take(name, n, dtype):
+            a = o.get(name, None)
+            return np.empty(n, dtype) if a is None else a
+        labels, path = take("labels", cap, np.uint8), take("path", cap, np.int32)
+        offsets, lens, status = take("offsets", N, np.int64), take("lens", N, np.int32), take("status", N, np.int32)
         used = _i64(0)
-        self._check(self._L.fctc_beam_search_batch(self._h, post.ctypes.data, N, T, Cn, beam_size, beam_cut_threshold,
-                                                   int(collapse_repeats), labels.ctypes.data, path.ctypes.data,
-                                                   labels.size, offsets.ctypes.data, lens.ctypes.data,
-                                                   status.ctypes.data, C.byref(used)))
+        fn = self._L.fctc_beam_search_batch_f16 if f16 else self._L.fctc_beam_search_batch
+        self._check(fn(self._h, post.ctypes.data, N, T, Cn, beam_size, beam_cut_threshold, int(collapse_repeats),
+                       labels.ctypes.data, path.ctypes.data, labels.size, offsets.ctypes.data, lens.ctypes.data,
+                       status.ctypes.data, C.byref(used)))
         return dict(labels=labels, path=path, offsets=offsets, lens=lens, status=status, used=used.value)
 
     def beam_search_duplex_batch(self, post1, post2, envelope=None, beam_size=5, beam_cut_threshold=0.0,

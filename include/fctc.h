@@ -147,6 +147,21 @@ int fctc_beam_search_batch_device(fctc_handle* h, const float* post_dev, int64_t
                                   int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev, int32_t* status_dev,
                                   unsigned long long* pool_used_dev, void* scratch_dev, int64_t scratch_bytes,
                                   int32_t nodes_per_row, void* stream);
+/* fctc_beam_search_batch_device_f16 / fctc_beam_search_batch_f16: fctc_beam_search_batch_device and
+ *   fctc_beam_search_batch for binary16 posteriors (no counterpart in the
+ *   reference, which takes float32 only).  Values are widened exactly to float32 as they are fetched,
+ *   so sequences and paths equal the reference's on the widened array. */
+int fctc_beam_search_batch_device_f16(fctc_handle* h, const void* post_dev_f16, int64_t n_reads, int64_t n_rows,
+                                      int32_t n_labels, int32_t beam_size, float beam_cut_threshold,
+                                      int32_t collapse_repeats, uint8_t* labels_dev, int32_t* path_dev,
+                                      int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev,
+                                      int32_t* status_dev, unsigned long long* pool_used_dev, void* scratch_dev,
+                                      int64_t scratch_bytes, int32_t nodes_per_row, void* stream);
+int fctc_beam_search_batch_f16(fctc_handle* h, const void* post_host_f16, int64_t n_reads, int64_t n_rows,
+                               int32_t n_labels, int32_t beam_size, float beam_cut_threshold, int32_t collapse_repeats,
+                               uint8_t* labels, int32_t* path, int64_t pool_capacity, int64_t* offsets, int32_t* lens,
+                               int32_t* status, int64_t* pool_used);
+
 /* fctc_beam_search_batch_device_static — no counterpart in the reference.  The same decode as
  * fctc_beam_search_batch_device for callers that cannot allocate device memory when they call
  * (all HBM pre-assigned to their own arena, allocator calls forbidden on the calling thread, ...):

@@ -180,3 +180,21 @@ def test_device_batch_synthetic(dec, oracle):
             pth = res["path"][o:o + ln]
             assert (np.diff(pth) > 0).all() and (ln == 0 or (pth[0] >= 0 and pth[-1] < T))
             assert (res["labels"][o:o + ln] >= 1).all() and (res["labels"][o:o + ln] < Cn).all()
+
+
+# ---- binary16 posteriors: decoded as the exactly widened float32 values --------------------------------
+@pytest.mark.parametrize("case", [(12, 500, 5, 5, 0.1, True), (6, 400, 5, 32, 0.0, True), (6, 300, 3, 10, 0.02, False),
+                                  (4, 300, 12, 5, 0.0, True)],
+                         ids=lambda c: "N{}_T{}_C{}_b{}_thr{}_c{}".format(*c))
+def test_f16_posteriors_host_batch(dec, oracle, case):
+    N, T, Cn, beam, thr, collapse = case
+    rng = np.random.default_rng(4242 + T + Cn + beam)
+    half = softmax_posteriors(rng, (N, T, Cn)).astype(np.float16)
+    res = dec.beam_search_batch(half, beam, thr, collapse)
+    ol, op, olen, ost, _ = oracle.beam_search_batch(half.astype(np.float32), beam, thr, collapse)
+    for n in range(N):
+        off, ln = int(res["offsets"][n]), int(res["lens"][n])
+        assert res["status"][n] == ost[n]
+        if ost[n] == 0:
+            assert ln == olen[n]
+            assert np.array_equal(res["labels"][off:off + ln], ol[n, :ln]) and np.array_equal(res["path"][off:off + ln], op[n, :ln])
