@@ -268,22 +268,47 @@ __global__ void __launch_bounds__(VW_THREADS, QSTRING ? VW_MINBLOCKS_Q : VW_MINB
             } else {
                 const long long e0 = n * read_elems + (long long)ti * tile_elems;
                 const uint32_t stagef = r_stage + 4u * uint32_t(e0 & 3);
+                const bool tile_safe = e0 + tile_elems <= safe_elems;  // warp-uniform: the whole tile came through the bulk copy
+                auto ld = [&](int i) {
+                    return (tile_safe || e0 + i < safe_elems) ? lds_f1(stagef + 4u * uint32_t(i)) : p.post[e0 + i];
+                };
+                if (RPL > 1) {
+                    // Rows are read interleaved (lane, lane + 32, ...): the lanes of one load are then C words
+                    // apart instead of RPL*C, which for alphabets of 4, 8, 16 labels is the difference between an
+                    // 8-way and a 32-way shared-memory bank conflict.  The {probability, label} pairs go through
+                    // the (idle) quality queue to reach the lanes that own them as RPL consecutive rows.
+                    __syncwarp();  // the previous tile's queue reads are over
 #pragma unroll
-                for (int r = 0; r < RPL; ++r) {
-                    const int row = r_base + r;
+                    for (int r = 0; r < RPL; ++r) {
+                        const int row = lane + 32 * r;
+                        int arg = 0;
+                        float best = 0.0f;
+                        if (row < rows) {
+                            const int le = row * C;
+                            best = ld(le);
+                            for (int c = 1; c < C; ++c) {
+                                const float v = ld(le + c);
+                                if (v > best) { best = v; arg = c; }
+                            }
+                        }
+                        sts_run(q_base + 8 * row, best, arg);  // rows past the end of the read count as blank
+                    }
+                    __syncwarp();
+#pragma unroll
+                    for (int r = 0; r < RPL; ++r) lds_run(q_base + 8 * (r_base + r), pr[r], lab[r]);
+                } else {
                     int arg = 0;
                     float best = 0.0f;
-                    if (row < rows) {
-                        const int le = row * C;
-                        auto ld = [&](int i) { return (e0 + i < safe_elems) ? lds_f1(stagef + 4u * uint32_t(i)) : p.post[e0 + i]; };
+                    if (lane < rows) {
+                        const int le = lane * C;
                         best = ld(le);
                         for (int c = 1; c < C; ++c) {
                             const float v = ld(le + c);
                             if (v > best) { best = v; arg = c; }
                         }
                     }
-                    pr[r] = best;
-                    lab[r] = arg;  // rows past the end of the read count as blank
+                    pr[0] = best;
+                    lab[0] = arg;  // rows past the end of the read count as blank
                 }
             }
             __syncwarp();  // stage fully consumed (and the previous tile's queue reads are over)

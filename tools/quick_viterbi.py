@@ -14,7 +14,7 @@ import fctc_b200  # noqa: E402
 def main():
     N = int(sys.argv[1]) if len(sys.argv) > 1 else 65536
     T = int(sys.argv[2]) if len(sys.argv) > 2 else 4000
-    Cn = 5
+    Cn = int(sys.argv[4]) if len(sys.argv) > 4 else 5
     kind = int(sys.argv[3]) if len(sys.argv) > 3 else 0
     dev = torch.device("cuda:0")
     dec = fctc_b200.Decoder(0)
