@@ -272,6 +272,7 @@ __global__ void __launch_bounds__(VW_THREADS, QSTRING ? VW_MINBLOCKS_Q : VW_MINB
                 auto ld = [&](int i) {
                     return (tile_safe || e0 + i < safe_elems) ? lds_f1(stagef + 4u * uint32_t(i)) : p.post[e0 + i];
                 };
+                const bool vec4 = tile_safe && (C & 3) == 0 && (e0 & 3) == 0;  // warp-uniform
                 if (RPL > 1) {
                     // Rows are read interleaved (lane, lane + 32, ...): the lanes of one load are then C words
                     // apart instead of RPL*C, which for alphabets of 4, 8, 16 labels is the difference between an
@@ -285,10 +286,25 @@ __global__ void __launch_bounds__(VW_THREADS, QSTRING ? VW_MINBLOCKS_Q : VW_MINB
                         float best = 0.0f;
                         if (row < rows) {
                             const int le = row * C;
-                            best = ld(le);
-                            for (int c = 1; c < C; ++c) {
-                                const float v = ld(le + c);
-                                if (v > best) { best = v; arg = c; }
+                            if (vec4) {  // rows of whole 16-byte groups: a quarter of the loads and of the conflicts
+                                float v[4];
+                                lds_f4(stagef + 4u * uint32_t(le), v);
+                                best = v[0];
+#pragma unroll
+                                for (int k = 1; k < 4; ++k)
+                                    if (v[k] > best) { best = v[k]; arg = k; }
+                                for (int c = 4; c < C; c += 4) {
+                                    lds_f4(stagef + 4u * uint32_t(le + c), v);
+#pragma unroll
+                                    for (int k = 0; k < 4; ++k)
+                                        if (v[k] > best) { best = v[k]; arg = c + k; }
+                                }
+                            } else {
+                                best = ld(le);
+                                for (int c = 1; c < C; ++c) {
+                                    const float v = ld(le + c);
+                                    if (v > best) { best = v; arg = c; }
+                                }
                             }
                         }
                         sts_run(q_base + 8 * row, best, arg);  // rows past the end of the read count as blank
