@@ -273,6 +273,33 @@ __global__ void __launch_bounds__(VW_THREADS, QSTRING ? VW_MINBLOCKS_Q : VW_MINB
                     return (tile_safe || e0 + i < safe_elems) ? lds_f1(stagef + 4u * uint32_t(i)) : p.post[e0 + i];
                 };
                 const bool vec4 = tile_safe && (C & 3) == 0 && (e0 & 3) == 0;  // warp-uniform
+                // argmax of one staged row (strict '>' from label 0: first maximum, NaN never wins unless it is label 0)
+                auto row_argmax = [&](int row, int& arg, float& best) {
+                    arg = 0;
+                    best = 0.0f;  // rows past the end of the read count as blank
+                    if (row >= rows) return;
+                    const int le = row * C;
+                    if (vec4) {  // rows of whole 16-byte groups: a quarter of the loads and of the bank conflicts
+                        float v[4];
+                        lds_f4(stagef + 4u * uint32_t(le), v);
+                        best = v[0];
+#pragma unroll
+                        for (int k = 1; k < 4; ++k)
+                            if (v[k] > best) { best = v[k]; arg = k; }
+                        for (int c = 4; c < C; c += 4) {
+                            lds_f4(stagef + 4u * uint32_t(le + c), v);
+#pragma unroll
+                            for (int k = 0; k < 4; ++k)
+                                if (v[k] > best) { best = v[k]; arg = c + k; }
+                        }
+                    } else {
+                        best = ld(le);
+                        for (int c = 1; c < C; ++c) {
+                            const float v = ld(le + c);
+                            if (v > best) { best = v; arg = c; }
+                        }
+                    }
+                };
                 if (RPL > 1) {
                     // Rows are read interleaved (lane, lane + 32, ...): the lanes of one load are then C words
                     // apart instead of RPL*C, which for alphabets of 4, 8, 16 labels is the difference between an
@@ -282,49 +309,16 @@ __global__ void __launch_bounds__(VW_THREADS, QSTRING ? VW_MINBLOCKS_Q : VW_MINB
 #pragma unroll
                     for (int r = 0; r < RPL; ++r) {
                         const int row = lane + 32 * r;
-                        int arg = 0;
-                        float best = 0.0f;
-                        if (row < rows) {
-                            const int le = row * C;
-                            if (vec4) {  // rows of whole 16-byte groups: a quarter of the loads and of the conflicts
-                                float v[4];
-                                lds_f4(stagef + 4u * uint32_t(le), v);
-                                best = v[0];
-#pragma unroll
-                                for (int k = 1; k < 4; ++k)
-                                    if (v[k] > best) { best = v[k]; arg = k; }
-                                for (int c = 4; c < C; c += 4) {
-                                    lds_f4(stagef + 4u * uint32_t(le + c), v);
-#pragma unroll
-                                    for (int k = 0; k < 4; ++k)
-                                        if (v[k] > best) { best = v[k]; arg = c + k; }
-                                }
-                            } else {
-                                best = ld(le);
-                                for (int c = 1; c < C; ++c) {
-                                    const float v = ld(le + c);
-                                    if (v > best) { best = v; arg = c; }
-                                }
-                            }
-                        }
-                        sts_run(q_base + 8 * row, best, arg);  // rows past the end of the read count as blank
+                        int arg;
+                        float best;
+                        row_argmax(row, arg, best);
+                        sts_run(q_base + 8 * row, best, arg);
                     }
                     __syncwarp();
 #pragma unroll
                     for (int r = 0; r < RPL; ++r) lds_run(q_base + 8 * (r_base + r), pr[r], lab[r]);
                 } else {
-                    int arg = 0;
-                    float best = 0.0f;
-                    if (lane < rows) {
-                        const int le = lane * C;
-                        best = ld(le);
-                        for (int c = 1; c < C; ++c) {
-                            const float v = ld(le + c);
-                            if (v > best) { best = v; arg = c; }
-                        }
-                    }
-                    pr[0] = best;
-                    lab[0] = arg;  // rows past the end of the read count as blank
+                    row_argmax(lane, lab[0], pr[0]);
                 }
             }
             __syncwarp();  // stage fully consumed (and the previous tile's queue reads are over)
@@ -694,7 +688,7 @@ static cudaError_t launch_viterbi_t(const ViterbiParams& p, int sm_count, cudaSt
         return fast5 ? launch_stream_flags<QT, 4, true, false>(p, L, sm_count, stream)
                      : launch_stream_flags<QT, 4, false, false>(p, L, sm_count, stream);
     }
-    if (p.C <= 64 && plan_stream<1>(p, &L)) {
+    if (p.C <= 127 && plan_stream<1>(p, &L)) {
         if (which) *which = 0;
         return launch_stream_flags<QT, 1, false, false>(p, L, sm_count, stream);
     }
