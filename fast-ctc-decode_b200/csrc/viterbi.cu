@@ -457,7 +457,7 @@ __global__ void __launch_bounds__(VW_THREADS, QSTRING ? VW_MINBLOCKS_Q : VW_MINB
 // ------------------------------------------------------------------------------------------
 // Generic kernel: any alphabet size, no alignment requirement.  One CTA per read, rows loaded
 // straight from global memory.  Used when the streaming kernel's shared-memory plan does not fit
-// (alphabets above 64 labels) or the input pointer is not 16-byte aligned.
+// (alphabets of 128 labels and more) or the input pointer is not 16-byte aligned.
 // ------------------------------------------------------------------------------------------
 constexpr int VG_THREADS = 256;
 constexpr int VG_RPT = 4;
