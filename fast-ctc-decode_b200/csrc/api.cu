@@ -770,6 +770,43 @@ int fctc_beam_search(fctc_handle* h, const float* post_host, int64_t n_rows, int
 }
 
 // ---------------------------------------------------------------------------------------------
+// FASTQ record assembly
+// ---------------------------------------------------------------------------------------------
+int64_t fctc_fastq_scratch_bytes(const fctc_handle* h, int64_t n_reads) {
+    (void)h;
+    return n_reads < 0 ? 0 : fctc::fastq_scratch_bytes(n_reads);
+}
+
+int fctc_fastq_records_device(fctc_handle* h, const uint8_t* labels_dev, const uint8_t* quals_dev,
+                              const int64_t* offsets_dev, const int32_t* lens_dev, const int32_t* status_dev,
+                              int64_t n_reads, const char* alphabet, int32_t n_labels, const char* name_prefix,
+                              int64_t first_index, uint8_t* out_dev, int64_t out_capacity, int64_t* record_offsets_dev,
+                              void* scratch_dev, int64_t scratch_bytes, void* stream) {
+    if (!h) return FCTC_E_ARGUMENT;
+    if (n_reads < 0 || first_index < 0) return fail(h, FCTC_E_ARGUMENT, "negative read count or first index");
+    if (!labels_dev || !quals_dev || !offsets_dev || !lens_dev || !status_dev || !out_dev || !record_offsets_dev || !scratch_dev)
+        return fail(h, FCTC_E_ARGUMENT, "null device pointer");
+    if (!alphabet || n_labels < 1 || n_labels > 256)
+        return fail(h, FCTC_E_ARGUMENT, "alphabet must give one character for each of 1..256 labels");
+    const size_t plen = name_prefix ? strlen(name_prefix) : 0;
+    if (plen > 63) return fail(h, FCTC_E_ARGUMENT, "name_prefix longer than 63 characters");
+    if (scratch_bytes < fctc::fastq_scratch_bytes(n_reads))
+        return fail(h, FCTC_E_CAPACITY, "fastq scratch too small: %lld bytes given, %lld needed", (long long)scratch_bytes,
+                    (long long)fctc::fastq_scratch_bytes(n_reads));
+    if (reinterpret_cast<uintptr_t>(scratch_dev) & 7u) return fail(h, FCTC_E_ARGUMENT, "scratch_dev must be 8-byte aligned");
+    FCTC_CUDA(h, cudaSetDevice(h->device));
+    fctc::FastqParams p{};
+    p.labels = labels_dev; p.quals = quals_dev; p.offsets = offsets_dev; p.lens = lens_dev; p.status = status_dev;
+    p.N = n_reads; p.first_index = first_index; p.out = out_dev; p.out_capacity = out_capacity;
+    p.prefix_len = int(plen);
+    memcpy(p.prefix, name_prefix ? name_prefix : "", plen);
+    for (int i = 0; i < 256; ++i) p.alphabet[i] = (unsigned char)(i < n_labels ? alphabet[i] : '?');
+    FCTC_CUDA(h, fctc::launch_fastq(p, reinterpret_cast<long long*>(record_offsets_dev), scratch_dev,
+                                    static_cast<cudaStream_t>(stream)));
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
 // Synthetic input + host test hooks
 // ---------------------------------------------------------------------------------------------
 int fctc_synth_posteriors_device(fctc_handle* h, float* post_dev, int64_t n_reads, int64_t n_rows, int32_t n_labels,

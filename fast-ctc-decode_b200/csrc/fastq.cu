@@ -1,0 +1,178 @@
+// fastq.cu — FASTQ record assembly on the device.
+//
+// The reference returns a read as one string, sequence then quality characters
+// (src/search.rs:378-380), and leaves it to the caller to split it and to wrap it into a record.
+// With batched decoding on the GPU that host pass would touch every label again, so the slot-form
+// result of the Viterbi kernel (labels, quality characters, lens, status) is turned into FASTQ text
+// where it lies:
+//     @<prefix><first_index + n>\n<sequence>\n+\n<quality>\n
+// records concatenated in read order; reads whose status is not FCTC_OK produce no record.
+// Three small kernels: record lengths, an exclusive scan over them (block partials, one block for
+// the partials, add back), and the writer (one warp per read, lanes copy bytes in strides of 32 so
+// that both the loads from the slot and the stores into the text are contiguous).
+#include "device_utils.cuh"
+#include "kernels.h"
+
+#include "../../include/fctc.h"
+
+namespace fctc {
+
+namespace {
+
+constexpr int FQ_SCAN_THREADS = 256;
+constexpr int FQ_SCAN_ITEMS = 4;  // per thread
+constexpr int FQ_SCAN_TILE = FQ_SCAN_THREADS * FQ_SCAN_ITEMS;
+
+__device__ __forceinline__ int decimal_digits(unsigned long long v) {
+    int d = 1;
+    while (v >= 10ull) { v /= 10ull; ++d; }
+    return d;
+}
+
+__global__ void __launch_bounds__(256) fq_lengths_kernel(const FastqParams p, long long* rec_len) {
+    for (long long n = blockIdx.x * (long long)blockDim.x + threadIdx.x; n < p.N; n += (long long)gridDim.x * blockDim.x) {
+        long long len = 0;
+        if (p.status[n] == FCTC_OK) {
+            const long long L = p.lens[n];
+            len = 1 + p.prefix_len + decimal_digits((unsigned long long)(p.first_index + n)) + 1 + L + 3 + L + 1;
+        }
+        rec_len[n] = len;
+    }
+}
+
+// block-wise exclusive scan: out[i] = sum of in[0..i) within the tile, tile totals to block_sums
+__global__ void __launch_bounds__(FQ_SCAN_THREADS) fq_scan_tiles_kernel(const long long* in, long long* out, long long n,
+                                                                         long long* block_sums) {
+    __shared__ long long warp_sums[FQ_SCAN_THREADS / 32];
+    const long long base = (long long)blockIdx.x * FQ_SCAN_TILE + (long long)threadIdx.x * FQ_SCAN_ITEMS;
+    long long v[FQ_SCAN_ITEMS], tsum = 0;
+#pragma unroll
+    for (int k = 0; k < FQ_SCAN_ITEMS; ++k) {
+        v[k] = (base + k < n) ? in[base + k] : 0;
+        tsum += v[k];
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    long long incl = tsum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const long long o = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += o;
+    }
+    if (lane == 31) warp_sums[warp] = incl;
+    __syncthreads();
+    long long wbase = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < FQ_SCAN_THREADS / 32; ++w) {
+        const long long s = warp_sums[w];
+        if (w < warp) wbase += s;
+        total += s;
+    }
+    long long run = wbase + incl - tsum;
+#pragma unroll
+    for (int k = 0; k < FQ_SCAN_ITEMS; ++k) {
+        if (base + k < n) out[base + k] = run;
+        run += v[k];
+    }
+    if (threadIdx.x == 0) block_sums[blockIdx.x] = total;
+}
+
+// one block: exclusive scan of the tile totals in place (sequential over chunks of 256; at most a few thousand tiles)
+__global__ void __launch_bounds__(FQ_SCAN_THREADS) fq_scan_sums_kernel(long long* sums, long long n_tiles, long long* grand_total) {
+    __shared__ long long warp_sums[FQ_SCAN_THREADS / 32];
+    __shared__ long long carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (long long c0 = 0; c0 < n_tiles; c0 += FQ_SCAN_THREADS) {
+        const long long i = c0 + threadIdx.x;
+        const long long v = (i < n_tiles) ? sums[i] : 0;
+        long long incl = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const long long o = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += o;
+        }
+        if (lane == 31) warp_sums[warp] = incl;
+        __syncthreads();
+        long long wbase = 0, total = 0;
+#pragma unroll
+        for (int w = 0; w < FQ_SCAN_THREADS / 32; ++w) {
+            const long long s = warp_sums[w];
+            if (w < warp) wbase += s;
+            total += s;
+        }
+        const long long c = carry;
+        if (i < n_tiles) sums[i] = c + wbase + incl - v;
+        __syncthreads();
+        if (threadIdx.x == 0) carry = c + total;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *grand_total = carry;
+}
+
+__global__ void __launch_bounds__(256) fq_add_sums_kernel(long long* offs, long long n, const long long* sums,
+                                                          const long long* grand_total) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i <= n; i += (long long)gridDim.x * blockDim.x) {
+        if (i == n) offs[n] = *grand_total;
+        else offs[i] += sums[i / FQ_SCAN_TILE];
+    }
+}
+
+__global__ void __launch_bounds__(256) fq_write_kernel(const FastqParams p, const long long* rec_off) {
+    const int lane = threadIdx.x & 31;
+    const long long warps = (long long)gridDim.x * (blockDim.x >> 5);
+    const long long total = rec_off[p.N];
+    if (total > p.out_capacity) return;  // the host reports FCTC_E_CAPACITY from the same number
+    for (long long n = blockIdx.x * (long long)(blockDim.x >> 5) + (threadIdx.x >> 5); n < p.N; n += warps) {
+        if (p.status[n] != FCTC_OK) continue;
+        const long long L = p.lens[n];
+        const long long src = p.offsets[n];
+        unsigned char* o = p.out + rec_off[n];
+        const unsigned long long idx = (unsigned long long)(p.first_index + n);
+        const int digits = decimal_digits(idx);
+        const int head = 1 + p.prefix_len + digits + 1;
+        if (lane == 0) {
+            o[0] = '@';
+            for (int k = 0; k < p.prefix_len; ++k) o[1 + k] = p.prefix[k];
+            unsigned long long v = idx;
+            for (int k = digits - 1; k >= 0; --k) { o[1 + p.prefix_len + k] = (unsigned char)('0' + int(v % 10ull)); v /= 10ull; }
+            o[head - 1] = '\n';
+            o[head + L] = '\n';
+            o[head + L + 1] = '+';
+            o[head + L + 2] = '\n';
+            o[head + L + 3 + L] = '\n';
+        }
+        unsigned char* seq = o + head;
+        unsigned char* qual = o + head + L + 3;
+        for (long long k = lane; k < L; k += 32) {
+            seq[k] = p.alphabet[p.labels[src + k]];
+            qual[k] = p.quals[src + k];
+        }
+    }
+}
+
+}  // namespace
+
+int64_t fastq_scratch_bytes(int64_t N) {
+    const int64_t tiles = (N + FQ_SCAN_TILE - 1) / FQ_SCAN_TILE;
+    return 8 * (N + tiles + 2) + 256;
+}
+
+cudaError_t launch_fastq(const FastqParams& p, long long* rec_off, void* scratch, cudaStream_t stream) {
+    // scratch: [N] record lengths, [tiles] tile sums, [1] grand total
+    long long* rec_len = static_cast<long long*>(scratch);
+    const long long tiles = (p.N + FQ_SCAN_TILE - 1) / FQ_SCAN_TILE;
+    long long* sums = rec_len + p.N;
+    long long* grand = sums + tiles;
+    if (p.N <= 0) return cudaMemsetAsync(rec_off, 0, 8, stream);
+    const unsigned blocks = (unsigned)((p.N + 255) / 256 < 148 * 8 ? (p.N + 255) / 256 : 148 * 8);
+    fq_lengths_kernel<<<blocks, 256, 0, stream>>>(p, rec_len);
+    fq_scan_tiles_kernel<<<(unsigned)tiles, FQ_SCAN_THREADS, 0, stream>>>(rec_len, rec_off, p.N, sums);
+    fq_scan_sums_kernel<<<1, FQ_SCAN_THREADS, 0, stream>>>(sums, tiles, grand);
+    fq_add_sums_kernel<<<blocks, 256, 0, stream>>>(rec_off, p.N, sums, grand);
+    const long long want = (p.N + 7) / 8;  // 8 warps per block
+    fq_write_kernel<<<(unsigned)(want < 148 * 16 ? want : 148 * 16), 256, 0, stream>>>(p, rec_off);
+    return cudaGetLastError();
+}
+
+}  // namespace fctc

@@ -115,6 +115,24 @@ int64_t duplex_scratch_bytes(int sm_count, int64_t N, int T1, int T2, int C, int
                              int64_t budget_bytes, int64_t* nodes_per_slot, int* n_slots);
 cudaError_t launch_duplex(const DuplexParams& p, cudaStream_t stream);
 
+// FASTQ record assembly from the Viterbi slot form (fastq.cu)
+struct FastqParams {
+    const uint8_t* labels;   // slot-form labels (alphabet indices)
+    const uint8_t* quals;    // slot-form quality characters (qual_bytes == 1)
+    const int64_t* offsets;  // [N]
+    const int32_t* lens;     // [N]
+    const int32_t* status;   // [N]
+    int64_t N;
+    int64_t first_index;     // number of read 0 in the record names
+    unsigned char* out;
+    int64_t out_capacity;
+    int prefix_len;
+    char prefix[64];
+    unsigned char alphabet[256];  // label index -> character
+};
+int64_t fastq_scratch_bytes(int64_t N);
+cudaError_t launch_fastq(const FastqParams& p, long long* rec_off, void* scratch, cudaStream_t stream);
+
 cudaError_t launch_synth(float* post, int64_t N, int64_t T, int C, int kind, uint64_t seed, int64_t first_read,
                          cudaStream_t stream);
 

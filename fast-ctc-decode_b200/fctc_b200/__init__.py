@@ -71,6 +71,9 @@ _SIGNATURES = {
                                                            _vp, _vp, _i64, _i32, _vp]),
     "fctc_crf_beam_search_duplex": (C.c_int, [_vp, _vp, _i64, _vp, _i32, _vp, _i64, _vp, _i32, _i32, _i32, _vp, _i32,
                                               _f32, _i32, _vp, _i64, _vp]),
+    "fctc_fastq_scratch_bytes": (_i64, [_vp, _i64]),
+    "fctc_fastq_records_device": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, C.c_char_p, _i32, C.c_char_p, _i64, _vp,
+                                            _i64, _vp, _vp, _i64, _vp]),
     "fctc_synth_posteriors_device": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _i32, _u64, _i64, _vp]),
     "fctc_host_phred": (C.c_uint32, [_f32, _f32, _f32]),
     "fctc_host_log10f": (None, [_vp, _vp, _i64]),
@@ -156,6 +159,19 @@ class Decoder:
         self._check(fn(self._h, post_ptr, n_reads, n_rows, n_labels, int(qstring), qscale, qbias, int(collapse_repeats),
                        labels_ptr, quals_ptr or None, qual_bytes, path_ptr, pool_capacity, offsets_ptr, lens_ptr,
                        status_ptr, stream or None))
+
+    def fastq_scratch_bytes(self, n_reads):
+        return int(self._L.fctc_fastq_scratch_bytes(self._h, n_reads))
+
+    def fastq_records_device(self, labels_ptr, quals_ptr, offsets_ptr, lens_ptr, status_ptr, n_reads, alphabet,
+                             name_prefix, first_index, out_ptr, out_capacity, record_offsets_ptr, scratch_ptr,
+                             scratch_bytes, stream=0):
+        """FASTQ text from the slot-form Viterbi result (qstring, qual_bytes=1), assembled on the device."""
+        alpha = alphabet.encode("ascii") if isinstance(alphabet, str) else bytes(alphabet)
+        self._check(self._L.fctc_fastq_records_device(self._h, labels_ptr, quals_ptr, offsets_ptr, lens_ptr, status_ptr,
+                                                      n_reads, alpha, len(alpha), name_prefix.encode("ascii"), first_index,
+                                                      out_ptr, out_capacity, record_offsets_ptr, scratch_ptr,
+                                                      scratch_bytes, stream or None))
 
     def beam_scratch_bytes(self, n_reads, n_rows, n_labels, beam_size, nodes_per_row=0):
         return int(self._L.fctc_beam_scratch_bytes(self._h, n_reads, n_rows, n_labels, beam_size, nodes_per_row))

@@ -268,6 +268,27 @@ int fctc_crf_beam_search_duplex(fctc_handle* h, const float* post1_host, int64_t
                                 int64_t capacity, int64_t* out_len);
 
 /* ------------------------------------------------------------------------------------------
+ * FASTQ record assembly on the device — SURVEY.md section 8(f) rank 3; no counterpart in the
+ * reference, which returns sequence and quality as one concatenated string
+ * (src/search.rs:378-380) and leaves records to the caller.  Input is the slot-form result of
+ * fctc_viterbi_batch_device with qstring = 1 and qual_bytes = 1; output is the text
+ *     @<name_prefix><first_index + n>\n<sequence>\n+\n<quality>\n
+ * for every read whose status is FCTC_OK (others produce no record), concatenated in read order
+ * in out_dev.  alphabet gives one character per label index (n_labels of them; index 0, the
+ * blank, is never emitted).  record_offsets_dev[n_reads + 1] receives each record's first byte
+ * and, last, the total length; when that total exceeds out_capacity nothing is written and the
+ * caller learns the size it needs from that last entry (sum of 2*len + 7 + strlen(prefix) +
+ * digits per read bounds it).  scratch_dev: fctc_fastq_scratch_bytes(n_reads) bytes, 8-byte
+ * aligned.  Asynchronous on `stream`.
+ * ------------------------------------------------------------------------------------------ */
+int64_t fctc_fastq_scratch_bytes(const fctc_handle* h, int64_t n_reads);
+int fctc_fastq_records_device(fctc_handle* h, const uint8_t* labels_dev, const uint8_t* quals_dev,
+                              const int64_t* offsets_dev, const int32_t* lens_dev, const int32_t* status_dev,
+                              int64_t n_reads, const char* alphabet, int32_t n_labels, const char* name_prefix,
+                              int64_t first_index, uint8_t* out_dev, int64_t out_capacity, int64_t* record_offsets_dev,
+                              void* scratch_dev, int64_t scratch_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * Synthetic posterior generator used by bench.py and the tests (no reference counterpart; it
  * implements SURVEY.md §8d's input definition): fills post_dev[n_reads, n_rows, n_labels] with
  * kind 0: softmax(3*(2u-1)) rows, kind 1: peaked rows (dominant label, blank w.p. 0.65), kind 2: kind
