@@ -403,6 +403,16 @@ def run_ours(args, w):
         outd = dict(labels=hl.numpy(), quals=hq.numpy(), path=hp.numpy(), offsets=ho.numpy(), lens=hn.numpy(),
                     status=hs.numpy())
 
+    # the device-resident arrays of the first measurement are done with: the host-memory entry points
+    # size their own device buffers from what is free, as they would in a caller's process
+    torch.cuda.synchronize()
+    del post, labels, path, offsets, lens, status, used, scratch
+    if w["kind"] == "viterbi":
+        del quals
+    if w["kind"] == "duplex":
+        del post2, env
+    torch.cuda.empty_cache()
+
     def e2e_step():
         if w["kind"] == "viterbi":
             return dec.viterbi_batch(hnp, bool(w["qstring"]), w["qscale"], w["qbias"], bool(w["collapse"]),
