@@ -573,6 +573,9 @@ void* handle_device_buffer(fctc_handle* h, int index, size_t bytes) {
     if (ensure(h, h->extra_dev[index], bytes)) return nullptr;
     return h->extra_dev[index].p;
 }
+size_t handle_device_buffer_bytes(const fctc_handle* h, int index) {
+    return (index < 0 || index >= 16) ? 0 : h->extra_dev[index].bytes;
+}
 void* handle_pinned_buffer(fctc_handle* h, int index, size_t bytes) {
     if (index < 0 || index >= 16) return nullptr;
     if (bytes <= h->extra_pin_bytes[index]) return h->extra_pin[index];

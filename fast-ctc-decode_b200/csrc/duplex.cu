@@ -755,10 +755,12 @@ int dx_check(fctc_handle* h, int64_t n_pairs, int64_t T1, int64_t T2, int32_t C,
     return 0;
 }
 
-int64_t dx_free_budget() {
+// What the trie scratch of a host-memory call may take: three quarters of the device memory that is free
+// once the handle's own scratch buffer (kept from the previous call, and reused) is counted as free.
+int64_t dx_free_budget(const fctc_handle* h) {
     size_t free_b = 0, total_b = 0;
     if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return int64_t(8) << 30;
-    return int64_t(free_b / 2);
+    return int64_t((free_b + fctc::handle_device_buffer_bytes(h, 8)) / 4 * 3);
 }
 
 }  // namespace
@@ -835,7 +837,7 @@ int dx_host_chunk(fctc_handle* h, const float* post1, const float* post2, const 
     fctc::DuplexParams p{};
     p.W = W;
     const int64_t need = fctc::duplex_scratch_bytes(fctc::handle_sm_count(h), cnt, int(T1), int(T2), C, beam, W, nodes_per_row,
-                                                    dx_free_budget(), &p.nodes_per_slot, &p.n_slots);
+                                                    dx_free_budget(h), &p.nodes_per_slot, &p.n_slots);
     void* scratch = fctc::handle_device_buffer(h, 8, size_t(need));
     if (!scratch) return FCTC_E_NOMEM;
 #define DX_CUDA(call)                                                                          \
@@ -896,7 +898,12 @@ extern "C" int fctc_beam_search_duplex_batch(fctc_handle* h, const float* post1_
     }
     const int W = int(wmax + 1);
     const int64_t pair_bytes = (n_rows_1 + n_rows_2) * int64_t(n_labels) * 4;
-    const int64_t chunk = std::max<int64_t>(1, std::min<int64_t>(n_pairs, (int64_t(256) << 20) / std::max<int64_t>(pair_bytes, 1)));
+    // a chunk must fill the resident warps (24 per SM, one pair each) a few times over, or most of the GPU
+    // idles while the last pairs of the chunk finish; capped at 2 GiB of posteriors
+    int64_t chunk = std::max<int64_t>((int64_t(256) << 20) / std::max<int64_t>(pair_bytes, 1),
+                                      int64_t(fctc::handle_sm_count(h)) * 24 * 3);
+    chunk = std::min<int64_t>(chunk, std::max<int64_t>((int64_t(2) << 30) / std::max<int64_t>(pair_bytes, 1), 1));
+    chunk = std::max<int64_t>(1, std::min<int64_t>(chunk, n_pairs));
     int64_t used = 0;
     for (int64_t first = 0; first < n_pairs; first += chunk) {
         const int64_t cnt = std::min(chunk, n_pairs - first);
@@ -1056,7 +1063,7 @@ extern "C" int fctc_crf_beam_search_duplex(fctc_handle* h, const float* post1_ho
         int64_t nps = 0;
         int nsl = 0;
         const int64_t need = fctc::duplex_scratch_bytes(fctc::handle_sm_count(h), 1, int(n_rows_1), int(n_rows_2), n_labels, beam_size,
-                                                        int(wmax + 1), tries[attempt], dx_free_budget(), &nps, &nsl);
+                                                        int(wmax + 1), tries[attempt], dx_free_budget(h), &nps, &nsl);
         void* scratch = fctc::handle_device_buffer(h, 8, size_t(need));
         if (!scratch) return FCTC_E_NOMEM;
         DXC(cudaMemsetAsync(dcur, 0, 8, st));

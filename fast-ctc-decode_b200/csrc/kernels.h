@@ -15,6 +15,7 @@ int check_beam_call(fctc_handle* h, int64_t n_reads, int64_t n_rows, int32_t n_l
 int check_threshold_call(fctc_handle* h, int32_t n_labels, int32_t beam_size, float thr);  // src/lib.rs:433-443
 // Persistent, growable device / pinned-host buffers owned by the handle (index 0..15 each).
 void* handle_device_buffer(fctc_handle* h, int index, size_t bytes);  // NULL on failure (error text set)
+size_t handle_device_buffer_bytes(const fctc_handle* h, int index);   // current size of a persistent buffer
 void* handle_pinned_buffer(fctc_handle* h, int index, size_t bytes);
 cudaStream_t handle_stream(fctc_handle* h);
 
