@@ -27,6 +27,7 @@ struct DevBuf {
 struct Slot {  // one in-flight chunk of the host-memory pipeline
     cudaStream_t stream = nullptr;
     cudaEvent_t done = nullptr;
+    cudaEvent_t kernel_done = nullptr;  // the chunk's kernel alone (chunks that share one trie scratch run in turn)
     DevBuf post, labels, quals, path, offsets, lens, status, cursor, scratch;
     unsigned long long* cursor_host = nullptr;  // pinned
     int64_t dst_first = 0, count = 0;           // result rows of the chunk in flight
@@ -167,6 +168,7 @@ int fctc_create(int device, fctc_handle** out) {
     for (int i = 0; i < 2 && ok; ++i) {
         ok = ok && cudaStreamCreateWithFlags(&h->slot[i].stream, cudaStreamNonBlocking) == cudaSuccess;
         ok = ok && cudaEventCreateWithFlags(&h->slot[i].done, cudaEventDisableTiming) == cudaSuccess;
+        ok = ok && cudaEventCreateWithFlags(&h->slot[i].kernel_done, cudaEventDisableTiming) == cudaSuccess;
         ok = ok && cudaMallocHost(reinterpret_cast<void**>(&h->slot[i].cursor_host), 64) == cudaSuccess;
     }
     if (!ok) {
@@ -187,6 +189,7 @@ void fctc_destroy(fctc_handle* h) {
             release(*b);
         if (s.cursor_host) cudaFreeHost(s.cursor_host);
         if (s.done) cudaEventDestroy(s.done);
+        if (s.kernel_done) cudaEventDestroy(s.kernel_done);
         if (s.stream) cudaStreamDestroy(s.stream);
     }
     release(h->misc);
@@ -672,12 +675,19 @@ int beam_host_pass(fctc_handle* h, const void* post_host, int in_f16, int64_t n_
     int n_slots = 0;
     size_t free_b = 0, total_b = 0;
     if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) free_b = size_t(16) << 30;
-    const int64_t budget = std::max<int64_t>(int64_t(free_b / 2) + int64_t(h->slot[0].scratch.bytes + h->slot[1].scratch.bytes) / 2,
-                                             int64_t(1) << 28) / 2;  // two slots share the budget
+    // One trie scratch serves both pipeline slots: every kernel fills the GPU on its own, so the two
+    // chunks' kernels are made to run in turn (an event per kernel) and each gets the whole budget —
+    // with a scratch per slot, wide beams on long reads ran at half the resident warps.  The budget is
+    // three quarters of what is free once the handle's reusable scratch is counted as free.
+    Slot& owner = h->slot[0];
+    const int64_t budget = std::max<int64_t>(int64_t((free_b + owner.scratch.bytes) / 4 * 3), int64_t(1) << 28);
     const int64_t need = fctc::beam_scratch_bytes(h->sm_count, chunk, n_rows, n_labels, beam_size, nodes_per_row, budget,
                                                   &nodes_per_slot, &n_slots);
-    for (int i = 0; i < 2; ++i)
-        if (int rc = ensure(h, h->slot[i].scratch, size_t(need))) return rc;
+    if (int rc = ensure(h, owner.scratch, size_t(need))) return rc;
+    // every resident warp decodes one read at a time: a chunk that is not a whole number of such rounds
+    // pays a full round for its leftover reads
+    if (chunk > n_slots && chunk < n_reads) chunk = chunk / n_slots * n_slots;
+    bool first_launch = true;
     auto launch = [&](Slot& s, int64_t cnt) -> int {
         fctc::BeamParams p{};
         fctc::beam_scratch_bytes(h->sm_count, cnt, n_rows, n_labels, beam_size, nodes_per_row, need, &p.nodes_per_slot, &p.n_slots);
@@ -686,9 +696,13 @@ int beam_host_pass(fctc_handle* h, const void* post_host, int in_f16, int64_t n_
         p.labels = static_cast<uint8_t*>(s.labels.p); p.path = static_cast<int32_t*>(s.path.p);
         p.pool_cap = cnt * slot_entries; p.offsets = static_cast<int64_t*>(s.offsets.p);
         p.lens = static_cast<int32_t*>(s.lens.p); p.status = static_cast<int32_t*>(s.status.p);
-        p.cursor = static_cast<unsigned long long*>(s.cursor.p); p.scratch = s.scratch.p;
-        p.scratch_bytes = int64_t(s.scratch.bytes); p.ticket = static_cast<unsigned long long*>(s.scratch.p);
+        p.cursor = static_cast<unsigned long long*>(s.cursor.p); p.scratch = owner.scratch.p;
+        p.scratch_bytes = int64_t(owner.scratch.bytes); p.ticket = static_cast<unsigned long long*>(owner.scratch.p);
+        Slot& other = (&s == &h->slot[0]) ? h->slot[1] : h->slot[0];
+        if (!first_launch) FCTC_CUDA(h, cudaStreamWaitEvent(s.stream, other.kernel_done, 0));  // the scratch is free again
+        first_launch = false;
         FCTC_CUDA(h, fctc::launch_beam(p, h->sm_count, s.stream));
+        FCTC_CUDA(h, cudaEventRecord(s.kernel_done, s.stream));
         return 0;
     };
     return host_pipeline(h, post_host, elem_bytes, n_reads, n_rows, n_labels, out, chunk, launch);
