@@ -835,6 +835,15 @@ int fctc_synth_posteriors_device(fctc_handle* h, float* post_dev, int64_t n_read
     return 0;
 }
 
+int fctc_test_poison_shared_memory(fctc_handle* h, int32_t byte) {
+    if (!h) return FCTC_E_ARGUMENT;
+    FCTC_CUDA(h, cudaSetDevice(h->device));
+    if (int rc = ensure(h, h->misc, 256)) return rc;
+    FCTC_CUDA(h, fctc::launch_poison_smem(h->sm_count, byte, static_cast<unsigned int*>(h->misc.p), h->stream));
+    FCTC_CUDA(h, cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
 uint32_t fctc_host_phred(float prob, float qscale, float qbias) {
     static const double invc[16] = FCTC_LOGF_INVC;
     static const double logc[16] = FCTC_LOGF_LOGC;

@@ -134,6 +134,7 @@ struct FastqParams {
 int64_t fastq_scratch_bytes(int64_t N);
 cudaError_t launch_fastq(const FastqParams& p, long long* rec_off, void* scratch, cudaStream_t stream);
 
+cudaError_t launch_poison_smem(int sm_count, int byte, unsigned int* sink, cudaStream_t stream);
 cudaError_t launch_synth(float* post, int64_t N, int64_t T, int C, int kind, uint64_t seed, int64_t first_read,
                          cudaStream_t stream);
 

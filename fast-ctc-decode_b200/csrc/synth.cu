@@ -77,4 +77,23 @@ cudaError_t launch_synth(float* post, int64_t N, int64_t T, int C, int kind, uin
     return cudaGetLastError();
 }
 
+// Test hook: leaves `byte` in every byte of every SM's shared memory (one CTA per SM, each taking the whole
+// 227 KB), so that a kernel that reads shared memory it has not written meets a chosen pattern instead of
+// whatever the previous kernel left.  0xFF gives -1 / NaN words.
+__global__ void __launch_bounds__(1024) poison_smem_kernel(unsigned int word, int bytes, unsigned int* sink) {
+    extern __shared__ unsigned int pool[];
+    for (int i = threadIdx.x; i < bytes / 4; i += blockDim.x) pool[i] = word;
+    __syncthreads();
+    if (pool[(threadIdx.x * 131) % (bytes / 4)] != word) sink[0] = 1;  // keeps the stores alive
+}
+
+cudaError_t launch_poison_smem(int sm_count, int byte, unsigned int* sink, cudaStream_t stream) {
+    const int bytes = 227 * 1024;
+    cudaError_t e = cudaFuncSetAttribute(poison_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e != cudaSuccess) return e;
+    const unsigned int b = (unsigned int)(byte & 0xff);
+    poison_smem_kernel<<<sm_count * 2, 1024, bytes, stream>>>(b * 0x01010101u, bytes, sink);
+    return cudaGetLastError();
+}
+
 }  // namespace fctc

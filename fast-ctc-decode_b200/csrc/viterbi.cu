@@ -398,9 +398,12 @@ __global__ void __launch_bounds__(VW_THREADS, QSTRING ? VW_MINBLOCKS_Q : VW_MINB
                         if (reach[r]) { tS = S[r]; tn = nr[r]; }
                     const bool whole = c0 && reach[0];  // every row continues the run carried in
                     if (whole && prev0 != 0) tn = -1;   // its tail is unknown until the carry arrives
+                    // The run left open by the previous tile.  The cell is only meaningful when one is open
+                    // (open_in): otherwise shared memory may hold anything there — including the bit pattern
+                    // of the "tail unknown" marker, which would keep the carry loop below spinning.
                     float o_S = 0.0f;
                     int o_n = 0;
-                    if (lane == 0) lds_run(open_addr, o_S, o_n);
+                    if (lane == 0 && open_in) lds_run(open_addr, o_S, o_n);
                     float in_S;
                     int in_n;
                     for (;;) {

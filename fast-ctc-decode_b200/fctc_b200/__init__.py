@@ -75,6 +75,7 @@ _SIGNATURES = {
     "fctc_fastq_records_device": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, C.c_char_p, _i32, C.c_char_p, _i64, _vp,
                                             _i64, _vp, _vp, _i64, _vp]),
     "fctc_synth_posteriors_device": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _i32, _u64, _i64, _vp]),
+    "fctc_test_poison_shared_memory": (C.c_int, [_vp, _i32]),
     "fctc_host_phred": (C.c_uint32, [_f32, _f32, _f32]),
     "fctc_host_log10f": (None, [_vp, _vp, _i64]),
     "fctc_host_logf": (None, [_vp, _vp, _i64]),
@@ -159,6 +160,10 @@ class Decoder:
         self._check(fn(self._h, post_ptr, n_reads, n_rows, n_labels, int(qstring), qscale, qbias, int(collapse_repeats),
                        labels_ptr, quals_ptr or None, qual_bytes, path_ptr, pool_capacity, offsets_ptr, lens_ptr,
                        status_ptr, stream or None))
+
+    def poison_shared_memory(self, byte=0xFF):
+        """Test hook: every SM's shared memory is filled with `byte` before the next kernel starts."""
+        self._check(self._L.fctc_test_poison_shared_memory(self._h, byte))
 
     def fastq_scratch_bytes(self, n_reads):
         return int(self._L.fctc_fastq_scratch_bytes(self._h, n_reads))

@@ -298,6 +298,11 @@ int fctc_fastq_records_device(fctc_handle* h, const uint8_t* labels_dev, const u
 int fctc_synth_posteriors_device(fctc_handle* h, float* post_dev, int64_t n_reads, int64_t n_rows, int32_t n_labels,
                                  int32_t kind, uint64_t seed, int64_t first_read, void* stream);
 
+/* Test hook (replaces nothing): fills every SM's shared memory with `byte` and waits, so that the next
+ * kernels start from a chosen pattern (0xFF = -1 / NaN words) instead of what earlier kernels left.
+ * The GPU test-suite runs every test behind it: no kernel may depend on stale shared memory. */
+int fctc_test_poison_shared_memory(fctc_handle* h, int32_t byte);
+
 /* Host instantiation of the device phred()/log10f code (same source, compiled for the host), so
  * that CPU tests can compare it with glibc without a GPU.  Replaces nothing; test hook. */
 uint32_t fctc_host_phred(float prob, float qscale, float qbias);
