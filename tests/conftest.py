@@ -37,5 +37,5 @@ def poisoned_shared_memory(request):
     import fctc_b200
     if _POISONER is None:
         _POISONER = fctc_b200.Decoder(0)
-    _POISONER.poison_shared_memory(0xFF)
+    _POISONER.poison_shared_memory(int(os.environ.get("FCTC_TEST_POISON", "0xFF"), 0))
     yield
