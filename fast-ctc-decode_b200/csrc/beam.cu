@@ -19,8 +19,11 @@
 //   * merging needs no sort: a node can only receive its own blank/repeat continuation and its
 //     parent's extension (<= 2 non-zero terms per field, so f32 addition order is immaterial);
 //     each hypothesis looks up its parent in the beam and folds that term in itself;
-//   * ranking is a warp-level selection: lanes keep their best unselected candidate, two
-//     REDUX.MAX per rank pick (score, then lowest node id) — no comparison sort.
+//   * ranking is a warp-level selection, no comparison sort: every lane orders its own hypothesis'
+//     C candidates by pairwise counting, then each output rank is one REDUX.MAX over the list
+//     heads; exact score ties (two lanes holding the maximum) are detected afterwards and only
+//     then ranked again with the node-id key (lowest node id first);
+//   * narrow beams (beam_size * labels <= 32) take beam_small.cu instead: one lane per candidate.
 #include <cuda_fp16.h>
 
 #include "device_utils.cuh"
@@ -55,11 +58,6 @@ struct BeamLayout {  // per-warp shared memory plan, in bytes from the warp's ba
     int warp_bytes;
     int rows_per_chunk;
 };
-
-__device__ __forceinline__ uint32_t order_key(float v) {  // monotone map f32 -> u32, >= 1 for non-NaN
-    uint32_t u = __float_as_uint(v);
-    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
-}
 
 struct BeamView {  // one beam buffer
     int* nd;

@@ -40,11 +40,6 @@ constexpr int ROOT = -1;
 constexpr int BS_NODE_BYTES = 32;
 constexpr int BS_WARP_SMEM = 2 * BS_ROWBUF * 4 + 16 + 128;  // row buffers, the root's child row, traceback block heads
 
-__device__ __forceinline__ uint32_t order_key(float v) {  // monotone map f32 -> u32, >= 1 for non-NaN
-    const uint32_t u = __float_as_uint(v);
-    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
-}
-
 #ifndef BS_MINBLOCKS
 #define BS_MINBLOCKS 8
 #endif

@@ -83,6 +83,12 @@ __device__ __forceinline__ float div_keep_zero(float a, float b) {
     return zero_over_finite ? a : q;
 }
 
+// Monotone map f32 -> u32 (bigger float, bigger key; >= 1 for every non-NaN input): ranking by REDUX.MAX.
+__device__ __forceinline__ uint32_t order_key(float v) {
+    const uint32_t u = __float_as_uint(v);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
 __device__ __forceinline__ int warp_inclusive_scan(int v, int lane) {
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {

@@ -54,11 +54,6 @@ __device__ __forceinline__ float lg_add(float a, float b, int mode) {
 }
 __device__ __forceinline__ float lg_max(float a, float b) { return (a < b) ? b : a; }  // src/duplex.rs:33-39
 
-__device__ __forceinline__ uint32_t dx_order_key(float v) {
-    uint32_t u = __float_as_uint(v);
-    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
-}
-
 struct DuplexLayout {  // per-warp shared memory plan (bytes from the warp's base)
     int beam_stride;   // one beam buffer: 7 arrays of B words
     int off_newcnt, off_fold, off_key, off_node, off_lab, off_gap, off_p2, off_sel, off_row, off_root, off_newlist;
@@ -568,7 +563,7 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
                     if (node >= 0) cp2[s] = S.vmx[node];
                     const float tot = __fadd_rn(__fadd_rn(lg_add(clab[s], cgap[s], mode), cp2[s]), 0.0f);
                     if (tot != tot) any_nan = true;
-                    ckey[s] = (tot != tot) ? 1u : dx_order_key(tot);
+                    ckey[s] = (tot != tot) ? 1u : order_key(tot);
                     ++n_cand;
                 }
             }
