@@ -25,6 +25,8 @@
 #include <cstdio>
 #include <cstdlib>
 
+#include <cuda_fp16.h>
+
 #include "device_utils.cuh"
 #include "kernels.h"
 #include "phred.cuh"
@@ -214,6 +216,10 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
         const long long n = (long long)ticket;
         const float* rd1 = p.post1 + n * (long long)T1 * C * NS;
         const float* rd2 = p.post2 + n * (long long)T2 * C * NS;
+        // binary16 posteriors (plain search only): the same rows behind half pointers, widened on load
+        const __half* rh1 = reinterpret_cast<const __half*>(p.post1) + n * (long long)T1 * C;
+        const __half* rh2 = reinterpret_cast<const __half*>(p.post2) + n * (long long)T2 * C;
+        const bool half_in = !CRF && p.in_f16 != 0;
         // network-2 value of row i, state s, column c in log space
         auto lp2 = [&](int i, int s_, int c) -> float {
             if (CRF) return glibc_logf(rd2[((size_t)i * NS + s_) * C + c], s_invc, s_logc);
@@ -224,7 +230,8 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
 
         // network 2 in log space (src/duplex.rs:453)
         if (!CRF)
-            for (int i = lane; i < T2 * C; i += 32) S.logp2[i] = glibc_logf(rd2[i], s_invc, s_logc);
+            for (int i = lane; i < T2 * C; i += 32)
+                S.logp2[i] = glibc_logf(half_in ? __half2float(rh2[i]) : rd2[i], s_invc, s_logc);
         int init_state_1 = 0, init_state_2 = 0;
         if (CRF) {  // argmax of the initial state scores (src/duplex.rs:679, 691); NaN aborts the reference
             bool bad = false;
@@ -294,7 +301,8 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
                 break;
             }
             if (!CRF)
-                for (int c = lane; c < C; c += 32) lp1[c] = glibc_logf(rd1[(size_t)t * C + c], s_invc, s_logc);
+                for (int c = lane; c < C; c += 32)
+                    lp1[c] = glibc_logf(half_in ? __half2float(rh1[(size_t)t * C + c]) : rd1[(size_t)t * C + c], s_invc, s_logc);
             // network-1 value of this row for a hypothesis in state s_, column c
             auto row1 = [&](int s_, int c) -> float {
                 if (CRF) return glibc_logf(rd1[((size_t)t * NS + s_) * C + c], s_invc, s_logc);
@@ -770,15 +778,15 @@ extern "C" int64_t fctc_duplex_scratch_bytes(const fctc_handle* h, int64_t n_pai
                                       nodes_per_row, int64_t(96) << 30, nullptr, nullptr);
 }
 
-extern "C" int fctc_beam_search_duplex_batch_device(fctc_handle* h, const float* post1_dev, const float* post2_dev,
-                                                    int64_t n_pairs, int64_t n_rows_1, int64_t n_rows_2,
-                                                    int32_t n_labels, const int64_t* envelope_dev, int32_t max_window,
-                                                    int32_t beam_size, float beam_cut_threshold,
-                                                    int32_t collapse_repeats, int32_t exp_mode, uint8_t* labels_dev,
-                                                    int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev,
-                                                    int32_t* status_dev, unsigned long long* pool_used_dev,
-                                                    void* scratch_dev, int64_t scratch_bytes, int32_t nodes_per_row,
-                                                    void* stream) {
+static int dx_batch_device_any(fctc_handle* h, const void* post1_dev, const void* post2_dev, int in_f16,
+                               int64_t n_pairs, int64_t n_rows_1, int64_t n_rows_2,
+                               int32_t n_labels, const int64_t* envelope_dev, int32_t max_window,
+                               int32_t beam_size, float beam_cut_threshold,
+                               int32_t collapse_repeats, int32_t exp_mode, uint8_t* labels_dev,
+                               int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev,
+                               int32_t* status_dev, unsigned long long* pool_used_dev,
+                               void* scratch_dev, int64_t scratch_bytes, int32_t nodes_per_row,
+                               void* stream) {
     if (int rc = dx_check(h, n_pairs, n_rows_1, n_rows_2, n_labels, beam_size, beam_cut_threshold)) return rc;
     if (!post1_dev || !post2_dev || !labels_dev || !offsets_dev || !lens_dev || !status_dev || !pool_used_dev || !scratch_dev)
         return fctc::handle_fail(h, FCTC_E_ARGUMENT, "null device pointer");
@@ -798,7 +806,8 @@ extern "C" int fctc_beam_search_duplex_batch_device(fctc_handle* h, const float*
                  (long long)scratch_bytes, (long long)need, p.n_slots);
         return fctc::handle_fail(h, FCTC_E_CAPACITY, msg);
     }
-    p.post1 = post1_dev; p.post2 = post2_dev; p.env = reinterpret_cast<const long long*>(envelope_dev);
+    p.post1 = static_cast<const float*>(post1_dev); p.post2 = static_cast<const float*>(post2_dev); p.in_f16 = in_f16;
+    p.env = reinterpret_cast<const long long*>(envelope_dev);
     p.N = n_pairs; p.T1 = int(n_rows_1); p.T2 = int(n_rows_2); p.C = n_labels; p.beam_size = beam_size;
     p.threshold = beam_cut_threshold; p.collapse = collapse_repeats; p.exp_mode = exp_mode;
     p.labels = labels_dev; p.pool_cap = pool_capacity; p.offsets = offsets_dev; p.lens = lens_dev; p.status = status_dev;
@@ -806,6 +815,36 @@ extern "C" int fctc_beam_search_duplex_batch_device(fctc_handle* h, const float*
     e = fctc::launch_duplex(p, static_cast<cudaStream_t>(stream));
     if (e != cudaSuccess) return fctc::handle_fail(h, FCTC_E_CUDA, cudaGetErrorString(e));
     return 0;
+}
+
+extern "C" int fctc_beam_search_duplex_batch_device(fctc_handle* h, const float* post1_dev, const float* post2_dev,
+                                                    int64_t n_pairs, int64_t n_rows_1, int64_t n_rows_2,
+                                                    int32_t n_labels, const int64_t* envelope_dev, int32_t max_window,
+                                                    int32_t beam_size, float beam_cut_threshold,
+                                                    int32_t collapse_repeats, int32_t exp_mode, uint8_t* labels_dev,
+                                                    int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev,
+                                                    int32_t* status_dev, unsigned long long* pool_used_dev,
+                                                    void* scratch_dev, int64_t scratch_bytes, int32_t nodes_per_row,
+                                                    void* stream) {
+    return dx_batch_device_any(h, post1_dev, post2_dev, 0, n_pairs, n_rows_1, n_rows_2, n_labels, envelope_dev, max_window,
+                               beam_size, beam_cut_threshold, collapse_repeats, exp_mode, labels_dev, pool_capacity,
+                               offsets_dev, lens_dev, status_dev, pool_used_dev, scratch_dev, scratch_bytes, nodes_per_row,
+                               stream);
+}
+
+extern "C" int fctc_beam_search_duplex_batch_device_f16(fctc_handle* h, const void* post1_dev_f16,
+                                                        const void* post2_dev_f16, int64_t n_pairs, int64_t n_rows_1,
+                                                        int64_t n_rows_2, int32_t n_labels, const int64_t* envelope_dev,
+                                                        int32_t max_window, int32_t beam_size, float beam_cut_threshold,
+                                                        int32_t collapse_repeats, int32_t exp_mode, uint8_t* labels_dev,
+                                                        int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev,
+                                                        int32_t* status_dev, unsigned long long* pool_used_dev,
+                                                        void* scratch_dev, int64_t scratch_bytes, int32_t nodes_per_row,
+                                                        void* stream) {
+    return dx_batch_device_any(h, post1_dev_f16, post2_dev_f16, 1, n_pairs, n_rows_1, n_rows_2, n_labels, envelope_dev,
+                               max_window, beam_size, beam_cut_threshold, collapse_repeats, exp_mode, labels_dev,
+                               pool_capacity, offsets_dev, lens_dev, status_dev, pool_used_dev, scratch_dev, scratch_bytes,
+                               nodes_per_row, stream);
 }
 
 namespace {
@@ -989,7 +1028,8 @@ extern "C" int fctc_crf_beam_search_duplex_batch_device(
     const int64_t need = fctc::duplex_scratch_bytes(fctc::handle_sm_count(h), n_pairs, int(n_rows_1), int(n_rows_2), n_labels,
                                                     beam_size, p.W, nodes_per_row, scratch_bytes, &p.nodes_per_slot, &p.n_slots);
     if (need > scratch_bytes) return fctc::handle_fail(h, FCTC_E_CAPACITY, "duplex scratch too small (see fctc_duplex_scratch_bytes)");
-    p.post1 = post1_dev; p.post2 = post2_dev; p.env = reinterpret_cast<const long long*>(envelope_dev);
+    p.post1 = static_cast<const float*>(post1_dev); p.post2 = static_cast<const float*>(post2_dev); p.in_f16 = 0;
+    p.env = reinterpret_cast<const long long*>(envelope_dev);
     p.N = n_pairs; p.T1 = int(n_rows_1); p.T2 = int(n_rows_2); p.C = n_labels; p.beam_size = beam_size;
     p.threshold = beam_cut_threshold; p.collapse = 0; p.exp_mode = exp_mode;
     p.labels = labels_dev; p.pool_cap = pool_capacity; p.offsets = offsets_dev; p.lens = lens_dev; p.status = status_dev;

@@ -87,6 +87,7 @@ cudaError_t launch_beam_small(const BeamParams& p, cudaStream_t stream);
 struct DuplexParams {
     const float* post1;    // [N, T1, C]
     const float* post2;    // [N, T2, C]
+    int in_f16;            // 1: both are binary16 behind the same pointers, widened exactly to f32 on load (plain search only)
     const long long* env;  // [N, T1, 2] network-2 row bounds per network-1 row, or NULL (= [0, T2) everywhere)
     int64_t N;
     int T1, T2, C;

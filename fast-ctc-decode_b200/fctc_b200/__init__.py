@@ -55,6 +55,9 @@ _SIGNATURES = {
     "fctc_beam_search_duplex_batch_device": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i64, _i32, _vp, _i32, _i32, _f32,
                                                        _i32, _i32, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _i64, _i32,
                                                        _vp]),
+    "fctc_beam_search_duplex_batch_device_f16": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i64, _i32, _vp, _i32, _i32, _f32,
+                                                           _i32, _i32, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _i64, _i32,
+                                                           _vp]),
     "fctc_beam_search_duplex_batch": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i64, _i32, _vp, _i32, _f32, _i32, _i32,
                                                 _vp, _i64, _vp, _vp, _vp, _vp]),
     "fctc_beam_search_duplex": (C.c_int, [_vp, _vp, _i64, _i64, _i64, _vp, _i64, _i64, _i64, _i32, _vp, _i64, _i64,
@@ -198,8 +201,9 @@ class Decoder:
     def beam_search_duplex_batch_device(self, post1_ptr, post2_ptr, n_pairs, n_rows_1, n_rows_2, n_labels, envelope_ptr,
                                         max_window, beam_size, beam_cut_threshold, collapse_repeats, exp_mode,
                                         labels_ptr, pool_capacity, offsets_ptr, lens_ptr, status_ptr, pool_used_ptr,
-                                        scratch_ptr, scratch_bytes, nodes_per_row=0, stream=0):
-        self._check(self._L.fctc_beam_search_duplex_batch_device(self._h, post1_ptr, post2_ptr, n_pairs, n_rows_1,
+                                        scratch_ptr, scratch_bytes, nodes_per_row=0, stream=0, f16=False):
+        fn = self._L.fctc_beam_search_duplex_batch_device_f16 if f16 else self._L.fctc_beam_search_duplex_batch_device
+        self._check(fn(self._h, post1_ptr, post2_ptr, n_pairs, n_rows_1,
                                                                  n_rows_2, n_labels, envelope_ptr or None, max_window,
                                                                  beam_size, beam_cut_threshold, int(collapse_repeats),
                                                                  exp_mode, labels_ptr, pool_capacity, offsets_ptr,

@@ -210,6 +210,20 @@ int fctc_beam_search_duplex_batch_device(fctc_handle* h, const float* post1_dev,
                                          uint8_t* labels_dev, int64_t pool_capacity, int64_t* offsets_dev,
                                          int32_t* lens_dev, int32_t* status_dev, unsigned long long* pool_used_dev,
                                          void* scratch_dev, int64_t scratch_bytes, int32_t nodes_per_row, void* stream);
+
+/* fctc_beam_search_duplex_batch_device_f16: the device entry point above for binary16 posteriors
+ * (no counterpart in the reference).  Both networks are widened
+ * exactly to float32 as they are read, before the log mapping. */
+int fctc_beam_search_duplex_batch_device_f16(fctc_handle* h, const void* post1_dev_f16, const void* post2_dev_f16,
+                                             int64_t n_pairs, int64_t n_rows_1, int64_t n_rows_2, int32_t n_labels,
+                                             const int64_t* envelope_dev, int32_t max_window, int32_t beam_size,
+                                             float beam_cut_threshold, int32_t collapse_repeats, int32_t exp_mode,
+                                             uint8_t* labels_dev, int64_t pool_capacity, int64_t* offsets_dev,
+                                             int32_t* lens_dev, int32_t* status_dev, unsigned long long* pool_used_dev,
+                                             void* scratch_dev, int64_t scratch_bytes, int32_t nodes_per_row,
+                                             void* stream);
+
+
 int fctc_beam_search_duplex_batch(fctc_handle* h, const float* post1_host, const float* post2_host, int64_t n_pairs,
                                   int64_t n_rows_1, int64_t n_rows_2, int32_t n_labels, const int64_t* envelope_host,
                                   int32_t beam_size, float beam_cut_threshold, int32_t collapse_repeats,

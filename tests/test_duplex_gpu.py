@@ -111,3 +111,37 @@ def test_single_pair_with_envelope_and_strides(dec, oracle):
     st, labels = dec.beam_search_duplex(big1[::2, ::2], p2[0], env, 5, 0.0, True, exp_mode=1)
     ost, ol = oracle.beam_search_duplex(p1[0], p2[0], env, 5, 0.0, True, exp_mode=1)
     assert st == ost == 0 and labels.tolist() == ol.tolist()
+
+
+def test_f16_posteriors_device_batch(dec, oracle):
+    """Binary16 posteriors through the device entry point: identical to the oracle on the exactly widened
+    arrays (max-plus mode, which is bit-exact)."""
+    import torch
+    N, T1, T2, Cn, beam, w = 24, 300, 320, 5, 5, 12
+    rng = np.random.default_rng(555)
+    p1, p2 = duplex_pairs(rng, N, T1, T2, Cn)
+    h1, h2 = p1.astype(np.float16), p2.astype(np.float16)
+    env = band_envelope(N, T1, T2, w)
+    dev = torch.device("cuda:0")
+    st = torch.cuda.current_stream().cuda_stream
+    d1, d2, de = torch.from_numpy(h1).to(dev), torch.from_numpy(h2).to(dev), torch.from_numpy(env).to(dev)
+    stride = (T1 + 31) // 32 * 32
+    cap = N * stride
+    labels = torch.empty(cap, dtype=torch.uint8, device=dev)
+    offsets = torch.empty(N, dtype=torch.int64, device=dev)
+    lens = torch.empty(N, dtype=torch.int32, device=dev)
+    status = torch.empty(N, dtype=torch.int32, device=dev)
+    used = torch.zeros(1, dtype=torch.int64, device=dev)
+    mw = 2 * w + 1
+    nbytes = dec.duplex_scratch_bytes(N, T1, T2, Cn, beam, mw, 0)
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    dec.beam_search_duplex_batch_device(d1.data_ptr(), d2.data_ptr(), N, T1, T2, Cn, de.data_ptr(), mw, beam, 0.0, True, 1,
+                                        labels.data_ptr(), cap, offsets.data_ptr(), lens.data_ptr(), status.data_ptr(),
+                                        used.data_ptr(), scratch.data_ptr(), nbytes, 0, st, f16=True)
+    torch.cuda.synchronize()
+    ol, olen, ost = oracle.beam_search_duplex_batch(h1.astype(np.float32), h2.astype(np.float32), env.astype(np.uint64),
+                                                    beam, 0.0, True, exp_mode=1)
+    lab, off, ln, stt = labels.cpu().numpy(), offsets.cpu().numpy(), lens.cpu().numpy(), status.cpu().numpy()
+    assert stt.tolist() == ost.tolist()
+    for n in range(N):
+        assert lab[off[n]:off[n] + ln[n]].tolist() == ol[n, :olen[n]].tolist()
