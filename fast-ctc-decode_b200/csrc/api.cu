@@ -823,6 +823,26 @@ int fctc_fastq_records_device(fctc_handle* h, const uint8_t* labels_dev, const u
     return 0;
 }
 
+int fctc_duplex_envelope_device(fctc_handle* h, const int32_t* path1_dev, const int64_t* offsets1_dev,
+                                const int32_t* lens1_dev, const int32_t* path2_dev, const int64_t* offsets2_dev,
+                                const int32_t* lens2_dev, int64_t n_pairs, int64_t n_rows_1, int64_t n_rows_2,
+                                int32_t pad_rows, int64_t* envelope_dev, int32_t* max_window_dev, void* stream) {
+    if (!h) return FCTC_E_ARGUMENT;
+    if (n_pairs < 0 || n_rows_1 <= 0 || n_rows_2 <= 0 || pad_rows < 0)
+        return fail(h, FCTC_E_ARGUMENT, "n_pairs >= 0, n_rows_1 > 0, n_rows_2 > 0 and pad_rows >= 0 are required");
+    if (!path1_dev || !offsets1_dev || !lens1_dev || !path2_dev || !offsets2_dev || !lens2_dev || !envelope_dev)
+        return fail(h, FCTC_E_ARGUMENT, "null device pointer");
+    FCTC_CUDA(h, cudaSetDevice(h->device));
+    fctc::EnvelopeParams p{};
+    p.path1 = path1_dev; p.offsets1 = offsets1_dev; p.lens1 = lens1_dev;
+    p.path2 = path2_dev; p.offsets2 = offsets2_dev; p.lens2 = lens2_dev;
+    p.N = n_pairs; p.T1 = n_rows_1; p.T2 = n_rows_2; p.pad = pad_rows;
+    p.env = reinterpret_cast<long long*>(envelope_dev);
+    p.max_window = max_window_dev;
+    FCTC_CUDA(h, fctc::launch_envelope(p, static_cast<cudaStream_t>(stream)));
+    return 0;
+}
+
 // ---------------------------------------------------------------------------------------------
 // Synthetic input + host test hooks
 // ---------------------------------------------------------------------------------------------

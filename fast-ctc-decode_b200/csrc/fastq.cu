@@ -176,3 +176,85 @@ cudaError_t launch_fastq(const FastqParams& p, long long* rec_off, void* scratch
 }
 
 }  // namespace fctc
+
+// ---------------------------------------------------------------------------------------------
+// Duplex envelope from the two reads' Viterbi paths.
+//
+// The reference leaves the envelope to the caller (src/lib.rs:376-378).  This constructor needs no
+// aligner: base k of read 1 is anchored to base (k * L2) / L1 of read 2 — the two calls of one
+// molecule have nearly the same length, while their translocation speeds (rows per base) differ
+// locally, which a band that is diagonal in ROWS cannot follow.  For network-1 row t, with k(t) bases
+// of read 1 emitted at or before t:
+//     c(t) = path2[((k-1) * L2) / L1]                      k >= 1
+//          = min(path2[0], (t * T2) / T1)                  k == 0
+//          = (t * T2) / T1                                 either read empty
+//     hi(t) = min(T2, c(t) + pad + 1)
+//     lo(t) = min(max(0, c(t) - pad), hi(t-1))             (lo(0) without the second term)
+// c is non-decreasing, so hi is, and lo(t) <= hi(t-1) < ... keeps the reference's validity rule
+// (lo < hi, lo <= previous hi; src/duplex.rs:484-488).  One thread per (pair, row): a binary search
+// in read 1's emission rows, two loads from read 2's.
+// ---------------------------------------------------------------------------------------------
+namespace fctc {
+
+namespace {
+
+__device__ __forceinline__ long long env_center(const EnvelopeParams& p, long long n, long long t) {
+    const int L1 = p.lens1[n], L2 = p.lens2[n];
+    const long long prop = (t * p.T2) / p.T1;
+    if (L1 <= 0 || L2 <= 0) return prop < p.T2 ? prop : p.T2 - 1;
+    const int* a = p.path1 + p.offsets1[n];
+    const int* b = p.path2 + p.offsets2[n];
+    int lo = 0, hi = L1;  // k = number of entries of a[] that are <= t
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (a[mid] <= t) lo = mid + 1; else hi = mid;
+    }
+    const int k = lo;
+    if (k == 0) {
+        const long long first = b[0];
+        return prop < first ? prop : first;
+    }
+    return b[(long long)(k - 1) * L2 / L1];
+}
+
+__global__ void __launch_bounds__(256) envelope_kernel(const EnvelopeParams p) {
+    const long long total = p.N * p.T1;
+    int widest = 0;
+    for (long long g = blockIdx.x * (long long)blockDim.x + threadIdx.x; g < total; g += (long long)gridDim.x * blockDim.x) {
+        const long long n = g / p.T1, t = g - n * p.T1;
+        const long long c = env_center(p, n, t);
+        long long hi = c + p.pad + 1;
+        if (hi > p.T2) hi = p.T2;
+        long long lo = c - p.pad;
+        if (lo < 0) lo = 0;
+        if (t > 0) {
+            long long ph = env_center(p, n, t - 1) + p.pad + 1;
+            if (ph > p.T2) ph = p.T2;
+            if (lo > ph) lo = ph;
+        }
+        p.env[2 * g] = lo;
+        p.env[2 * g + 1] = hi;
+        if (p.max_window && int(hi - lo) > widest) widest = int(hi - lo);
+    }
+    if (p.max_window) {  // one atomic per warp: the widest window is what the duplex kernel sizes its rings by
+        widest = __reduce_max_sync(0xffffffffu, widest);
+        if ((threadIdx.x & 31) == 0 && widest > 0) atomicMax(p.max_window, widest);
+    }
+}
+
+}  // namespace
+
+cudaError_t launch_envelope(const EnvelopeParams& p, cudaStream_t stream) {
+    const long long total = p.N * p.T1;
+    if (total <= 0) return cudaSuccess;
+    long long blocks = (total + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    if (p.max_window) {
+        cudaError_t e = cudaMemsetAsync(p.max_window, 0, sizeof(int), stream);
+        if (e != cudaSuccess) return e;
+    }
+    envelope_kernel<<<(unsigned)blocks, 256, 0, stream>>>(p);
+    return cudaGetLastError();
+}
+
+}  // namespace fctc

@@ -135,6 +135,20 @@ struct FastqParams {
 int64_t fastq_scratch_bytes(int64_t N);
 cudaError_t launch_fastq(const FastqParams& p, long long* rec_off, void* scratch, cudaStream_t stream);
 
+// duplex envelope from the two reads' Viterbi paths (fastq.cu)
+struct EnvelopeParams {
+    const int32_t* path1;    // slot-form emission rows of read 1 / read 2
+    const int64_t* offsets1;
+    const int32_t* lens1;
+    const int32_t* path2;
+    const int64_t* offsets2;
+    const int32_t* lens2;
+    int64_t N, T1, T2;
+    int64_t pad;             // half-width of the window, in network-2 rows
+    long long* env;          // [N, T1, 2]
+    int* max_window;         // optional: receives the widest window (hi - lo) of the whole batch
+};
+cudaError_t launch_envelope(const EnvelopeParams& p, cudaStream_t stream);
 cudaError_t launch_poison_smem(int sm_count, int byte, unsigned int* sink, cudaStream_t stream);
 cudaError_t launch_synth(float* post, int64_t N, int64_t T, int C, int kind, uint64_t seed, int64_t first_read,
                          cudaStream_t stream);

@@ -77,6 +77,7 @@ _SIGNATURES = {
     "fctc_fastq_scratch_bytes": (_i64, [_vp, _i64]),
     "fctc_fastq_records_device": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, C.c_char_p, _i32, C.c_char_p, _i64, _vp,
                                             _i64, _vp, _vp, _i64, _vp]),
+    "fctc_duplex_envelope_device": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i32, _vp, _vp, _vp]),
     "fctc_synth_posteriors_device": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _i32, _u64, _i64, _vp]),
     "fctc_test_poison_shared_memory": (C.c_int, [_vp, _i32]),
     "fctc_host_phred": (C.c_uint32, [_f32, _f32, _f32]),
@@ -163,6 +164,13 @@ class Decoder:
         self._check(fn(self._h, post_ptr, n_reads, n_rows, n_labels, int(qstring), qscale, qbias, int(collapse_repeats),
                        labels_ptr, quals_ptr or None, qual_bytes, path_ptr, pool_capacity, offsets_ptr, lens_ptr,
                        status_ptr, stream or None))
+
+    def duplex_envelope_device(self, path1_ptr, offsets1_ptr, lens1_ptr, path2_ptr, offsets2_ptr, lens2_ptr, n_pairs,
+                               n_rows_1, n_rows_2, pad_rows, envelope_ptr, max_window_ptr=0, stream=0):
+        """int64 [n_pairs, n_rows_1, 2] envelope from the two reads' slot-form Viterbi paths."""
+        self._check(self._L.fctc_duplex_envelope_device(self._h, path1_ptr, offsets1_ptr, lens1_ptr, path2_ptr,
+                                                        offsets2_ptr, lens2_ptr, n_pairs, n_rows_1, n_rows_2, pad_rows,
+                                                        envelope_ptr, max_window_ptr or None, stream or None))
 
     def poison_shared_memory(self, byte=0xFF):
         """Test hook: every SM's shared memory is filled with `byte` before the next kernel starts."""

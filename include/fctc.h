@@ -303,6 +303,25 @@ int fctc_fastq_records_device(fctc_handle* h, const uint8_t* labels_dev, const u
                               void* scratch_dev, int64_t scratch_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Duplex envelope from the two reads' Viterbi paths — SURVEY.md section 8(f) rank 4; no counterpart
+ * in the reference, which leaves the envelope to the caller (src/lib.rs:376-378).  Inputs are the
+ * slot-form path / offsets / lens arrays of fctc_viterbi_batch_device run on both networks of every
+ * pair.  No aligner: base k of read 1 is anchored to base (k * len2) / len1 of read 2, and row t of
+ * network 1 gets the window [c - pad_rows, c + pad_rows + 1) around the network-2 row c of its
+ * anchor (clamped to [0, n_rows_2), lower bound pulled down to the previous row's upper bound so
+ * that the envelope passes the reference's validity rule, src/duplex.rs:484-488; pairs with an
+ * empty read get the plain diagonal band).  Where the anchor jumps (a stretch of read 2 without
+ * bases) a window is wider than 2 * pad_rows + 1; max_window_dev (optional, one int32 on the
+ * device) receives the widest window of the batch, the max_window to hand to
+ * fctc_beam_search_duplex_batch_device.
+ * envelope_dev: int64 [n_pairs, n_rows_1, 2], ready for fctc_beam_search_duplex_batch_device.
+ * ------------------------------------------------------------------------------------------ */
+int fctc_duplex_envelope_device(fctc_handle* h, const int32_t* path1_dev, const int64_t* offsets1_dev,
+                                const int32_t* lens1_dev, const int32_t* path2_dev, const int64_t* offsets2_dev,
+                                const int32_t* lens2_dev, int64_t n_pairs, int64_t n_rows_1, int64_t n_rows_2,
+                                int32_t pad_rows, int64_t* envelope_dev, int32_t* max_window_dev, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * Synthetic posterior generator used by bench.py and the tests (no reference counterpart; it
  * implements SURVEY.md §8d's input definition): fills post_dev[n_reads, n_rows, n_labels] with
  * kind 0: softmax(3*(2u-1)) rows, kind 1: peaked rows (dominant label, blank w.p. 0.65), kind 2: kind
