@@ -11,7 +11,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libfctc_b200.so")
-SOURCES = ["api.cu", "viterbi.cu", "beam.cu", "beam_small.cu", "duplex.cu", "crf.cu", "fastq.cu", "synth.cu"]
+SOURCES = ["api.cu", "viterbi.cu", "beam.cu", "beam_small.cu", "duplex.cu", "crf.cu", "fastq.cu", "pack.cu", "synth.cu"]
 HEADERS = ["kernels.h", "device_utils.cuh", "phred.cuh", os.path.join("..", "..", "include", "fctc.h")]
 
 NVCC_FLAGS = [
@@ -21,8 +21,9 @@ NVCC_FLAGS = [
     # denormals kept (all are nvcc defaults except -fmad)
     "-fmad=false", "-prec-div=true", "-prec-sqrt=true", "-ftz=false",
     "-Xcompiler", "-fPIC,-ffp-contract=off,-fno-fast-math",
-    "-shared", "-cudart", "static",
 ]
+LINK_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-cudart", "static"]
+OBJ_DIR = os.path.join(HERE, "build")
 
 
 def needs_build():
@@ -34,10 +35,27 @@ def needs_build():
 
 
 def build(force=False, verbose=False):
+    """Every .cu is compiled to its own object (in parallel, only when it or a header changed), then linked."""
     if not force and not needs_build():
         return OUT
-    srcs = [os.path.join(CSRC, s) for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
-    cmd = ["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", OUT] + srcs
+    os.makedirs(OBJ_DIR, exist_ok=True)
+    hdr_time = max(os.path.getmtime(os.path.join(CSRC, h)) for h in HEADERS if os.path.exists(os.path.join(CSRC, h)))
+    hdr_time = max(hdr_time, os.path.getmtime(os.path.abspath(__file__)))
+    jobs, objs = [], []
+    for name in SOURCES:
+        src = os.path.join(CSRC, name)
+        if not os.path.exists(src):
+            continue
+        obj = os.path.join(OBJ_DIR, name.replace(".cu", ".o"))
+        objs.append(obj)
+        if force or not os.path.exists(obj) or os.path.getmtime(obj) < max(os.path.getmtime(src), hdr_time):
+            cmd = ["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", "-o", obj, src]
+            print(" ".join(cmd), file=sys.stderr)
+            jobs.append((name, subprocess.Popen(cmd)))
+    failed = [name for name, proc in jobs if proc.wait() != 0]
+    if failed:
+        raise SystemExit("nvcc failed for: " + ", ".join(failed))
+    cmd = ["nvcc"] + LINK_FLAGS + ["-o", OUT] + objs
     print(" ".join(cmd), file=sys.stderr)
     subprocess.check_call(cmd)
     return OUT

@@ -29,6 +29,7 @@ struct Slot {  // one in-flight chunk of the host-memory pipeline
     cudaEvent_t done = nullptr;
     cudaEvent_t kernel_done = nullptr;  // the chunk's kernel alone (chunks that share one trie scratch run in turn)
     DevBuf post, labels, quals, path, offsets, lens, status, cursor, scratch;
+    DevBuf slot_labels, slot_quals, slot_path, slot_offsets;  // slot-form results ahead of the packing step
     unsigned long long* cursor_host = nullptr;  // pinned
     int64_t dst_first = 0, count = 0;           // result rows of the chunk in flight
     bool busy = false;
@@ -185,7 +186,8 @@ void fctc_destroy(fctc_handle* h) {
     cudaSetDevice(h->device);
     for (Slot& s : h->slot) {
         if (s.stream) cudaStreamSynchronize(s.stream);
-        for (DevBuf* b : {&s.post, &s.labels, &s.quals, &s.path, &s.offsets, &s.lens, &s.status, &s.cursor, &s.scratch})
+        for (DevBuf* b : {&s.post, &s.labels, &s.quals, &s.path, &s.offsets, &s.lens, &s.status, &s.cursor, &s.scratch,
+                          &s.slot_labels, &s.slot_quals, &s.slot_path, &s.slot_offsets})
             release(*b);
         if (s.cursor_host) cudaFreeHost(s.cursor_host);
         if (s.done) cudaEventDestroy(s.done);
@@ -319,7 +321,7 @@ int host_pipeline(fctc_handle* h, const void* post_host_any, int elem_bytes, int
     }
     // FCTC_TRACE_PIPELINE=1 prints, per chunk, when its copy-in started / ended and when its kernel ended
     // (milliseconds on the device clock since the first chunk was queued): a development aid.
-    const bool trace = getenv("FCTC_TRACE_PIPELINE") != nullptr;
+    static const bool trace = getenv("FCTC_TRACE_PIPELINE") != nullptr;
     std::vector<cudaEvent_t> tev;
     auto mark = [&](cudaStream_t st) {
         if (!trace) return;
@@ -455,6 +457,83 @@ int viterbi_batch_any(fctc_handle* h, const void* post_host_any, int in_f16, int
 }
 }  // namespace
 
+namespace {
+// fctc_viterbi_batch_packed: the chunk's kernel writes slot form into side buffers, pack.cu squeezes the used
+// prefixes into the slot's result buffers, and the shared host pipeline reads back just those (its per-chunk
+// cursor tells the host how many entries that is).
+int viterbi_batch_packed_any(fctc_handle* h, const void* post_host, int in_f16, int64_t n_reads, int64_t n_rows,
+                             int32_t n_labels, int32_t qstring, float qscale, float qbias, int32_t collapse_repeats,
+                             uint8_t* labels, void* quals, int32_t qual_bytes, int32_t* path, int64_t pool_capacity,
+                             int64_t* offsets, int32_t* lens, int32_t* status, int64_t* pool_used) {
+    const int elem_bytes = in_f16 ? 2 : 4;
+    if (int rc = check_common(h, n_reads, n_rows, n_labels)) return rc;
+    if (n_rows == 0) return fail(h, FCTC_E_ARGUMENT, "n_rows must be >= 1 (the reference asserts a non-empty matrix)");
+    if (!post_host || !labels || !path || !offsets || !lens || !status)
+        return fail(h, FCTC_E_ARGUMENT, "null host pointer");
+    if (qstring && !quals) return fail(h, FCTC_E_ARGUMENT, "qstring requested but quals is NULL");
+    if (qual_bytes != 1 && qual_bytes != 4) return fail(h, FCTC_E_ARGUMENT, "qual_bytes must be 1 or 4");
+    if (qstring && qual_bytes == 1 && !quality_fits_u8(qscale, qbias))
+        return fail(h, FCTC_E_ARGUMENT, "qual_bytes=1 cannot hold the quality codes of qscale=%g qbias=%g; use 4", qscale,
+                    qbias);
+    if (pool_used) *pool_used = 0;
+    FCTC_CUDA(h, cudaSetDevice(h->device));
+    if (n_reads == 0) return 0;
+    const int64_t stride = roundup32(n_rows);
+    const int64_t read_bytes = n_rows * int64_t(n_labels) * elem_bytes;
+    const int64_t chunk = std::min(default_chunk_reads(read_bytes), n_reads);
+    for (int i = 0; i < 2; ++i) {
+        Slot& s = h->slot[i];
+        if (int rc = ensure(h, s.slot_labels, size_t(chunk * stride))) return rc;
+        if (int rc = ensure(h, s.slot_path, size_t(chunk * stride) * 4)) return rc;
+        if (qstring)
+            if (int rc = ensure(h, s.slot_quals, size_t(chunk * stride) * qual_bytes)) return rc;
+        if (int rc = ensure(h, s.slot_offsets, size_t(chunk) * 8)) return rc;
+    }
+    HostOut out{labels, qstring ? quals : nullptr, qual_bytes, path, pool_capacity, offsets, lens, status};
+    auto launch = [&](Slot& s, int64_t cnt) -> int {
+        fctc::ViterbiParams p{};
+        p.post = static_cast<const float*>(s.post.p); p.in_f16 = in_f16; p.N = cnt; p.T = n_rows; p.C = n_labels;
+        p.qstring = qstring; p.qscale = qscale; p.qbias = qbias; p.collapse = collapse_repeats;
+        p.labels = static_cast<uint8_t*>(s.slot_labels.p); p.quals = s.slot_quals.p; p.qual_bytes = qual_bytes;
+        p.path = static_cast<int32_t*>(s.slot_path.p); p.slot_stride = stride; p.offset_base = 0;
+        p.offsets = static_cast<int64_t*>(s.slot_offsets.p); p.lens = static_cast<int32_t*>(s.lens.p);
+        p.status = static_cast<int32_t*>(s.status.p);
+        FCTC_CUDA(h, fctc::launch_viterbi(p, h->sm_count, s.stream, nullptr));
+        fctc::PackParams k{};
+        k.labels = p.labels; k.quals = qstring ? s.slot_quals.p : nullptr; k.qual_bytes = qual_bytes; k.path = p.path;
+        k.offsets = p.offsets; k.offset_base = 0; k.lens = p.lens; k.N = cnt;
+        k.out_labels = static_cast<uint8_t*>(s.labels.p); k.out_quals = s.quals.p;
+        k.out_path = static_cast<int32_t*>(s.path.p); k.out_offsets = static_cast<int64_t*>(s.offsets.p);
+        k.out_capacity = cnt * stride; k.cursor = static_cast<unsigned long long*>(s.cursor.p);
+        FCTC_CUDA(h, fctc::launch_pack(k, h->sm_count, s.stream));
+        return 0;
+    };
+    if (int rc = host_pipeline(h, post_host, elem_bytes, n_reads, n_rows, n_labels, out, chunk, launch)) return rc;
+    if (pool_used) *pool_used = out.used;
+    if (out.overflow)
+        return fail(h, FCTC_E_CAPACITY, "result pool too small: %lld entries given (n_reads*round_up(n_rows,32) always suffices)",
+                    (long long)pool_capacity);
+    return 0;
+}
+}  // namespace
+
+int fctc_viterbi_batch_packed(fctc_handle* h, const float* post_host, int64_t n_reads, int64_t n_rows, int32_t n_labels,
+                              int32_t qstring, float qscale, float qbias, int32_t collapse_repeats, uint8_t* labels,
+                              void* quals, int32_t qual_bytes, int32_t* path, int64_t pool_capacity, int64_t* offsets,
+                              int32_t* lens, int32_t* status, int64_t* pool_used) {
+    return viterbi_batch_packed_any(h, post_host, 0, n_reads, n_rows, n_labels, qstring, qscale, qbias, collapse_repeats,
+                                    labels, quals, qual_bytes, path, pool_capacity, offsets, lens, status, pool_used);
+}
+
+int fctc_viterbi_batch_packed_f16(fctc_handle* h, const void* post_host_f16, int64_t n_reads, int64_t n_rows,
+                                  int32_t n_labels, int32_t qstring, float qscale, float qbias, int32_t collapse_repeats,
+                                  uint8_t* labels, void* quals, int32_t qual_bytes, int32_t* path, int64_t pool_capacity,
+                                  int64_t* offsets, int32_t* lens, int32_t* status, int64_t* pool_used) {
+    return viterbi_batch_packed_any(h, post_host_f16, 1, n_reads, n_rows, n_labels, qstring, qscale, qbias,
+                                    collapse_repeats, labels, quals, qual_bytes, path, pool_capacity, offsets, lens, status,
+                                    pool_used);
+}
+
 int fctc_viterbi_batch(fctc_handle* h, const float* post_host, int64_t n_reads, int64_t n_rows, int32_t n_labels,
                        int32_t qstring, float qscale, float qbias, int32_t collapse_repeats, uint8_t* labels,
                        void* quals, int32_t qual_bytes, int32_t* path, int64_t pool_capacity, int64_t* offsets,
@@ -557,6 +636,11 @@ int check_beam(fctc_handle* h, int32_t n_labels, int32_t beam_size, float thr) {
 }  // namespace
 
 namespace fctc {
+int env_knob(const char* name) {
+    const char* e = getenv(name);
+    const long long v = e ? atoll(e) : 0;
+    return v > 0 && v < (1ll << 31) ? int(v) : 0;
+}
 int handle_device(const fctc_handle* h) { return h->device; }
 int handle_sm_count(const fctc_handle* h) { return h->sm_count; }
 int handle_fail(fctc_handle* h, int code, const char* message) { return fail(h, code, "%s", message); }
@@ -669,7 +753,8 @@ int beam_host_pass(fctc_handle* h, const void* post_host, int in_f16, int64_t n_
     const int64_t read_bytes = std::max<int64_t>(n_rows * int64_t(n_labels) * elem_bytes, 1);
     int64_t chunk = std::max<int64_t>(default_chunk_reads(read_bytes), int64_t(h->sm_count) * 24 * 4);
     chunk = std::min<int64_t>(chunk, std::max<int64_t>((int64_t(2) << 30) / read_bytes, 1));
-    if (const char* e = getenv("FCTC_BEAM_CHUNK_READS")) chunk = atoll(e) > 0 ? atoll(e) : chunk;  // tuning knob
+    static const int chunk_knob = fctc::env_knob("FCTC_BEAM_CHUNK_READS");  // tuning knob
+    if (chunk_knob > 0) chunk = chunk_knob;
     chunk = std::min<int64_t>(chunk, n_reads);
     int64_t nodes_per_slot = 0;
     int n_slots = 0;

@@ -29,6 +29,7 @@
 #include "device_utils.cuh"
 #include "kernels.h"
 
+#include <atomic>
 #include <cstdio>
 #include <cstdlib>
 
@@ -573,7 +574,8 @@ int64_t beam_scratch_bytes(int sm_count, int64_t N, int64_t T, int C, int beam_s
     // The kernel is latency-bound (sequential per read), so throughput follows the number of resident
     // warps: 24 per SM is what registers and shared memory allow.  One trie pool per resident warp.
     int per_sm = 24;
-    if (const char* e = getenv("FCTC_BEAM_WARPS_PER_SM")) per_sm = atoi(e) > 0 ? atoi(e) : per_sm;  // tuning knob
+    static const int per_sm_knob = env_knob("FCTC_BEAM_WARPS_PER_SM");  // tuning knob
+    if (per_sm_knob > 0) per_sm = per_sm_knob;
     if (beam_small_eligible(beam_size, C, T)) per_sm = beam_small_warps_per_sm();  // narrow beams: lighter warps
     const int wpc = beam_warps_per_cta(beam_size, C, T);
     long long slots = (long long)sm_count * per_sm;
@@ -617,6 +619,8 @@ cudaError_t launch_beam(const BeamParams& p, int sm_count, cudaStream_t stream) 
     if (e != cudaSuccess) return e;
     e = cudaMemsetAsync(p.ticket, 0, sizeof(unsigned long long), stream);
     if (e != cudaSuccess) return e;
+    e = cudaMemsetAsync(p.cursor, 0, sizeof(unsigned long long), stream);  // the pool fills from entry 0 on every call
+    if (e != cudaSuccess) return e;
     const int grid = p.n_slots / BM_WARPS;
     kernel<<<grid, BM_THREADS, smem, stream>>>(p, L);
     return cudaGetLastError();
@@ -659,7 +663,9 @@ static __device__ __align__(256) unsigned char g_beam_static_scratch[FCTC_BEAM_S
 
 namespace {
 constexpr int kMaxDevices = 64;
-void* g_static_scratch_ptr[kMaxDevices] = {};  // device address of the array, per device (0 = not looked up yet)
+// device address of the array, per device (null = not looked up yet).  Atomic: two handles on one device, each on
+// its own host thread, may both make the first call; they store the same address.
+std::atomic<void*> g_static_scratch_ptr[kMaxDevices] = {};
 }  // namespace
 
 extern "C" int fctc_beam_search_batch_device_static(fctc_handle* h, const float* post_dev, int64_t n_reads,
@@ -677,12 +683,14 @@ extern "C" int fctc_beam_search_batch_device_static(fctc_handle* h, const float*
     if (dev < 0 || dev >= kMaxDevices) return fctc::handle_fail(h, FCTC_E_UNSUPPORTED, "device index above 63");
     cudaError_t e = cudaSetDevice(dev);
     if (e != cudaSuccess) return fctc::handle_fail(h, FCTC_E_CUDA, cudaGetErrorString(e));
-    if (!g_static_scratch_ptr[dev]) {  // first call on this device: resolve the symbol's device address
+    void* static_ptr = g_static_scratch_ptr[dev].load(std::memory_order_relaxed);
+    if (!static_ptr) {  // first call on this device: resolve the symbol's device address
         void* ptr = nullptr;
         e = cudaGetSymbolAddress(&ptr, g_beam_static_scratch);
         if (e != cudaSuccess || !ptr)
             return fctc::handle_fail(h, FCTC_E_CUDA, e != cudaSuccess ? cudaGetErrorString(e) : "cudaGetSymbolAddress returned NULL");
-        g_static_scratch_ptr[dev] = ptr;
+        g_static_scratch_ptr[dev].store(ptr, std::memory_order_relaxed);
+        static_ptr = ptr;
     }
 
     // Fit the launch into the fixed array: fewer resident warps (pool slots) if need be, never more bytes.
@@ -708,7 +716,7 @@ extern "C" int fctc_beam_search_batch_device_static(fctc_handle* h, const float*
     p.threshold = beam_cut_threshold; p.collapse = collapse_repeats; p.labels = labels_dev; p.path = path_dev;
     p.pool_cap = pool_capacity; p.offsets = offsets_dev; p.lens = lens_dev; p.status = status_dev;
     p.cursor = pool_used_dev;
-    p.scratch = g_static_scratch_ptr[dev];
+    p.scratch = static_ptr;
     p.scratch_bytes = FCTC_BEAM_STATIC_SCRATCH_BYTES;
     p.ticket = static_cast<unsigned long long*>(p.scratch);  // cleared by launch_beam on `stream`
     e = fctc::launch_beam(p, sm_count, static_cast<cudaStream_t>(stream));

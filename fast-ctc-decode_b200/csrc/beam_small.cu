@@ -363,9 +363,11 @@ __global__ void __launch_bounds__(BS_THREADS, BS_MINBLOCKS) beam_small_kernel(co
 }  // namespace
 
 bool beam_small_eligible(int beam_size, int C, int64_t T) {
-    if (const char* e = getenv("FCTC_BEAM_SMALL")) {  // tuning knob: 0 forces the wide kernel
-        if (atoi(e) == 0) return false;
-    }
+    static const bool forced_wide = [] {  // tuning knob: FCTC_BEAM_SMALL=0 forces the wide kernel (read once)
+        const char* e = getenv("FCTC_BEAM_SMALL");
+        return e && atoi(e) == 0;
+    }();
+    if (forced_wide) return false;
     return C >= 2 && C <= 5 && beam_size >= 1 && beam_size * C <= 32 && T < (1LL << 24);
 }
 
@@ -375,7 +377,8 @@ int beam_small_warps_per_cta() { return BS_WARPS; }
 
 int beam_small_warps_per_sm() {
     int per_sm = 32;
-    if (const char* e = getenv("FCTC_BEAM_SMALL_WARPS_PER_SM")) per_sm = atoi(e) > 0 ? atoi(e) : per_sm;  // tuning knob
+    static const int per_sm_knob = env_knob("FCTC_BEAM_SMALL_WARPS_PER_SM");  // tuning knob
+    if (per_sm_knob > 0) per_sm = per_sm_knob;
     return per_sm;
 }
 
@@ -387,6 +390,8 @@ cudaError_t launch_beam_small(const BeamParams& p, cudaStream_t stream) {
                                  : (p.C == 5 ? beam_small_kernel<false, 5, false> : beam_small_kernel<false, 0, false>);
     const int smem = BS_WARP_SMEM * BS_WARPS;
     cudaError_t e = cudaMemsetAsync(p.ticket, 0, sizeof(unsigned long long), stream);
+    if (e != cudaSuccess) return e;
+    e = cudaMemsetAsync(p.cursor, 0, sizeof(unsigned long long), stream);  // the pool fills from entry 0 on every call
     if (e != cudaSuccess) return e;
     const int grid = (p.n_slots + BS_WARPS - 1) / BS_WARPS;
     kernel<<<grid, BS_THREADS, smem, stream>>>(p);

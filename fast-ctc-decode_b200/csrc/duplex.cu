@@ -705,7 +705,8 @@ int64_t duplex_scratch_bytes(int sm_count, int64_t N, int T1, int T2, int C, int
     const long long cap = (long long)nodes_per_row * (T1 > 0 ? T1 : 1);
     const long long per_slot = (long long)dx_slot_bytes(cap, T2, C, W);
     int per_sm = 24;  // latency-bound, sequential per pair: throughput follows the resident warps
-    if (const char* e = getenv("FCTC_DUPLEX_WARPS_PER_SM")) per_sm = atoi(e) > 0 ? atoi(e) : per_sm;  // tuning knob
+    static const int per_sm_knob = env_knob("FCTC_DUPLEX_WARPS_PER_SM");  // tuning knob
+    if (per_sm_knob > 0) per_sm = per_sm_knob;
     long long slots = (long long)sm_count * per_sm;
     if (slots > N) slots = N;
     if (slots < 1) slots = 1;
@@ -731,6 +732,8 @@ cudaError_t launch_duplex(const DuplexParams& p, cudaStream_t stream) {
                         : cudaFuncSetAttribute(duplex_search_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
     e = cudaMemsetAsync(p.ticket, 0, sizeof(unsigned long long), stream);
+    if (e != cudaSuccess) return e;
+    e = cudaMemsetAsync(p.cursor, 0, sizeof(unsigned long long), stream);  // the pool fills from entry 0 on every call
     if (e != cudaSuccess) return e;
     if (crf) duplex_search_kernel<true><<<p.n_slots / DX_WARPS, DX_THREADS, smem, stream>>>(p, L);
     else duplex_search_kernel<false><<<p.n_slots / DX_WARPS, DX_THREADS, smem, stream>>>(p, L);

@@ -19,6 +19,10 @@ size_t handle_device_buffer_bytes(const fctc_handle* h, int index);   // current
 void* handle_pinned_buffer(fctc_handle* h, int index, size_t bytes);
 cudaStream_t handle_stream(fctc_handle* h);
 
+// Integer tuning knob from the environment (development aid), 0 when unset or not positive.  Each call site keeps
+// the value in a function-local static, so the environment is read once per process, not once per launch.
+int env_knob(const char* name);
+
 struct ViterbiParams {
     const float* post;  // [N, T, C] contiguous, device (binary16 values behind the same pointer when in_f16)
     int in_f16;         // 1: the posteriors are IEEE binary16; every value is widened exactly to f32 before use
@@ -42,6 +46,27 @@ struct ViterbiParams {
 // one; returns cudaSuccess or the launch error.  `which` (optional) receives 0 = streaming,
 // 1 = generic.
 cudaError_t launch_viterbi(const ViterbiParams& p, int sm_count, cudaStream_t stream, int* which);
+
+// Slot form -> packed pool (pack.cu): read n moves from [offsets[n] - offset_base, +lens[n]) of the slot arrays to
+// [out_offsets[n], +lens[n]) of the packed ones, out_offsets = exclusive scan of round_up(lens, 32) in read order,
+// *cursor = the total.
+struct PackParams {
+    const uint8_t* labels;
+    const void* quals;  // may be null
+    int qual_bytes;
+    const int32_t* path;
+    const int64_t* offsets;
+    int64_t offset_base;
+    const int32_t* lens;
+    int64_t N;
+    uint8_t* out_labels;
+    void* out_quals;
+    int32_t* out_path;
+    int64_t* out_offsets;
+    int64_t out_capacity;
+    unsigned long long* cursor;
+};
+cudaError_t launch_pack(const PackParams& p, int sm_count, cudaStream_t stream);
 
 struct BeamParams {
     const float* post;  // [N, T, C] (binary16 values behind the same pointer when in_f16)

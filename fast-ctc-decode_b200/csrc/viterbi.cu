@@ -630,7 +630,8 @@ static bool plan_stream(const ViterbiParams& p, WarpLayout* L) {
     // enough bytes in flight per warp to cover HBM latency at the variant's resident warps per SM
     int ns = int(((p.qstring ? 8 : 11) * 1024) / stage);
     if (p.in_f16) ns = p.qstring ? 6 : 10;  // half-size tiles: deeper rings (measured: 3 stages 1.43 ms, 10 stages 0.58 ms)
-    if (const char* e = getenv("FCTC_VIT_STAGES")) ns = atoi(e) > 0 ? atoi(e) : ns;  // tuning knob
+    static const int stages_knob = env_knob("FCTC_VIT_STAGES");  // tuning knob
+    if (stages_knob > 0) ns = stages_knob;
     if (ns > VW_MAX_STAGES) ns = VW_MAX_STAGES;
     if (ns < 2) ns = 2;
     L->nstage = ns;

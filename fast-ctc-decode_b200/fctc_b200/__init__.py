@@ -37,6 +37,10 @@ _SIGNATURES = {
                                                 _vp, _i64, _vp, _vp, _vp, _vp]),
     "fctc_viterbi_batch_f16": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _i32, _f32, _f32, _i32, _vp, _vp, _i32, _vp, _i64,
                                          _vp, _vp, _vp, _vp]),
+    "fctc_viterbi_batch_packed": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _i32, _f32, _f32, _i32, _vp, _vp, _i32, _vp, _i64,
+                                            _vp, _vp, _vp, _vp]),
+    "fctc_viterbi_batch_packed_f16": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _i32, _f32, _f32, _i32, _vp, _vp, _i32, _vp,
+                                                _i64, _vp, _vp, _vp, _vp]),
     "fctc_viterbi_search": (C.c_int, [_vp, _vp, _i64, _i32, _i64, _i64, _i32, _f32, _f32, _i32, _vp, _vp, _vp, _i64,
                                       _vp]),
     "fctc_beam_scratch_bytes": (_i64, [_vp, _i64, _i64, _i32, _i32, _i32]),
@@ -232,10 +236,12 @@ class Decoder:
 
     # ---- host-memory batch API ------------------------------------------------------------------
     def viterbi_batch(self, post, qstring=False, qscale=1.0, qbias=0.0, collapse_repeats=True, qual_bytes=1,
-                      out=None):
+                      out=None, packed=False):
         """post: C-contiguous float32 — or float16, decoded as the exactly widened float32 values —
         [N, T, C] (numpy; pinned memory gives full copy overlap).
-        Returns dict(labels, quals, path, offsets, lens, status, used)."""
+        packed=True: fctc_viterbi_batch_packed — results squeezed together on the device before the read-back
+        (offsets are then the running sum of round_up(len, 32), not n * round_up(T, 32)).
+        Returns dict(labels, quals, path, offsets, lens, status, used, d2h_bytes)."""
         f16 = getattr(post, "dtype", None) == np.float16
         post = np.ascontiguousarray(post) if f16 else _as_f32_3d(post)
         if post.ndim != 3:
@@ -257,12 +263,17 @@ class Decoder:
         status = o.get("status", None)
         status = np.empty(N, np.int32) if status is None else status
         used = _i64(0)
-        fn = self._L.fctc_viterbi_batch_f16 if f16 else self._L.fctc_viterbi_batch
+        if packed:
+            fn = self._L.fctc_viterbi_batch_packed_f16 if f16 else self._L.fctc_viterbi_batch_packed
+        else:
+            fn = self._L.fctc_viterbi_batch_f16 if f16 else self._L.fctc_viterbi_batch
         self._check(fn(self._h, post.ctypes.data, N, T, Cn, int(qstring), qscale, qbias, int(collapse_repeats),
                        labels.ctypes.data, _np_ptr(quals) if qstring else None, qual_bytes, path.ctypes.data,
                        labels.size, offsets.ctypes.data, lens.ctypes.data, status.ctypes.data, C.byref(used)))
+        # bytes the call moved device -> host: result entries (label + row + quality) and 16 B per read
+        d2h = used.value * (1 + 4 + (qual_bytes if qstring else 0)) + N * 16
         return dict(labels=labels, quals=quals if qstring else None, path=path, offsets=offsets, lens=lens,
-                    status=status, used=used.value)
+                    status=status, used=used.value, d2h_bytes=d2h)
 
     def beam_search_batch(self, post, beam_size=5, beam_cut_threshold=0.0, collapse_repeats=True, out=None):
         """post: C-contiguous float32 — or float16, decoded as the exactly widened float32 values — [N, T, C].

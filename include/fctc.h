@@ -16,6 +16,10 @@
  *     layout is fully deterministic and needs no atomics); beam search packs reads with one atomic
  *     add per read (rounded up to 32 entries), so there the *placement* of a read depends on
  *     scheduling while the *content* per read is deterministic.
+ *   - *pool_used_dev (device entry points with a packed pool): one 64-bit counter in device memory.  Every call
+ *     clears it on `stream` before its kernel runs and leaves the number of pool entries handed out, so the
+ *     caller need not initialise it; results of successive calls go to separate pools (or the caller copies them
+ *     out in between).
  *   - `path` entries are row indices into the read (int32 on the device, the reference's
  *     Vec<usize>): emission row for Viterbi, first-proposal row for beam search.
  *   - Return value: >= 0 is a per-call decode status for single-read calls (FCTC_OK or one of the
@@ -115,6 +119,24 @@ int fctc_viterbi_batch_f16(fctc_handle* h, const void* post_host_f16, int64_t n_
                            int32_t qstring, float qscale, float qbias, int32_t collapse_repeats, uint8_t* labels,
                            void* quals, int32_t qual_bytes, int32_t* path, int64_t pool_capacity, int64_t* offsets,
                            int32_t* lens, int32_t* status, int64_t* pool_used);
+
+/* fctc_viterbi_batch_packed / fctc_viterbi_batch_packed_f16: fctc_viterbi_batch(_f16) with the results packed
+ *   before they cross PCIe — no counterpart in the reference (src/search.rs:320-383 decodes one read in host
+ *   memory).  The slot form gives every read round_up(n_rows, 32) entries although it fills only its emitted
+ *   labels (a third to two thirds of the rows), and fctc_viterbi_batch copies whole slots back.  Here the used
+ *   prefixes are moved together on the device first: offsets[n] is the exclusive sum of round_up(lens[m], 32)
+ *   over m < n (read order, deterministic; entries between a read's end and the next start are 0), *pool_used
+ *   the total, and only that many entries of labels / quals / path are written.  pool_capacity may be anything
+ *   >= the total (n_reads * round_up(n_rows, 32) always suffices); FCTC_E_CAPACITY otherwise.  Same arguments
+ *   and per-read results as fctc_viterbi_batch; about 1.5x less device-to-host traffic. */
+int fctc_viterbi_batch_packed(fctc_handle* h, const float* post_host, int64_t n_reads, int64_t n_rows, int32_t n_labels,
+                              int32_t qstring, float qscale, float qbias, int32_t collapse_repeats, uint8_t* labels,
+                              void* quals, int32_t qual_bytes, int32_t* path, int64_t pool_capacity, int64_t* offsets,
+                              int32_t* lens, int32_t* status, int64_t* pool_used);
+int fctc_viterbi_batch_packed_f16(fctc_handle* h, const void* post_host_f16, int64_t n_reads, int64_t n_rows,
+                                  int32_t n_labels, int32_t qstring, float qscale, float qbias, int32_t collapse_repeats,
+                                  uint8_t* labels, void* quals, int32_t qual_bytes, int32_t* path, int64_t pool_capacity,
+                                  int64_t* offsets, int32_t* lens, int32_t* status, int64_t* pool_used);
 
 /* fctc_viterbi_search: one read, any strides (in elements) — the shape of the pyo3 entry point
  *   src/lib.rs:171-212.  labels/quals/path hold `capacity` entries (n_rows always suffices).
@@ -246,7 +268,9 @@ int fctc_beam_search_duplex(fctc_handle* h, const float* post1_host, int64_t n_r
  * argmax().unwrap()) and states outside [0, n_state) abort the reference; here the read gets
  * FCTC_REFERENCE_PANIC.  Greedy results are in slot form (as Viterbi), beam results in the packed
  * pool (as beam search; scratch from fctc_beam_scratch_bytes).  Host arrays of the single-read
- * calls must be C-contiguous.  crf_beam_search_duplex (src/duplex.rs:652-834) is not built yet.
+ * calls must be C-contiguous.  crf_beam_search_duplex (src/duplex.rs:652-834) is the last pair of declarations
+ * below: built on the duplex kernel; the reference holds no test vector for it, so its results are checked
+ * against this repository's CPU restatement only (parity unpinned by the reference).
  * ------------------------------------------------------------------------------------------ */
 int fctc_crf_greedy_batch_device(fctc_handle* h, const float* post_dev, const float* init_dev, int64_t n_reads,
                                  int64_t n_rows, int32_t n_state, int32_t n_labels, int32_t n_init, int32_t qstring,

@@ -240,3 +240,55 @@ def test_f16_posteriors_device_batch(dec, oracle):
                offsets=offsets.cpu().numpy(), lens=lens.cpu().numpy(), status=status.cpu().numpy())
     reads = list(range(0, N, 37))
     check_batch(oracle, half.float().cpu().numpy(), res, True, 1.0, 0.0, True, reads=reads)
+
+
+def check_packed_layout(res):
+    lens = res["lens"].astype(np.int64)
+    want = np.concatenate([[0], np.cumsum((lens + 31) & ~31)])
+    assert np.array_equal(res["offsets"], want[:-1]), "packed offsets are the running sum of round_up(len, 32)"
+    assert res["used"] == want[-1]
+    for off, ln in zip(res["offsets"], lens):  # the gap up to the next read's start is cleared
+        pad = ((ln + 31) & ~31) - ln
+        assert not res["labels"][off + ln:off + ln + pad].any() and not res["path"][off + ln:off + ln + pad].any()
+
+
+@pytest.mark.parametrize("shape", [(7, 100, 5), (4, 4099, 5), (9, 1025, 5), (6, 777, 3), (3, 1500, 12), (2, 1, 5),
+                                   (3, 2, 2), (2100, 4000, 5)], ids=lambda s: "x".join(map(str, s)))
+def test_packed_host_batch(dec, oracle, shape):
+    """fctc_viterbi_batch_packed: the same per-read results as the slot form, squeezed together on the device
+    before the read-back ((2100, 4000, 5) spans three pipeline chunks)."""
+    rng = np.random.default_rng(77 + sum(shape))
+    post = softmax_posteriors(rng, shape) if shape[0] % 2 else peaked_posteriors(rng, shape)
+    for qstring, qscale, qbias, collapse, qb in [(True, 0.7, 2.0, True, 1), (False, 1.0, 0.0, False, 1), (True, 30.0, 100.0, True, 4)]:
+        res = dec.viterbi_batch(post, qstring, qscale, qbias, collapse, qual_bytes=qb, packed=True)
+        check_packed_layout(res)
+        sample = None if shape[0] < 100 else list(range(0, shape[0], 37)) + [shape[0] - 1]
+        check_batch(oracle, post, res, qstring, qscale, qbias, collapse, reads=sample)
+        if shape[0] >= 100:  # every read against the slot form
+            ref = dec.viterbi_batch(post, qstring, qscale, qbias, collapse, qual_bytes=qb)
+            assert np.array_equal(ref["lens"], res["lens"]) and np.array_equal(ref["status"], res["status"])
+            for n in range(shape[0]):
+                a, b, ln = int(ref["offsets"][n]), int(res["offsets"][n]), int(ref["lens"][n])
+                assert np.array_equal(ref["labels"][a:a + ln], res["labels"][b:b + ln])
+                assert np.array_equal(ref["path"][a:a + ln], res["path"][b:b + ln])
+                if qstring:
+                    assert np.array_equal(ref["quals"][a:a + ln], res["quals"][b:b + ln])
+            assert res["d2h_bytes"] < ref["d2h_bytes"]
+
+
+def test_packed_f16_and_capacity(dec, oracle):
+    import fctc_b200
+    rng = np.random.default_rng(5)
+    half = softmax_posteriors(rng, (6, 1200, 5)).astype(np.float16)
+    res = dec.viterbi_batch(half, True, 1.0, 0.0, True, packed=True)
+    check_packed_layout(res)
+    check_batch(oracle, half.astype(np.float32), res, True, 1.0, 0.0, True)
+    # a pool of exactly the used size is enough; one entry less is refused
+    used = res["used"]
+    out = dict(labels=np.empty(used, np.uint8), quals=np.empty(used, np.uint8), path=np.empty(used, np.int32))
+    again = dec.viterbi_batch(half, True, 1.0, 0.0, True, packed=True, out=out)
+    assert again["used"] == used and np.array_equal(again["labels"], res["labels"][:used])
+    out = dict(labels=np.empty(used - 32, np.uint8), quals=np.empty(used - 32, np.uint8), path=np.empty(used - 32, np.int32))
+    with pytest.raises(fctc_b200.FctcError) as err:
+        dec.viterbi_batch(half, True, 1.0, 0.0, True, packed=True, out=out)
+    assert err.value.code == fctc_b200.E_CAPACITY
