@@ -961,6 +961,24 @@ void fctc_host_logf(const float* x, float* y, int64_t n) {
     for (int64_t i = 0; i < n; ++i) y[i] = fctc::glibc_logf(x[i], invc, logc);
 }
 
+void fctc_host_expf(const float* x, float* y, int64_t n) {
+    static const uint64_t tab[32] = FCTC_EXP2F_TAB;
+    for (int64_t i = 0; i < n; ++i) y[i] = fctc::glibc_expf(x[i], tab);
+}
+
+void fctc_host_log1pf(const float* x, float* y, int64_t n) {
+    for (int64_t i = 0; i < n; ++i) y[i] = fctc::glibc_log1pf(x[i]);
+}
+
+void fctc_host_expf_nonpos(const float* x, float* y, int64_t n) {
+    static const uint64_t tab[32] = FCTC_EXP2F_TAB;
+    for (int64_t i = 0; i < n; ++i) y[i] = fctc::glibc_expf_nonpos(x[i], tab);
+}
+
+void fctc_host_log1pf_unit(const float* x, float* y, int64_t n) {
+    for (int64_t i = 0; i < n; ++i) y[i] = fctc::glibc_log1pf_unit(x[i]);
+}
+
 void fctc_host_log10f(const float* x, float* y, int64_t n) {
     static const double invc[16] = FCTC_LOGF_INVC;
     static const double logc[16] = FCTC_LOGF_LOGC;

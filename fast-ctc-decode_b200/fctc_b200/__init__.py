@@ -87,6 +87,10 @@ _SIGNATURES = {
     "fctc_host_phred": (C.c_uint32, [_f32, _f32, _f32]),
     "fctc_host_log10f": (None, [_vp, _vp, _i64]),
     "fctc_host_logf": (None, [_vp, _vp, _i64]),
+    "fctc_host_expf": (None, [_vp, _vp, _i64]),
+    "fctc_host_log1pf": (None, [_vp, _vp, _i64]),
+    "fctc_host_expf_nonpos": (None, [_vp, _vp, _i64]),
+    "fctc_host_log1pf_unit": (None, [_vp, _vp, _i64]),
 }
 
 

@@ -218,7 +218,10 @@ int fctc_beam_search(fctc_handle* h, const float* post_host, int64_t n_rows, int
  * gives, per network-1 row, the [lower, upper) network-2 rows to align against ([n_pairs,
  * n_rows_1, 2]; NULL = all of network 2, src/lib.rs:457-469).  Output: labels only (the reference
  * returns just the sequence).  exp_mode 0 = exact exp (the --no-default-features build, the parity
- * target), 1 = the reference's default build (its fastexp() evaluates to 0, so '+' is max).
+ * target; glibc's expf and log1pf are evaluated operation by operation, so results are bit-identical to
+ * a glibc host), 1 = the reference's default build (its fastexp() evaluates to 0, so '+' is max),
+ * 2 = exact exp through CUDA's own expf / log1pf (faster; last-bit differences from a glibc host can flip
+ * a near-tie).
  * beam_size <= 32 in this release.  max_window (device API): the widest upper-lower of the
  * envelope, 0 = n_rows_2; a row wider than that gets FCTC_NODE_POOL_OVERFLOW.  The device API
  * uses as many pair slots as scratch_bytes holds (at least 4 must fit).
@@ -365,6 +368,10 @@ int fctc_test_poison_shared_memory(fctc_handle* h, int32_t byte);
 uint32_t fctc_host_phred(float prob, float qscale, float qbias);
 void fctc_host_log10f(const float* x, float* y, int64_t n);
 void fctc_host_logf(const float* x, float* y, int64_t n);
+void fctc_host_expf(const float* x, float* y, int64_t n);   /* the LogSpace '+' pair of the duplex search */
+void fctc_host_log1pf(const float* x, float* y, int64_t n);
+void fctc_host_expf_nonpos(const float* x, float* y, int64_t n);  /* the branch-free forms the kernels run: x <= 0 or NaN */
+void fctc_host_log1pf_unit(const float* x, float* y, int64_t n);  /* ... 0 <= x <= 1 or NaN */
 
 #ifdef __cplusplus
 }

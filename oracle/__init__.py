@@ -41,6 +41,9 @@ def lib():
         L.oracle_log10f_n.argtypes = [vp, vp, i64]
         L.oracle_logf_n.restype = None
         L.oracle_logf_n.argtypes = [vp, vp, i64]
+        for name in ("oracle_expf_n", "oracle_log1pf_n"):
+            getattr(L, name).restype = None
+            getattr(L, name).argtypes = [vp, vp, i64]
         L.oracle_fastexp_as_shipped.restype = C.c_float
         L.oracle_fastexp_as_shipped.argtypes = [C.c_float]
         L.oracle_logadd.restype = C.c_float

@@ -738,6 +738,9 @@ uint32_t oracle_phred(float prob, float qscale, float qbias, int* valid) {
 void oracle_log10f_n(const float* x, float* y, int64_t n) { for (int64_t i = 0; i < n; ++i) y[i] = log10f(x[i]); }
 
 void oracle_logf_n(const float* x, float* y, int64_t n) { for (int64_t i = 0; i < n; ++i) y[i] = logf(x[i]); }
+// the system libm's expf / log1pf: what Rust's f32::exp / f32::ln_1p call in LogSpace '+' (src/duplex.rs:45-52)
+void oracle_expf_n(const float* x, float* y, int64_t n) { for (int64_t i = 0; i < n; ++i) y[i] = expf(x[i]); }
+void oracle_log1pf_n(const float* x, float* y, int64_t n) { for (int64_t i = 0; i < n; ++i) y[i] = log1pf(x[i]); }
 
 float oracle_fastexp_as_shipped(float a) { return fastexp_as_shipped(a); }
 float oracle_logadd(float a, float b, int exp_mode) { g_exp_mode = exp_mode; return (Lg{a} + Lg{b}).v; }

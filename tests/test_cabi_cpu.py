@@ -89,6 +89,44 @@ def test_logf_replica_matches_glibc(fctc, oracle):
     assert np.array_equal(mine.view(np.uint32)[~nan], ref.view(np.uint32)[~nan])
 
 
+def test_expf_log1pf_replicas_match_glibc(fctc, oracle):
+    """LogSpace '+' (src/duplex.rs:45-52) is big + ln_1p(exp(small - big)) through the system libm.  The duplex
+    kernels evaluate glibc's expf and log1pf themselves (phred.cuh); the host build of that code must agree with libm
+    bit for bit: strided sweeps over all bit patterns, dense over the domains the search uses (expf of (-104, 0],
+    log1pf of [0, 1]), plus special values; the branch-free forms the kernels actually run are swept over their own
+    domains.  tools/libm_replica_sweep.c is the exhaustive version (every bit pattern)."""
+    L, O = fctc.lib(), oracle.lib()
+
+    def check(mine_fn, ref_fn, bits):
+        x = bits.view(np.float32).copy()
+        mine, ref = np.empty_like(x), np.empty_like(x)
+        mine_fn(x.ctypes.data, mine.ctypes.data, x.size)
+        ref_fn(x.ctypes.data, ref.ctypes.data, x.size)
+        nan = np.isnan(ref)
+        assert np.array_equal(np.isnan(mine), nan)
+        bad = np.flatnonzero(mine.view(np.uint32)[~nan] != ref.view(np.uint32)[~nan])
+        assert bad.size == 0, f"{bad.size} differ, first x={x[~nan][bad[0]]!r}"
+        return x.size
+
+    special = np.array([0, 0x80000000, 0x7F800000, 0xFF800000, 0x7FC00000, 0xBF800000, 0x3F800000, 0x00800000, 0x007FFFFF,
+                        1, 0x4202422F, 0xC27C65D9, 0xC2CFF1B4, 0xC2CFF1B5, 0x42B17218, 0xBE95F61A, 0xBE95F61F, 0x3ED413D7,
+                        0x31000000, 0x24800000], dtype=np.uint32)
+    strided = np.arange(0, 2**32, 1999, dtype=np.uint64).astype(np.uint32)
+    neg = np.arange(0xB0000000, 0xC2D20000, 61, dtype=np.uint32)      # -4.7e-10 .. -105: the search's small - big
+    unit = np.arange(0x00000000, 0x3F800001, 53, dtype=np.uint32)     # [0, 1]: exp of a non-positive number
+    n = check(L.fctc_host_expf, O.oracle_expf_n, np.concatenate([strided, neg, special]))
+    n += check(L.fctc_host_log1pf, O.oracle_log1pf_n, np.concatenate([strided, unit, special]))
+    nonpos = np.concatenate([np.arange(0x80000000, 2**32, 499, dtype=np.uint64).astype(np.uint32), neg,
+                             np.array([0, 0x80000000, 0xFF800000, 0x7FC00000, 0xFFC00000, 0xC27C65D9, 0xC2CFF1B4, 0xC2CFF1B5],
+                                      dtype=np.uint32)])
+    n += check(L.fctc_host_expf_nonpos, O.oracle_expf_n, nonpos)
+    n += check(L.fctc_host_log1pf_unit, O.oracle_log1pf_n,
+               np.concatenate([unit, np.arange(0x3ED41000, 0x3ED42000, dtype=np.uint32),      # around 0.41422
+                               np.arange(0x3F7FF000, 0x3F800001, dtype=np.uint32),            # up to 1
+                               np.array([0, 0x7FC00000, 0x30FFFFFF, 0x31000000, 0x247FFFFF, 0x24800000], dtype=np.uint32)]))
+    assert n > 40_000_000
+
+
 def test_phred_host_build_matches_oracle(fctc, oracle):
     L = fctc.lib()
     rng = np.random.default_rng(3)
