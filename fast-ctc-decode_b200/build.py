@@ -11,8 +11,8 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libfctc_b200.so")
-SOURCES = ["api.cu", "viterbi.cu", "beam.cu", "beam_small.cu", "duplex.cu", "crf.cu", "fastq.cu", "pack.cu", "synth.cu"]
-HEADERS = ["kernels.h", "device_utils.cuh", "phred.cuh", os.path.join("..", "..", "include", "fctc.h")]
+SOURCES = ["api.cu", "viterbi.cu", "beam.cu", "beam_small.cu", "duplex.cu", "duplex_packed.cu", "crf.cu", "fastq.cu", "pack.cu", "synth.cu"]
+HEADERS = ["kernels.h", "device_utils.cuh", "phred.cuh", "duplex_common.cuh", os.path.join("..", "..", "include", "fctc.h")]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

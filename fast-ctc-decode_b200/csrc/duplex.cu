@@ -28,33 +28,13 @@
 #include <cuda_fp16.h>
 
 #include "device_utils.cuh"
+#include "duplex_common.cuh"
 #include "kernels.h"
 #include "phred.cuh"
 
 #include "../../include/fctc.h"
 
 namespace fctc {
-
-constexpr int DX_WARPS = 4;
-constexpr int DX_THREADS = DX_WARPS * 32;
-constexpr int DX_MAX_BEAM = 32;
-constexpr unsigned DXFULL = 0xffffffffu;
-constexpr int DXROOT = -1;
-
-__constant__ double c_dx_invc[16] = FCTC_LOGF_INVC;
-__constant__ double c_dx_logc[16] = FCTC_LOGF_LOGC;
-
-__device__ __forceinline__ float dx_neg_inf() { return __uint_as_float(0xff800000u); }
-
-// LogSpace '+' (src/duplex.rs:42-63): operands ordered so that a+b == b+a, -inf is an exact unit.
-__device__ __forceinline__ float lg_add(float a, float b, int mode) {
-    float big, small;
-    if (a <= b) { big = b; small = a; } else { big = a; small = b; }
-    if (small == dx_neg_inf()) return big;
-    if (mode != 0) return __fadd_rn(big, 0.0f);  // shipped fastexp() == 0: big + ln_1p(0)
-    return __fadd_rn(big, log1pf(expf(__fadd_rn(small, -big))));
-}
-__device__ __forceinline__ float lg_max(float a, float b) { return (a < b) ? b : a; }  // src/duplex.rs:33-39
 
 struct DuplexLayout {  // per-warp shared memory plan (bytes from the warp's base)
     int beam_stride;   // one beam buffer: 7 arrays of B words
@@ -63,101 +43,33 @@ struct DuplexLayout {  // per-warp shared memory plan (bytes from the warp's bas
     int cta_fixed;
 };
 
-struct DxBeam {
-    int* nd;
-    int* par;
-    int* tip;
-    int* dep;
-    float* lab;
-    float* gap;
-    float* p2;
-    int* st;  // crf transition state
-};
-__device__ __forceinline__ DxBeam dx_beam(unsigned char* base, int B) {
-    DxBeam v;
-    v.nd = reinterpret_cast<int*>(base);
-    v.par = v.nd + B;
-    v.tip = v.par + B;
-    v.dep = v.tip + B;
-    v.lab = reinterpret_cast<float*>(v.dep + B);
-    v.gap = v.lab + B;
-    v.p2 = v.gap + B;
-    v.st = reinterpret_cast<int*>(v.p2 + B);
-    return v;
-}
-
-// Scratch of one warp slot (all sections 256-byte aligned).
-struct DxSlot {
-    float* logp2;   // [T2][C]
-    float* rootv;   // [T2 + 1] running product of network-2 blank probabilities (src/duplex.rs:389-409)
-    int* parent;    // [cap]
-    int* child;     // [cap][C-1]
-    uint8_t* nlab;  // [cap]
-    int* voff;      // [cap]  first valid network-2 index of the node's vector
-    int* vend;      // [cap]  one past the last
-    float* vmx;     // [cap]  max_prob
-    int* vlo;       // [cap]  lower bound that max_prob currently covers (lets update_max skip rescans)
-    float* vlast;   // [cap]  label probability of the vector's last cell (older label cells are never read)
-    float* vdata;   // [cap][2][W]: gap, total
-};
-__host__ __device__ inline size_t dx_up256(size_t v) { return (v + 255) & ~size_t(255); }
-__host__ __device__ inline size_t dx_slot_bytes(long long cap, int T2, int C, int W) {
-    const int NL = C - 1 > 0 ? C - 1 : 1;
-    return dx_up256((size_t)T2 * C * 4) + dx_up256((size_t)(T2 + 1) * 4) + dx_up256((size_t)cap * 4) +
-           dx_up256((size_t)cap * NL * 4) + dx_up256((size_t)cap) + 5 * dx_up256((size_t)cap * 4) +
-           dx_up256((size_t)cap * 2 * (size_t)W * 4);
-}
-__device__ __forceinline__ DxSlot dx_slot(unsigned char* base, long long cap, int T2, int C, int W) {
-    const int NL = C - 1 > 0 ? C - 1 : 1;
-    DxSlot s;
-    unsigned char* p = base;
-    s.logp2 = reinterpret_cast<float*>(p); p += dx_up256((size_t)T2 * C * 4);
-    s.rootv = reinterpret_cast<float*>(p); p += dx_up256((size_t)(T2 + 1) * 4);
-    s.parent = reinterpret_cast<int*>(p);  p += dx_up256((size_t)cap * 4);
-    s.child = reinterpret_cast<int*>(p);   p += dx_up256((size_t)cap * NL * 4);
-    s.nlab = p;                            p += dx_up256((size_t)cap);
-    s.voff = reinterpret_cast<int*>(p);    p += dx_up256((size_t)cap * 4);
-    s.vend = reinterpret_cast<int*>(p);    p += dx_up256((size_t)cap * 4);
-    s.vmx = reinterpret_cast<float*>(p);   p += dx_up256((size_t)cap * 4);
-    s.vlo = reinterpret_cast<int*>(p);     p += dx_up256((size_t)cap * 4);
-    s.vlast = reinterpret_cast<float*>(p); p += dx_up256((size_t)cap * 4);
-    s.vdata = reinterpret_cast<float*>(p);
-    return s;
-}
-
-struct DxCell {
-    float label, gap, total;
-};
-
 // SecondaryProbs::get of the parent at index `at` (src/duplex.rs:167-179); only gap and
 // probability() are ever used by the recurrences.
 // `pslot` is at mod W, kept incrementally by the caller; `par_off` the parent's first valid index.
 __device__ __forceinline__ void dx_parent_get(const DxSlot& S, int par, const float* pv, int at, int pslot, int root_len,
-                                              int par_off, int par_end, int W, int mode, float& pgap, float& ptotal) {
+                                              int par_off, int par_end, int W, int mode, const uint64_t* XT, float& pgap,
+                                              float& ptotal) {
     pgap = dx_neg_inf();
     ptotal = dx_neg_inf();
     if (par == DXROOT) {
         const int idx = at + 1;  // root offset is -1
         if (idx >= 0 && idx < root_len) {
             pgap = S.rootv[idx];
-            ptotal = lg_add(dx_neg_inf(), pgap, mode);
+            ptotal = lg_add(dx_neg_inf(), pgap, mode, XT);
         }
     } else if (at >= par_off && at < par_end) {
         pgap = pv[pslot];
         ptotal = pv[W + pslot];
     }
 }
-__device__ __forceinline__ int dx_mod(int i, int W) {  // i mod W for i >= -1
-    return i < 0 ? i + W : i % W;
-}
 
 // One step of the forward recurrence (src/duplex.rs:234-246 and :373-385).
 __device__ __forceinline__ DxCell dx_step(const DxCell& last, float pgap, float ptotal, float p_blank, float p_label,
-                                          bool repeat, int mode) {
+                                          bool repeat, int mode, const uint64_t* XT) {
     DxCell c;
     c.gap = __fadd_rn(last.total, p_blank);
-    c.label = __fadd_rn(p_label, lg_add(last.label, repeat ? pgap : ptotal, mode));
-    c.total = lg_add(c.label, c.gap, mode);
+    c.label = __fadd_rn(p_label, lg_add(last.label, repeat ? pgap : ptotal, mode, XT));
+    c.total = lg_add(c.label, c.gap, mode, XT);
     return c;
 }
 
@@ -173,12 +85,14 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
     extern __shared__ __align__(16) unsigned char smem[];
     double* s_invc = reinterpret_cast<double*>(smem);
     double* s_logc = s_invc + 16;
+    uint64_t* XT = reinterpret_cast<uint64_t*>(s_logc + 16);  // glibc expf's 2^(i/32) table
     const int lane = threadIdx.x & 31;
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);  // tells the compiler it is warp-uniform
     if (threadIdx.x < 16) {
         s_invc[threadIdx.x] = c_dx_invc[threadIdx.x];
         s_logc[threadIdx.x] = c_dx_logc[threadIdx.x];
     }
+    if (threadIdx.x < 32) XT[threadIdx.x] = c_dx_exp2f[threadIdx.x];
     __syncthreads();
     const int slot_id = blockIdx.x * DX_WARPS + warp;
     if (slot_id >= p.n_slots) return;
@@ -398,8 +312,8 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
                         float pgap, ptot;
                         // a parent that is in the beam has (by now) cells up to i-1; others are as stored
                         dx_parent_get(S, my_par, pv, i - 1, sl_p, root_len, par_off, (my_par >= 0 && par_end == hi) ? i : par_end, W,
-                                      mode, pgap, ptot);
-                        const DxCell c = dx_step(last, pgap, ptot, lp2(i, my_state, 0), lp2(i, my_state, my_lab + 1), repeat, mode);
+                                      mode, XT, pgap, ptot);
+                        const DxCell c = dx_step(last, pgap, ptot, lp2(i, my_state, 0), lp2(i, my_state, my_lab + 1), repeat, mode, XT);
                         vd[sl_w] = c.gap; vd[W + sl_w] = c.total;
                         mx = lg_max(mx, c.total);
                         last = c;
@@ -430,7 +344,7 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
                 bool has_self = false;
                 float s_lab = NEG, s_gap = NEG;
                 if (p_blank > thr) {  // src/duplex.rs:529-534
-                    s_gap = __fadd_rn(lg_add(lab, gap, mode), p_blank);
+                    s_gap = __fadd_rn(lg_add(lab, gap, mode, XT), p_blank);
                     has_self = true;
                 }
                 if (collapse && tip >= 0) {  // :540-544
@@ -450,8 +364,8 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
                         if (!(pt < thr)) {
                             float c;
                             if (collapse && bv.tip[r] == tip) c = __fadd_rn(bv.gap[r], pt);           // :563-568
-                            else c = __fadd_rn(lg_add(bv.lab[r], bv.gap[r], mode), pt);               // :586-590
-                            s_lab = lg_add(s_lab, c, mode);                                            // :604
+                            else c = __fadd_rn(lg_add(bv.lab[r], bv.gap[r], mode, XT), pt);               // :586-590
+                            s_lab = lg_add(s_lab, c, mode, XT);                                            // :604
                             fold[r * NL + tip] = 1;
                         }
                     }
@@ -489,7 +403,7 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
                         }
                         if (take) {
                             cnode[s] = x;
-                            clab[s] = repeat ? __fadd_rn(gap, pl) : __fadd_rn(lg_add(lab, gap, mode), pl);
+                            clab[s] = repeat ? __fadd_rn(gap, pl) : __fadd_rn(lg_add(lab, gap, mode, XT), pl);
                             cgap[s] = NEG;
                             cp2[s] = bv.p2[b];
                             key = 1u;
@@ -537,9 +451,9 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
                     int sl = dx_mod(lo, W), sl_p = dx_mod(lo - 1, W);
                     for (int i = lo; i < hi; ++i) {
                         float pgap, ptot;
-                        dx_parent_get(S, pnode, pv, i - 1, sl_p, root_len, par_off, par_end, W, mode, pgap, ptot);
+                        dx_parent_get(S, pnode, pv, i - 1, sl_p, root_len, par_off, par_end, W, mode, XT, pgap, ptot);
                         if (++sl_p == W) sl_p = 0;
-                        const DxCell c = dx_step(last, pgap, ptot, lp2(i, tstate, 0), lp2(i, tstate, l + 1), repeat, mode);
+                        const DxCell c = dx_step(last, pgap, ptot, lp2(i, tstate, 0), lp2(i, tstate, l + 1), repeat, mode, XT);
                         vd[sl] = c.gap; vd[W + sl] = c.total;
                         mx = lg_max(mx, c.total);
                         last = c;
@@ -569,7 +483,7 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
                     if (ckey[s] == 0u) continue;
                     const int node = cnode[s];
                     if (node >= 0) cp2[s] = S.vmx[node];
-                    const float tot = __fadd_rn(__fadd_rn(lg_add(clab[s], cgap[s], mode), cp2[s]), 0.0f);
+                    const float tot = __fadd_rn(__fadd_rn(lg_add(clab[s], cgap[s], mode, XT), cp2[s]), 0.0f);
                     if (tot != tot) any_nan = true;
                     ckey[s] = (tot != tot) ? 1u : order_key(tot);
                     ++n_cand;
@@ -679,7 +593,7 @@ static bool plan_duplex(int B, int C, DuplexLayout* L) {
     L->off_root = int(o);    o = up(o + 4LL * NL, 16);
     L->off_newlist = int(o); o = up(o + 4LL * B * NL, 16);
     L->warp_bytes = int(up(o, 128));
-    L->cta_fixed = 256;
+    L->cta_fixed = 512;  // logf tables (2 x 16 doubles) + expf table (32 x 8 bytes)
     return L->cta_fixed + (long long)L->warp_bytes * DX_WARPS <= 200 * 1024;
 }
 
@@ -724,6 +638,7 @@ int64_t duplex_scratch_bytes(int sm_count, int64_t N, int T1, int T2, int C, int
 
 cudaError_t launch_duplex(const DuplexParams& p, cudaStream_t stream) {
     if (p.N <= 0) return cudaSuccess;
+    if (duplex_packed_eligible(p)) return launch_duplex_packed(p, stream);  // narrow beams: four pairs per warp
     DuplexLayout L;
     if (!plan_duplex(p.beam_size, p.C, &L)) return cudaErrorInvalidConfiguration;
     const int smem = L.cta_fixed + L.warp_bytes * DX_WARPS;
@@ -795,7 +710,7 @@ static int dx_batch_device_any(fctc_handle* h, const void* post1_dev, const void
         return fctc::handle_fail(h, FCTC_E_ARGUMENT, "null device pointer");
     if (reinterpret_cast<uintptr_t>(scratch_dev) & 255u)
         return fctc::handle_fail(h, FCTC_E_ARGUMENT, "scratch_dev must be 256-byte aligned");
-    if (exp_mode != 0 && exp_mode != 1) return fctc::handle_fail(h, FCTC_E_ARGUMENT, "exp_mode must be 0 (exact exp) or 1 (fastexp as shipped)");
+    if (exp_mode < 0 || exp_mode > 2) return fctc::handle_fail(h, FCTC_E_ARGUMENT, "exp_mode must be 0 (exact exp), 1 (fastexp as shipped) or 2 (CUDA expf/log1pf)");
     cudaError_t e = cudaSetDevice(fctc::handle_device(h));
     if (e != cudaSuccess) return fctc::handle_fail(h, FCTC_E_CUDA, cudaGetErrorString(e));
     fctc::DuplexParams p{};
@@ -917,7 +832,7 @@ extern "C" int fctc_beam_search_duplex_batch(fctc_handle* h, const float* post1_
     if (int rc = dx_check(h, n_pairs, n_rows_1, n_rows_2, n_labels, beam_size, beam_cut_threshold)) return rc;
     if (!post1_host || (!post2_host && n_rows_2 > 0) || !labels || !offsets || !lens || !status)
         return fctc::handle_fail(h, FCTC_E_ARGUMENT, "null host pointer");
-    if (exp_mode != 0 && exp_mode != 1) return fctc::handle_fail(h, FCTC_E_ARGUMENT, "exp_mode must be 0 (exact exp) or 1 (fastexp as shipped)");
+    if (exp_mode < 0 || exp_mode > 2) return fctc::handle_fail(h, FCTC_E_ARGUMENT, "exp_mode must be 0 (exact exp), 1 (fastexp as shipped) or 2 (CUDA expf/log1pf)");
     cudaError_t e = cudaSetDevice(fctc::handle_device(h));
     if (e != cudaSuccess) return fctc::handle_fail(h, FCTC_E_CUDA, cudaGetErrorString(e));
     if (pool_used) *pool_used = 0;
@@ -1023,7 +938,7 @@ extern "C" int fctc_crf_beam_search_duplex_batch_device(
         !pool_used_dev || !scratch_dev)
         return fctc::handle_fail(h, FCTC_E_ARGUMENT, "null device pointer");
     if (reinterpret_cast<uintptr_t>(scratch_dev) & 255u) return fctc::handle_fail(h, FCTC_E_ARGUMENT, "scratch_dev must be 256-byte aligned");
-    if (exp_mode != 0 && exp_mode != 1) return fctc::handle_fail(h, FCTC_E_ARGUMENT, "exp_mode must be 0 (exact exp) or 1 (fastexp as shipped)");
+    if (exp_mode < 0 || exp_mode > 2) return fctc::handle_fail(h, FCTC_E_ARGUMENT, "exp_mode must be 0 (exact exp), 1 (fastexp as shipped) or 2 (CUDA expf/log1pf)");
     cudaError_t e = cudaSetDevice(fctc::handle_device(h));
     if (e != cudaSuccess) return fctc::handle_fail(h, FCTC_E_CUDA, cudaGetErrorString(e));
     fctc::DuplexParams p{};

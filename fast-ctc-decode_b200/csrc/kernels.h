@@ -119,7 +119,7 @@ struct DuplexParams {
     int beam_size;
     float threshold;
     int collapse;
-    int exp_mode;  // 0 exact exp (parity target), 1 the reference's default build (fastexp == 0: '+' is max)
+    int exp_mode;  // 0 exact exp (parity target, glibc's expf/log1pf), 1 the reference's default build (fastexp == 0: '+' is max), 2 CUDA's expf/log1pf
     int W;         // ring size of a node's vector: max window + 1
     uint8_t* labels;
     int64_t pool_cap;
@@ -141,6 +141,9 @@ bool duplex_shape_supported(int beam_size, int C);
 int64_t duplex_scratch_bytes(int sm_count, int64_t N, int T1, int T2, int C, int beam_size, int W, int nodes_per_row,
                              int64_t budget_bytes, int64_t* nodes_per_slot, int* n_slots);
 cudaError_t launch_duplex(const DuplexParams& p, cudaStream_t stream);
+// duplex_packed.cu: four pairs per warp, beam_size <= 8, at most 8 labels, plain (non-crf) search; same scratch plan
+bool duplex_packed_eligible(const DuplexParams& p);
+cudaError_t launch_duplex_packed(const DuplexParams& p, cudaStream_t stream);
 
 // FASTQ record assembly from the Viterbi slot form (fastq.cu)
 struct FastqParams {

@@ -22,7 +22,7 @@ namespace py = pybind11;
 
 namespace {
 
-int g_exp_mode = 0;  // 0 = exact exp (--no-default-features semantics), 1 = default build (fastexp == 0)
+int g_exp_mode = 0;  // 0 = exact exp (--no-default-features semantics), 1 = default build (fastexp == 0), 2 = CUDA libm
 
 struct Handle {  // lives as long as its thread; not destroyed at exit (the CUDA runtime may be gone by then)
     fctc_handle* h = nullptr;
@@ -342,7 +342,10 @@ PYBIND11_MODULE(fast_ctc_decode, m) {
     m.def("set_exp_mode", [](const std::string& mode) {
         if (mode == "exact") g_exp_mode = 0;
         else if (mode == "fastexp") g_exp_mode = 1;
-        else throw py::value_error("mode must be 'exact' (the --no-default-features build) or 'fastexp' (the default build)");
-    }, "mode"_a, "LogSpace '+' of the duplex searches: 'exact' exp (default here) or the reference's default 'fastexp' build.");
+        else if (mode == "cuda") g_exp_mode = 2;
+        else throw py::value_error("mode must be 'exact' (the --no-default-features build), 'fastexp' (the default build) or "
+                                   "'cuda' (CUDA's expf/log1pf: faster, last-bit differences from a glibc host)");
+    }, "mode"_a, "LogSpace '+' of the duplex searches: 'exact' exp (default here, bit-identical to a glibc host), the "
+                 "reference's default 'fastexp' build, or 'cuda'.");
     m.attr("__version__") = "0.3.7";  // CARGO_PKG_VERSION, src/lib.rs:626
 }

@@ -140,6 +140,6 @@ def test_crf_duplex_matches_oracle(dec, oracle):
         assert st == ost == 0 and labels.tolist() == ol.tolist()
         st, labels = dec.crf_beam_search_duplex(p1, i1, p2, i2, env, beam, 0.0, exp_mode=0)
         ost, ol = oracle.crf_beam_search_duplex(p1, i1, p2, i2, env, beam, 0.0, exp_mode=0)
-        assert st == ost == 0 and abs(len(labels) - len(ol)) <= max(2, len(ol) // 10)
+        assert st == ost == 0 and labels.tolist() == ol.tolist()  # glibc's expf / log1pf on the device: identical
         seq = fcd.crf_beam_search_duplex(p1, i1, p2, i2, "NACGT"[:C], envelope=env, beam_size=beam)
         assert isinstance(seq, str) and abs(len(seq) - len(ol)) <= max(2, len(ol) // 10)

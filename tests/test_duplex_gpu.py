@@ -1,10 +1,12 @@
 """GPU parity tests for the 2-D (duplex) beam search through the C ABI vs the CPU oracle.
 
-exp_mode 1 (the reference's default build: fastexp() == 0, LogSpace '+' is max) involves no
-exp/log1p at all and the kernel maps inputs to log space with glibc's logf algorithm, so results
-must be identical.  exp_mode 0 (exact exp, the north-star parity target) goes through CUDA's
-expf/log1pf, which differ from glibc's in the last bits: sequences are compared with a tolerance
-on the fraction of identical pairs (SURVEY.md §7 hard part 7)."""
+The kernels map inputs to log space with glibc's logf algorithm and, in exp_mode 0 (exact exp, the
+north-star parity target), evaluate LogSpace '+' with glibc's expf and log1pf algorithms (phred.cuh,
+checked against libm over every bit pattern), so every score has the bits the oracle computes:
+results must be identical in exp_mode 0 as in exp_mode 1 (the reference's default build: fastexp()
+== 0, '+' is max).  Only exp_mode 2 (CUDA's own expf/log1pf, the opt-in fast mode) is compared with
+a tolerance on the fraction of identical pairs.  Beams up to 8 run duplex_packed.cu (four pairs per
+warp), wider ones duplex.cu; the cases below cover both."""
 import numpy as np
 import pytest
 
@@ -61,7 +63,8 @@ def test_max_plus_mode_is_exact(dec, oracle, case):
 
 
 @pytest.mark.parametrize("case", CASES, ids=lambda c: "N{}_T{}x{}_C{}_b{}_thr{}_c{}_w{}".format(*c))
-def test_exact_exp_mode_tolerance(dec, oracle, case):
+def test_exact_exp_mode_is_exact(dec, oracle, case):
+    """exp_mode 0, the --no-default-features build the north star names as the parity target: identical."""
     N, T1, T2, Cn, beam, thr, collapse, w = case
     rng = np.random.default_rng(2003 * (N + T1 + T2 + beam))
     p1, p2 = duplex_pairs(rng, N, T1, T2, Cn)
@@ -70,10 +73,61 @@ def test_exact_exp_mode_tolerance(dec, oracle, case):
     ol, olen, ost = oracle.beam_search_duplex_batch(p1, p2, None if env is None else env.astype(np.uint64), beam, thr,
                                                     collapse, exp_mode=0)
     assert res["status"].tolist() == ost.tolist()
+    assert seqs(res) == [ol[n, :olen[n]].tolist() for n in range(N)]
+
+
+def test_exact_exp_mode_soft_rows(dec, oracle):
+    """Softmax rows (every label plausible on every row) keep both operands of most log-adds within a few units of
+    each other, the regime where expf / log1pf rounding decides bits: still identical.  Beams 5 and 8 take the
+    four-pairs-per-warp kernel, 32 the one-pair-per-warp kernel; 19 pairs leave the last warp partly empty."""
+    rng = np.random.default_rng(31337)
+    N, T1, T2 = 19, 250, 260
+    p1, p2 = softmax_posteriors(rng, (N, T1, 5), scale=1.5), softmax_posteriors(rng, (N, T2, 5), scale=1.5)
+    env = band_envelope(N, T1, T2, 10)
+    for beam, thr in [(5, 0.0), (8, 0.05), (32, 0.0), (3, 0.0)]:
+        for mode in (0, 1):
+            res = dec.beam_search_duplex_batch(p1, p2, env, beam, thr, True, exp_mode=mode)
+            ol, olen, ost = oracle.beam_search_duplex_batch(p1, p2, env.astype(np.uint64), beam, thr, True, exp_mode=mode)
+            assert res["status"].tolist() == ost.tolist()
+            assert seqs(res) == [ol[n, :olen[n]].tolist() for n in range(N)]
+
+
+def test_packed_kernel_matches_one_pair_per_warp_kernel(dec, oracle):
+    """Ragged windows (every pair its own band width and drift) through the device entry point: the pairs of one warp
+    then run windows of different lengths side by side.  Checked against the oracle, both modes."""
+    rng = np.random.default_rng(99)
+    N, T1, T2 = 23, 180, 200
+    p1, p2 = duplex_pairs(rng, N, T1, T2, 5)
+    env = np.empty((N, T1, 2), np.int64)
+    for n in range(N):
+        w = 3 + (n * 5) % 17
+        c = (np.arange(T1) * T2) // T1 + (n % 3) - 1
+        hi = np.maximum.accumulate(np.clip(c + w + 1, 1, T2))
+        lo = np.clip(c - w, 0, None)
+        lo = np.minimum(lo, np.concatenate([[0], hi[:-1]]))
+        lo = np.minimum(lo, hi - 1)
+        env[n, :, 0], env[n, :, 1] = lo, hi
+    for mode in (0, 1):
+        res = dec.beam_search_duplex_batch(p1, p2, env, 5, 0.0, True, exp_mode=mode)
+        ol, olen, ost = oracle.beam_search_duplex_batch(p1, p2, env.astype(np.uint64), 5, 0.0, True, exp_mode=mode)
+        assert res["status"].tolist() == ost.tolist() and (ost == 0).all()
+        assert seqs(res) == [ol[n, :olen[n]].tolist() for n in range(N)]
+
+
+@pytest.mark.parametrize("case", CASES[:5], ids=lambda c: "N{}_T{}x{}_C{}_b{}_thr{}_c{}_w{}".format(*c))
+def test_cuda_exp_mode_tolerance(dec, oracle, case):
+    """exp_mode 2 (CUDA's expf / log1pf): last-bit differences may flip a near-tie in a few pairs."""
+    N, T1, T2, Cn, beam, thr, collapse, w = case
+    rng = np.random.default_rng(2003 * (N + T1 + T2 + beam))
+    p1, p2 = duplex_pairs(rng, N, T1, T2, Cn)
+    env = None if w is None else band_envelope(N, T1, T2, w)
+    res = dec.beam_search_duplex_batch(p1, p2, env, beam, thr, collapse, exp_mode=2)
+    ol, olen, ost = oracle.beam_search_duplex_batch(p1, p2, None if env is None else env.astype(np.uint64), beam, thr,
+                                                    collapse, exp_mode=0)
+    assert res["status"].tolist() == ost.tolist()
     got = seqs(res)
     want = [ol[n, :olen[n]].tolist() for n in range(N)]
     same = sum(g == w_ for g, w_ in zip(got, want))
-    # last-bit differences of expf/log1pf may flip a near-tie in a few pairs; lengths must stay close
     assert same >= int(np.ceil(0.75 * N)), f"only {same}/{N} pairs identical"
     for g, w_ in zip(got, want):
         assert abs(len(g) - len(w_)) <= max(2, len(w_) // 20)

@@ -177,7 +177,7 @@ def test_duplex_full_batch(dec, oracle):
     assert set(np.unique(st_np)) <= {0, 4} and int((st_np == 4).sum()) <= N // 100
     off_np, len_np, lab_np = offsets.cpu().numpy(), lens.cpu().numpy(), labels.cpu().numpy()
     assert (len_np[st_np == 0] > 0).all()
-    sample = np.linspace(0, N - 1, 64).astype(np.int64)
+    sample = np.linspace(0, N - 1, 256).astype(np.int64)
     idx = torch.from_numpy(sample).to(dev)
     ol, olen, ost = oracle.beam_search_duplex_batch(a[idx].cpu().numpy(), b[idx].cpu().numpy(),
                                                     np.ascontiguousarray(np.broadcast_to(env1, (len(sample), T, 2))).astype(np.uint64),
@@ -188,7 +188,6 @@ def test_duplex_full_batch(dec, oracle):
             same += 1
             continue
         o, ln = off_np[n], len_np[n]
-        assert abs(int(ln) - int(olen[j])) <= max(2, olen[j] // 50)
         same += int(ln == olen[j] and np.array_equal(lab_np[o:o + ln], ol[j, :ln]))
-    assert same >= len(sample) - 2   # exact-exp mode: tolerance parity (measured: 100 % identical)
+    assert same == len(sample)   # exact-exp mode evaluates glibc's expf / log1pf: identical, not merely close
     print(f"duplex full batch: {same}/{len(sample)} sampled pairs identical to the oracle")

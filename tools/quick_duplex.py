@@ -17,6 +17,7 @@ def main():
     band = int(sys.argv[3]) if len(sys.argv) > 3 else 32
     mode = int(sys.argv[4]) if len(sys.argv) > 4 else 0
     reps = int(sys.argv[5]) if len(sys.argv) > 5 else 2
+    npr = int(sys.argv[6]) if len(sys.argv) > 6 else 0   # nodes_per_row (0 = default)
     Cn, beam = 5, 5
     dev = torch.device("cuda:0")
     dec = fctc_b200.Decoder(0)
@@ -35,7 +36,7 @@ def main():
     status = torch.empty(N, dtype=torch.int32, device=dev)
     used = torch.zeros(1, dtype=torch.int64, device=dev)
     mw = 2 * band + 1
-    nbytes = dec.duplex_scratch_bytes(N, T, T, Cn, beam, mw, 0)
+    nbytes = dec.duplex_scratch_bytes(N, T, T, Cn, beam, mw, npr)
     scratch = torch.empty(nbytes, dtype=torch.uint8, device=dev)
     times = []
     for _ in range(reps):
@@ -44,7 +45,7 @@ def main():
         e0.record()
         dec.beam_search_duplex_batch_device(a.data_ptr(), b.data_ptr(), N, T, T, Cn, env.data_ptr(), mw, beam, 0.0, True, mode,
                                             labels.data_ptr(), cap, offsets.data_ptr(), lens.data_ptr(), status.data_ptr(),
-                                            used.data_ptr(), scratch.data_ptr(), nbytes, 0, st)
+                                            used.data_ptr(), scratch.data_ptr(), nbytes, npr, st)
         e1.record()
         torch.cuda.synchronize()
         times.append(e0.elapsed_time(e1))
