@@ -57,7 +57,13 @@ WORKLOADS = {
                    e2e_reads=32768, label="beam_search 65,536 reads x T=10,000 x C=5, beam_size=32, beam_cut_threshold=0.0"),
     "duplex": dict(reads=16_384, T=4000, T2=4000, C=5, kind="duplex", beam=5, thr=0.0, collapse=1, band=32, exp_mode=0,
                    cpu_sample=64, e2e_reads=7104,  # two full rounds of 3,552 resident pairs
-                   label="duplex 2D envelope beam search: 16,384 pairs x T1=T2=4000 x C=5, beam_size=5, band +-32, exact exp"),
+                   label="duplex 2D envelope beam search: 16,384 pairs x T1=T2=4000 x C=5, beam_size=5, band +-32, exact exp "
+                         "(exp_mode 0: glibc's expf/log1pf evaluated on the device, results bit-identical to the CPU reference)"),
+    # the same search with CUDA's own expf/log1pf (exp_mode 2, the opt-in fast mode; round 1's duplex figure was measured this way)
+    "duplex_cuda_exp": dict(reads=16_384, T=4000, T2=4000, C=5, kind="duplex", beam=5, thr=0.0, collapse=1, band=32, exp_mode=2,
+                            cpu_sample=64, e2e_reads=7104,
+                            label="duplex 2D envelope beam search: 16,384 pairs x T1=T2=4000 x C=5, beam_size=5, band +-32, "
+                                  "exp_mode 2 (CUDA expf/log1pf: last-bit differences from a glibc host)"),
 }
 
 
@@ -134,7 +140,7 @@ def cpu_pass(w, post_np, n_threads):
     elif w["kind"] == "duplex":
         p1, p2, env = post_np
         oracle.beam_search_duplex_batch(p1, p2, env.astype(np.uint64), w["beam"], w["thr"], bool(w["collapse"]),
-                                        w["exp_mode"], n_threads=n_threads)
+                                        min(w["exp_mode"], 1) if w["exp_mode"] != 2 else 0, n_threads=n_threads)
         return p1.shape[0] * p1.shape[1], time.perf_counter() - t0
     else:
         oracle.beam_search_batch(post_np, w["beam"], w["thr"], bool(w["collapse"]), n_threads=n_threads, keep=False)
@@ -553,7 +559,7 @@ def run_ours(args, names):
         dist.destroy_process_group()
 
 
-ALL = ["viterbi", "viterbi_f16", "beam5", "beam32", "duplex"]
+ALL = ["viterbi", "viterbi_f16", "beam5", "beam32", "duplex", "duplex_cuda_exp"]
 
 
 def main():

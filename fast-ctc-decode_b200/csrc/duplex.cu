@@ -612,13 +612,19 @@ static int dx_default_nodes_per_row(int C, int B) {
 }
 
 int64_t duplex_scratch_bytes(int sm_count, int64_t N, int T1, int T2, int C, int beam_size, int W, int nodes_per_row,
-                             int64_t budget_bytes, int64_t* nodes_per_slot, int* n_slots) {
+                             int64_t budget_bytes, int64_t* nodes_per_slot, int* n_slots, int crf, int64_t* n_rings) {
     if (nodes_per_row <= 0) nodes_per_row = dx_default_nodes_per_row(C, beam_size);
     const long long bound = (long long)(C - 1) * beam_size;
     if (nodes_per_row > bound) nodes_per_row = int(bound > 0 ? bound : 1);
     const long long cap = (long long)nodes_per_row * (T1 > 0 ? T1 : 1);
-    const long long per_slot = (long long)dx_slot_bytes(cap, T2, C, W);
-    int per_sm = 24;  // latency-bound, sequential per pair: throughput follows the resident warps
+    // narrow beams run duplex_packed.cu: its pairs share a small pool of rings, so a slot is ~10x smaller and the
+    // register file, not memory, sets the number of pairs in flight
+    const bool packed = duplex_packed_shape(beam_size, C, crf);
+    const long long rings = packed ? duplex_packed_rings(cap, nodes_per_row, bound > 0 ? bound : 1) : cap;
+    if (n_rings) *n_rings = rings;
+    const long long per_slot = packed ? (long long)duplex_packed_slot_bytes(cap, rings, T2, C, W)
+                                      : (long long)dx_slot_bytes(cap, T2, C, W);
+    int per_sm = packed ? duplex_packed_slots_per_sm() : 24;  // latency-bound, sequential per pair: throughput follows the resident warps
     static const int per_sm_knob = env_knob("FCTC_DUPLEX_WARPS_PER_SM");  // tuning knob
     if (per_sm_knob > 0) per_sm = per_sm_knob;
     long long slots = (long long)sm_count * per_sm;
@@ -630,6 +636,14 @@ int64_t duplex_scratch_bytes(int sm_count, int64_t N, int T1, int T2, int C, int
         fit = fit / DX_WARPS * DX_WARPS;
         if (fit < DX_WARPS) fit = DX_WARPS;
         if (slots > fit) slots = fit;
+    }
+    // every pair of a batch takes about the same time, so the pairs run in rounds of `slots`: even the rounds out
+    // (16,384 pairs over 9,472 slots would run 9,472 + 6,912; two rounds of 8,192 keep every warp as busy)
+    if (N > slots) {
+        const long long rounds = (N + slots - 1) / slots;
+        long long even = (N + rounds - 1) / rounds;
+        even = (even + DX_WARPS - 1) / DX_WARPS * DX_WARPS;
+        if (even < slots) slots = even;
     }
     if (nodes_per_slot) *nodes_per_slot = cap;
     if (n_slots) *n_slots = int(slots);
@@ -693,7 +707,7 @@ extern "C" int64_t fctc_duplex_scratch_bytes(const fctc_handle* h, int64_t n_pai
     const int W = int((max_window > 0 && max_window < n_rows_2 ? max_window : n_rows_2) + 1);
     // recommended: a pool per resident warp, capped at 96 GiB (smaller buffers run fewer pairs in flight)
     return fctc::duplex_scratch_bytes(fctc::handle_sm_count(h), n_pairs, int(n_rows_1), int(n_rows_2), n_labels, beam_size, W,
-                                      nodes_per_row, int64_t(96) << 30, nullptr, nullptr);
+                                      nodes_per_row, int64_t(96) << 30, nullptr, nullptr, 0, nullptr);
 }
 
 static int dx_batch_device_any(fctc_handle* h, const void* post1_dev, const void* post2_dev, int in_f16,
@@ -717,7 +731,8 @@ static int dx_batch_device_any(fctc_handle* h, const void* post1_dev, const void
     p.W = int((max_window > 0 && max_window < n_rows_2 ? max_window : n_rows_2) + 1);
     // use as many pair slots as the caller's scratch holds
     const int64_t need = fctc::duplex_scratch_bytes(fctc::handle_sm_count(h), n_pairs, int(n_rows_1), int(n_rows_2), n_labels,
-                                                    beam_size, p.W, nodes_per_row, scratch_bytes, &p.nodes_per_slot, &p.n_slots);
+                                                    beam_size, p.W, nodes_per_row, scratch_bytes, &p.nodes_per_slot, &p.n_slots, 0,
+                                                    &p.n_rings);
     if (need > scratch_bytes) {
         char msg[200];
         snprintf(msg, sizeof msg, "duplex scratch too small: %lld bytes given, %lld needed for %d pair slots",
@@ -789,7 +804,7 @@ int dx_host_chunk(fctc_handle* h, const float* post1, const float* post2, const 
     fctc::DuplexParams p{};
     p.W = W;
     const int64_t need = fctc::duplex_scratch_bytes(fctc::handle_sm_count(h), cnt, int(T1), int(T2), C, beam, W, nodes_per_row,
-                                                    dx_free_budget(h), &p.nodes_per_slot, &p.n_slots);
+                                                    dx_free_budget(h), &p.nodes_per_slot, &p.n_slots, 0, &p.n_rings);
     void* scratch = fctc::handle_device_buffer(h, 8, size_t(need));
     if (!scratch) return FCTC_E_NOMEM;
 #define DX_CUDA(call)                                                                          \
@@ -850,11 +865,12 @@ extern "C" int fctc_beam_search_duplex_batch(fctc_handle* h, const float* post1_
     }
     const int W = int(wmax + 1);
     const int64_t pair_bytes = (n_rows_1 + n_rows_2) * int64_t(n_labels) * 4;
-    // a chunk must fill the resident warps (24 per SM, one pair each) a few times over, or most of the GPU
-    // idles while the last pairs of the chunk finish; capped at 2 GiB of posteriors
-    int64_t chunk = std::max<int64_t>((int64_t(256) << 20) / std::max<int64_t>(pair_bytes, 1),
-                                      int64_t(fctc::handle_sm_count(h)) * 24 * 3);
-    chunk = std::min<int64_t>(chunk, std::max<int64_t>((int64_t(2) << 30) / std::max<int64_t>(pair_bytes, 1), 1));
+    // a chunk is a whole number of rounds of the pairs in flight (a partial round costs a full one), as many as 2 GiB
+    // of posteriors hold, at least one
+    const int64_t in_flight = int64_t(fctc::handle_sm_count(h)) *
+                              (fctc::duplex_packed_shape(beam_size, n_labels, 0) ? fctc::duplex_packed_slots_per_sm() : 24);
+    int64_t chunk = std::max<int64_t>((int64_t(2) << 30) / std::max<int64_t>(pair_bytes, 1), 1);
+    if (chunk > in_flight) chunk = chunk / in_flight * in_flight;
     chunk = std::max<int64_t>(1, std::min<int64_t>(chunk, n_pairs));
     int64_t used = 0;
     for (int64_t first = 0; first < n_pairs; first += chunk) {
@@ -944,7 +960,8 @@ extern "C" int fctc_crf_beam_search_duplex_batch_device(
     fctc::DuplexParams p{};
     p.W = int((max_window > 0 && max_window < n_rows_2 ? max_window : n_rows_2) + 1);
     const int64_t need = fctc::duplex_scratch_bytes(fctc::handle_sm_count(h), n_pairs, int(n_rows_1), int(n_rows_2), n_labels,
-                                                    beam_size, p.W, nodes_per_row, scratch_bytes, &p.nodes_per_slot, &p.n_slots);
+                                                    beam_size, p.W, nodes_per_row, scratch_bytes, &p.nodes_per_slot, &p.n_slots, 1,
+                                                    &p.n_rings);
     if (need > scratch_bytes) return fctc::handle_fail(h, FCTC_E_CAPACITY, "duplex scratch too small (see fctc_duplex_scratch_bytes)");
     p.post1 = static_cast<const float*>(post1_dev); p.post2 = static_cast<const float*>(post2_dev); p.in_f16 = 0;
     p.env = reinterpret_cast<const long long*>(envelope_dev);
@@ -1016,7 +1033,7 @@ extern "C" int fctc_crf_beam_search_duplex(fctc_handle* h, const float* post1_ho
         int64_t nps = 0;
         int nsl = 0;
         const int64_t need = fctc::duplex_scratch_bytes(fctc::handle_sm_count(h), 1, int(n_rows_1), int(n_rows_2), n_labels, beam_size,
-                                                        int(wmax + 1), tries[attempt], dx_free_budget(h), &nps, &nsl);
+                                                        int(wmax + 1), tries[attempt], dx_free_budget(h), &nps, &nsl, 1, nullptr);
         void* scratch = fctc::handle_device_buffer(h, 8, size_t(need));
         if (!scratch) return FCTC_E_NOMEM;
         DXC(cudaMemsetAsync(dcur, 0, 8, st));

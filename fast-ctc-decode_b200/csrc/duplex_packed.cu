@@ -1,7 +1,7 @@
 // duplex_packed.cu — the 2-D ("duplex") beam search for narrow beams: four pairs per warp.
 //
 // Same search as duplex.cu (duplex::beam_search, src/duplex.rs:443-650, with LogSpace :7-80, SecondaryProbs
-// :152-210, build_/extend_secondary_probs :212-249, :338-387, root_probs :389-409), same scratch layout, same
+// :152-210, build_/extend_secondary_probs :212-249, :338-387, root_probs :389-409), same
 // results bit for bit — another mapping of the work onto the warp.  With one pair per warp and one lane per beam
 // entry, the reference's default beam of 5 keeps 5 of 32 lanes busy in the beam steps and, in the step that
 // dominates — the forward recurrence that builds a SecondaryProbs vector over the envelope window for every
@@ -18,6 +18,14 @@
 //     label_i.  The even lane runs the label chain, the odd lane follows one cell behind with gap and total (one
 //     shuffle per cell hands label_i over) and stores the cell.  Sixteen nodes are in flight per pass and every
 //     lane executes one log-add per cell, in the reference's operation order, so values are unchanged.
+//   * a node's SecondaryProbs cells live in a pool of R rings indexed by node id mod R instead of one ring per node
+//     id.  A ring is only ever read for a node whose depth is at least (lowest depth in the beam) - 1: the beam's
+//     nodes, their parents (extension reads the parent's cells) and their children; beam depths never decrease, so
+//     a node below that depth is dead for good and its ring can be handed to a new node.  The hand-over checks
+//     exactly that (depth of the ring's previous owner); if it ever fails the pair is flagged
+//     FCTC_NODE_POOL_OVERFLOW, and a call with nodes_per_row at the hard bound (what the host entry points retry
+//     with) gets one ring per node, which cannot fail.  A pair then needs ~3 MB of scratch instead of ~27 MB
+//     (T = 4000, band 65), so the number of pairs in flight is set by registers, not by memory.
 // The crf variant and beams above 8 stay with duplex.cu.
 #include <cuda_fp16.h>
 
@@ -36,6 +44,51 @@ constexpr int DP_GROUP = 8;   // lanes per pair
 constexpr int DP_PAIRS = 4;   // pairs per warp
 constexpr int DP_SLOTS = 16;  // node-build jobs per pass (two lanes each)
 constexpr int DP_FIXED = 512; // logf tables (2 x 16 doubles) + expf table (32 x 8 bytes)
+#ifndef DP_MIN_CTAS
+#define DP_MIN_CTAS 16        // one-warp CTAs per SM the register allocation aims at (16 -> at most 128 registers)
+#endif
+
+// Scratch of one pair (all sections 256-byte aligned).
+struct DpSlot {
+    float* logp2;   // [T2][C]
+    float* rootv;   // [T2 + 1] running product of network-2 blank probabilities (src/duplex.rs:389-409)
+    float* roott;   // [T2 + 1] probability() of the same cells: zero (+) gap
+    int* parent;    // [cap]
+    int* child;     // [cap][C-1]
+    uint8_t* nlab;  // [cap]
+    int* voff;      // [cap]  first valid network-2 index of the node's vector
+    int* vend;      // [cap]  one past the last
+    float* vmx;     // [cap]  max_prob
+    int* vlo;       // [cap]  lower bound that max_prob currently covers (lets update_max skip rescans)
+    float* vlast;   // [cap]  label probability of the vector's last cell (older label cells are never read)
+    int* rdepth;    // [R]    depth of the node that owns the ring
+    float2* rings;  // [R][W] cells {gap, total}; node n uses ring n & ring_mask
+};
+__host__ __device__ inline size_t dp_slot_bytes(long long cap, long long R, int T2, int C, int W) {
+    const int NL = C - 1 > 0 ? C - 1 : 1;
+    return dx_up256((size_t)T2 * C * 4) + 2 * dx_up256((size_t)(T2 + 1) * 4) + dx_up256((size_t)cap * 4) +
+           dx_up256((size_t)cap * NL * 4) + dx_up256((size_t)cap) + 5 * dx_up256((size_t)cap * 4) +
+           dx_up256((size_t)R * 4) + dx_up256((size_t)R * (size_t)W * 8);
+}
+__device__ __forceinline__ DpSlot dp_slot(unsigned char* base, long long cap, long long R, int T2, int C, int W) {
+    const int NL = C - 1 > 0 ? C - 1 : 1;
+    DpSlot s;
+    unsigned char* p = base;
+    s.logp2 = reinterpret_cast<float*>(p); p += dx_up256((size_t)T2 * C * 4);
+    s.rootv = reinterpret_cast<float*>(p); p += dx_up256((size_t)(T2 + 1) * 4);
+    s.roott = reinterpret_cast<float*>(p); p += dx_up256((size_t)(T2 + 1) * 4);
+    s.parent = reinterpret_cast<int*>(p);  p += dx_up256((size_t)cap * 4);
+    s.child = reinterpret_cast<int*>(p);   p += dx_up256((size_t)cap * NL * 4);
+    s.nlab = p;                            p += dx_up256((size_t)cap);
+    s.voff = reinterpret_cast<int*>(p);    p += dx_up256((size_t)cap * 4);
+    s.vend = reinterpret_cast<int*>(p);    p += dx_up256((size_t)cap * 4);
+    s.vmx = reinterpret_cast<float*>(p);   p += dx_up256((size_t)cap * 4);
+    s.vlo = reinterpret_cast<int*>(p);     p += dx_up256((size_t)cap * 4);
+    s.vlast = reinterpret_cast<float*>(p); p += dx_up256((size_t)cap * 4);
+    s.rdepth = reinterpret_cast<int*>(p);  p += dx_up256((size_t)R * 4);
+    s.rings = reinterpret_cast<float2*>(p);
+    return s;
+}
 
 struct PackedLayout {
     int beam_stride;  // bytes of one beam buffer (8 arrays of B words)
@@ -45,7 +98,7 @@ struct PackedLayout {
     int warp_bytes;
 };
 
-__global__ void __launch_bounds__(32) duplex_packed_kernel(const DuplexParams p, const PackedLayout L) {
+__global__ void __launch_bounds__(32, DP_MIN_CTAS) duplex_packed_kernel(const DuplexParams p, const PackedLayout L) {
     extern __shared__ __align__(16) unsigned char smem[];
     double* s_invc = reinterpret_cast<double*>(smem);
     double* s_logc = s_invc + 16;
@@ -73,9 +126,11 @@ __global__ void __launch_bounds__(32) duplex_packed_kernel(const DuplexParams p,
     unsigned char* wbase = smem + DP_FIXED;
     unsigned char* gs = wbase + g * L.group_bytes;
     int* jobs = reinterpret_cast<int*>(wbase + L.off_jobs);
-    const size_t slot_bytes = dx_slot_bytes(cap, T2, C, W);
+    const long long R = p.n_rings;                                  // a power of two, or cap (one ring per node)
+    const int ring_mask = (R == cap) ? 0x7fffffff : int(R - 1);
+    const size_t slot_bytes = dp_slot_bytes(cap, R, T2, C, W);
     unsigned char* scratch0 = static_cast<unsigned char*>(p.scratch) + 256;
-    const DxSlot S = dx_slot(scratch0 + (size_t)(have_slot ? slot0 + g : slot0) * slot_bytes, cap, T2, C, W);
+    const DpSlot S = dp_slot(scratch0 + (size_t)(have_slot ? slot0 + g : slot0) * slot_bytes, cap, R, T2, C, W);
 
     unsigned char* fold = gs + L.off_fold;
     uint32_t* ckey = reinterpret_cast<uint32_t*>(gs + L.off_key);
@@ -189,11 +244,11 @@ __global__ void __launch_bounds__(32) duplex_packed_kernel(const DuplexParams p,
                 bool repeat = false;
                 float mx = NEG;
                 DxCell last{NEG, NEG, NEG};
-                float* vd = nullptr;
+                float2* vd = nullptr;
                 if (active) {
                     my_par = bv.par[bl];
                     my_lab = bv.tip[bl];
-                    vd = S.vdata + (size_t)node * 2 * W;
+                    vd = S.rings + (size_t)(node & ring_mask) * W;
                     int off = S.voff[node];
                     v_end = S.vend[node];
                     mx = S.vmx[node];
@@ -213,7 +268,7 @@ __global__ void __launch_bounds__(32) duplex_packed_kernel(const DuplexParams p,
                         if (!rescan) {
                             int sl = dx_mod(old_lo, W);
                             for (int i = old_lo; i < b0; ++i) {
-                                if (vd[W + sl] >= mx) rescan = true;
+                                if (vd[sl].y >= mx) rescan = true;
                                 if (++sl == W) sl = 0;
                             }
                         }
@@ -221,7 +276,7 @@ __global__ void __launch_bounds__(32) duplex_packed_kernel(const DuplexParams p,
                             mx = NEG;
                             int sl = dx_mod(b0, W);
                             for (int i = b0; i < e0; ++i) {
-                                mx = lg_max(mx, vd[W + sl]);
+                                mx = lg_max(mx, vd[sl].y);
                                 if (++sl == W) sl = 0;
                             }
                         }
@@ -230,7 +285,8 @@ __global__ void __launch_bounds__(32) duplex_packed_kernel(const DuplexParams p,
                     }
                     if (v_end > off) {
                         const int sl = dx_mod(v_end - 1, W);
-                        last.label = S.vlast[node]; last.gap = vd[sl]; last.total = vd[W + sl];
+                        const float2 cell = vd[sl];
+                        last.label = S.vlast[node]; last.gap = cell.x; last.total = cell.y;
                     }
                     // the parent's label decides the repeat case, independent of collapse (:511)
                     const int plab = (my_par >= 0) ? int(S.nlab[my_par]) : -1;
@@ -241,7 +297,7 @@ __global__ void __launch_bounds__(32) duplex_packed_kernel(const DuplexParams p,
                 }
                 __syncwarp();  // every node's new offset is visible before children read their parents
                 const int par_off = (active && my_par >= 0) ? S.voff[my_par] : 0;
-                const float* pv = (active && my_par >= 0) ? S.vdata + (size_t)my_par * 2 * W : nullptr;
+                const float2* pv = (active && my_par >= 0) ? S.rings + (size_t)(my_par & ring_mask) * W : nullptr;
                 int imin = hi;
                 if (ext) imin = __reduce_min_sync(gmask, active ? v_end : hi);
                 const int steps = __reduce_max_sync(DXFULL, ext ? hi - imin : 0);
@@ -255,13 +311,14 @@ __global__ void __launch_bounds__(32) duplex_packed_kernel(const DuplexParams p,
                         if (my_par == DXROOT) {
                             if (at + 1 < root_len) { pgap = S.rootv[at + 1]; ptot = S.roott[at + 1]; }
                         } else if (at >= par_off && at < ((par_end == hi) ? i : par_end)) {
-                            pgap = pv[sl_p]; ptot = pv[W + sl_p];
+                            const float2 cell = pv[sl_p];
+                            pgap = cell.x; ptot = cell.y;
                         }
                         DxCell c;
                         c.gap = __fadd_rn(last.total, S.logp2[(size_t)i * C]);
                         c.label = __fadd_rn(S.logp2[(size_t)i * C + my_lab + 1], lg_add(last.label, repeat ? pgap : ptot, mode, XT));
                         c.total = lg_add(c.label, c.gap, mode, XT);
-                        vd[sl_w] = c.gap; vd[W + sl_w] = c.total;
+                        vd[sl_w] = make_float2(c.gap, c.total);
                         mx = lg_max(mx, c.total);
                         last = c;
                     }
@@ -368,6 +425,19 @@ __global__ void __launch_bounds__(32) duplex_packed_kernel(const DuplexParams p,
                 status = FCTC_NODE_POOL_OVERFLOW;
                 ok = false;
             }
+            // ring hand-over: node id takes ring id & ring_mask; its previous owner (node id - R) must be dead, i.e.
+            // lie more than one level below the shallowest hypothesis of the beam
+            const int dmin = __reduce_min_sync(gmask, (ok && bl < nbeam) ? bv.dep[bl] : 0x7fffffff);
+            bool ring_busy = false;
+            if (ok && bl < nbeam)
+                for (int k = 0; k < n_new; ++k) {
+                    const int id = n_nodes + my_base + k;
+                    if (id > ring_mask && S.rdepth[id & ring_mask] >= dmin - 1) ring_busy = true;
+                }
+            if (__any_sync(gmask, ring_busy) && ok) {
+                status = FCTC_NODE_POOL_OVERFLOW;
+                ok = false;
+            }
             // the four pairs' new nodes in one job list
             const int gjobs = ok ? total_new : 0;
             const int c0 = __shfl_sync(DXFULL, gjobs, 0), c1 = __shfl_sync(DXFULL, gjobs, 8);
@@ -381,6 +451,7 @@ __global__ void __launch_bounds__(32) duplex_packed_kernel(const DuplexParams p,
                     if (ckey[s] != 0u && cnode[s] <= -2) {
                         jobs[gbase + my_base + k] = (g << 16) | (bl << 8) | l;
                         cnode[s] = n_nodes + my_base + k;
+                        S.rdepth[(n_nodes + my_base + k) & ring_mask] = bv.dep[bl] + 1;
                         ++k;
                     }
                 }
@@ -399,7 +470,7 @@ __global__ void __launch_bounds__(32) duplex_packed_kernel(const DuplexParams p,
                 const int* jinfo = reinterpret_cast<const int*>(js + L.off_info);
                 const int jlo = jinfo[0], jhi = jinfo[1], jroot_len = jinfo[2];
                 const DxBeam jbv = dx_beam(js + jinfo[3] * L.beam_stride, B);
-                const DxSlot JS = dx_slot(scratch0 + (size_t)(slot0 + jg) * slot_bytes, cap, T2, C, W);
+                const DpSlot JS = dp_slot(scratch0 + (size_t)(slot0 + jg) * slot_bytes, cap, R, T2, C, W);
                 int id = 0, pnode = DXROOT, par_end = 0, par_off = 0;
                 bool repeat = false;
                 if (valid) {
@@ -408,8 +479,8 @@ __global__ void __launch_bounds__(32) duplex_packed_kernel(const DuplexParams p,
                     repeat = collapse && jl == jbv.tip[jb];
                     if (pnode >= 0) { par_end = JS.vend[pnode]; par_off = JS.voff[pnode]; }
                 }
-                const float* pv = JS.vdata + (size_t)(pnode >= 0 ? pnode : 0) * 2 * W;
-                float* vd = JS.vdata + (size_t)id * 2 * W;
+                const float2* pv = JS.rings + (size_t)((pnode >= 0 ? pnode : 0) & ring_mask) * W;
+                float2* vd = JS.rings + (size_t)(id & ring_mask) * W;
                 const int len = valid ? jhi - jlo : 0;
                 const int n_iter = __reduce_max_sync(DXFULL, len) + 1;
                 // Iteration k: the label lane (role 0) computes cell jlo + k, the gap/total lane (role 1) cell
@@ -417,8 +488,11 @@ __global__ void __launch_bounds__(32) duplex_packed_kernel(const DuplexParams p,
                 // iteration k + 1 are issued before the log-add of iteration k.
                 const float* col = JS.logp2 + (size_t)(jlo - role) * C + (role == 0 ? jl + 1 : 0);  // p2[row][label | blank]
                 // parent term of cell jlo + k = parent cell jlo + k - 1 (SecondaryProbs::get, src/duplex.rs:167-179):
-                // present for k in [k_lo, k_hi), read at index pidx (linear for the root vector, a ring otherwise)
-                const float* psrc = (pnode == DXROOT) ? (repeat ? JS.rootv : JS.roott) : (repeat ? pv : pv + W);
+                // present for k in [k_lo, k_hi), read at index pidx (linear for the root vector; a ring of {gap,
+                // total} cells otherwise, gap for the repeat case)
+                const float* psrc = (pnode == DXROOT) ? (repeat ? JS.rootv : JS.roott)
+                                                      : reinterpret_cast<const float*>(pv) + (repeat ? 0 : 1);
+                const int pstride = (pnode == DXROOT) ? 1 : 2;
                 int k_lo = 0, k_hi = 0, pidx = 0, pwrap = 0x7fffffff;
                 if (valid && role == 0) {
                     if (pnode == DXROOT) { k_hi = jroot_len - jlo; pidx = jlo; }
@@ -433,30 +507,27 @@ __global__ void __launch_bounds__(32) duplex_packed_kernel(const DuplexParams p,
                 int coff = 0;
                 float qa_n = NEG, qb_n = 0.0f;
                 if (unsigned(0 - role) < ulen) qb_n = col[0];
-                if (unsigned(0 - k_lo) < k_span) qa_n = psrc[pidx];
+                if (unsigned(0 - k_lo) < k_span) qa_n = psrc[pidx * pstride];
                 for (int k = 0; k < n_iter; ++k) {
                     const float qa = qa_n, qb = qb_n;
                     const bool act = unsigned(k - role) < ulen;
+                    const bool act0 = act && role == 0, act1 = act && role == 1;
                     {  // next iteration's inputs
                         coff += C;
-                        if (++pidx == pwrap) pidx = 0;
+                        pidx = (pidx + 1 == pwrap) ? 0 : pidx + 1;
                         qb_n = (unsigned(k + 1 - role) < ulen) ? col[coff] : 0.0f;
-                        qa_n = (unsigned(k + 1 - k_lo) < k_span) ? psrc[pidx] : NEG;
+                        qa_n = (unsigned(k + 1 - k_lo) < k_span) ? psrc[pidx * pstride] : NEG;
                     }
                     const float gap = __fadd_rn(total_prev, qb);  // gap_i (role 1)
                     const float a = role == 0 ? label_prev : label_in;
                     const float b2 = role == 0 ? qa : gap;
                     const float r = lg_add(a, b2, mode, XT);
-                    if (act) {
-                        if (role == 0) {
-                            label_prev = __fadd_rn(qb, r);
-                        } else {
-                            vd[sl] = gap; vd[W + sl] = r;
-                            mx = lg_max(mx, r);
-                            total_prev = r;
-                            if (++sl == W) sl = 0;
-                        }
-                    }
+                    const float lab_new = __fadd_rn(qb, r);
+                    label_prev = act0 ? lab_new : label_prev;
+                    if (act1) vd[sl] = make_float2(gap, r);
+                    mx = act1 ? lg_max(mx, r) : mx;
+                    total_prev = act1 ? r : total_prev;
+                    sl = act1 ? ((sl + 1 == W) ? 0 : sl + 1) : sl;
                     label_in = __shfl_sync(DXFULL, label_prev, lane & ~1);
                 }
                 if (valid) {
@@ -603,13 +674,33 @@ bool plan_packed(int B, int C, PackedLayout* L) {
 
 }  // namespace
 
-bool duplex_packed_eligible(const DuplexParams& p) {
+bool duplex_packed_shape(int beam_size, int C, int crf) {
     static const bool forced_off = [] {  // tuning knob: FCTC_DUPLEX_PACKED=0 keeps every shape on duplex.cu (read once)
         const char* e = getenv("FCTC_DUPLEX_PACKED");
         return e && atoi(e) == 0;
     }();
     PackedLayout L;
-    return !forced_off && p.S == 0 && plan_packed(p.beam_size, p.C, &L);
+    return !forced_off && !crf && plan_packed(beam_size, C, &L);
+}
+
+// Rings of one pair: one per node when the caller asks for the hard bound of proposals per row (the retry of the
+// host entry points: cannot overflow), else 1024 — hundreds of times what is alive at once on nanopore-like data.
+int64_t duplex_packed_rings(int64_t cap, int nodes_per_row, int64_t bound) {
+    static const int knob = env_knob("FCTC_DUPLEX_RINGS");  // test / tuning knob: a smaller (power-of-two) pool
+    int64_t rings = 1024;
+    if (knob > 0 && (knob & (knob - 1)) == 0) rings = knob;
+    if (nodes_per_row >= bound || cap <= rings) return cap;
+    return rings;
+}
+
+int64_t duplex_packed_slot_bytes(int64_t cap, int64_t rings, int T2, int C, int W) {
+    return int64_t(dp_slot_bytes(cap, rings, T2, C, W));
+}
+
+int duplex_packed_slots_per_sm() { return 4 * DP_MIN_CTAS; }  // DP_MIN_CTAS warps of four pairs
+
+bool duplex_packed_eligible(const DuplexParams& p) {
+    return duplex_packed_shape(p.beam_size, p.C, p.S > 0);
 }
 
 cudaError_t launch_duplex_packed(const DuplexParams& p, cudaStream_t stream) {

@@ -129,6 +129,7 @@ struct DuplexParams {
     unsigned long long* cursor;
     void* scratch;
     int64_t nodes_per_slot;
+    int64_t n_rings;  // packed kernel: rings of SecondaryProbs cells per pair slot (a power of two, or nodes_per_slot)
     int n_slots;
     unsigned long long* ticket;
     // crf variant (duplex::crf_beam_search): S > 0 selects it; posts are [N, T, S, C]
@@ -138,11 +139,17 @@ struct DuplexParams {
     int n_init1, n_init2;
 };
 bool duplex_shape_supported(int beam_size, int C);
+// crf: the state-conditioned search (always duplex.cu); n_rings (optional) receives DuplexParams::n_rings
 int64_t duplex_scratch_bytes(int sm_count, int64_t N, int T1, int T2, int C, int beam_size, int W, int nodes_per_row,
-                             int64_t budget_bytes, int64_t* nodes_per_slot, int* n_slots);
+                             int64_t budget_bytes, int64_t* nodes_per_slot, int* n_slots, int crf = 0,
+                             int64_t* n_rings = nullptr);
 cudaError_t launch_duplex(const DuplexParams& p, cudaStream_t stream);
 // duplex_packed.cu: four pairs per warp, beam_size <= 8, at most 8 labels, plain (non-crf) search; same scratch plan
 bool duplex_packed_eligible(const DuplexParams& p);
+bool duplex_packed_shape(int beam_size, int C, int crf);
+int64_t duplex_packed_rings(int64_t cap, int nodes_per_row, int64_t bound);
+int64_t duplex_packed_slot_bytes(int64_t cap, int64_t rings, int T2, int C, int W);
+int duplex_packed_slots_per_sm();
 cudaError_t launch_duplex_packed(const DuplexParams& p, cudaStream_t stream);
 
 // FASTQ record assembly from the Viterbi slot form (fastq.cu)

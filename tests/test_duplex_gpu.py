@@ -114,6 +114,64 @@ def test_packed_kernel_matches_one_pair_per_warp_kernel(dec, oracle):
         assert seqs(res) == [ol[n, :olen[n]].tolist() for n in range(N)]
 
 
+RING_SCRIPT = r"""
+import json, sys, numpy as np
+import fctc_b200, oracle, torch
+from helpers import band_envelope, duplex_pairs
+rng = np.random.default_rng(4242)
+N, T = 9, 1500
+p1, p2 = duplex_pairs(rng, N, T, T, 5)
+env = band_envelope(N, T, T, 12)
+dec = fctc_b200.Decoder(0)
+out = {}
+for mode in (0, 1):
+    res = dec.beam_search_duplex_batch(p1, p2, env, 5, 0.0, True, exp_mode=mode)
+    ol, olen, ost = oracle.beam_search_duplex_batch(p1, p2, env.astype(np.uint64), 5, 0.0, True, exp_mode=mode)
+    got = [res["labels"][o:o + n].tolist() for o, n in zip(res["offsets"], res["lens"])]
+    out[str(mode)] = bool(res["status"].tolist() == ost.tolist() and got == [ol[n, :olen[n]].tolist() for n in range(N)])
+# the device entry point reports a refused hand-over instead of retrying
+dev = torch.device("cuda:0")
+d1, d2, de = torch.from_numpy(p1).to(dev), torch.from_numpy(p2).to(dev), torch.from_numpy(env).to(dev)
+cap = N * ((T + 31) // 32 * 32)
+labels = torch.empty(cap, dtype=torch.uint8, device=dev); offsets = torch.empty(N, dtype=torch.int64, device=dev)
+lens = torch.empty(N, dtype=torch.int32, device=dev); status = torch.empty(N, dtype=torch.int32, device=dev)
+used = torch.zeros(1, dtype=torch.int64, device=dev)
+nb = dec.duplex_scratch_bytes(N, T, T, 5, 5, 25, 0)
+scratch = torch.empty(nb, dtype=torch.uint8, device=dev)
+dec.beam_search_duplex_batch_device(d1.data_ptr(), d2.data_ptr(), N, T, T, 5, de.data_ptr(), 25, 5, 0.0, True, 1,
+                                    labels.data_ptr(), cap, offsets.data_ptr(), lens.data_ptr(), status.data_ptr(),
+                                    used.data_ptr(), scratch.data_ptr(), nb, 0, torch.cuda.current_stream().cuda_stream)
+torch.cuda.synchronize()
+out["device_status"] = status.cpu().tolist()
+print(json.dumps(out))
+"""
+
+
+def test_ring_pool_reuse_and_overflow_retry():
+    """The four-pairs-per-warp kernel keeps the nodes' SecondaryProbs cells in a pool of rings that dead nodes hand
+    on to new ones.  With the default pool (1024 rings) a 1500-row pair reuses every ring several times; with a pool
+    of 16 (FCTC_DUPLEX_RINGS, read once per process, hence the subprocess) the hand-over check refuses rings that
+    are still alive, the pair is flagged, and the host entry point decodes it again with one ring per node.  Both
+    ways the host result is the oracle's."""
+    import json
+    import os
+    import subprocess
+    import sys
+    here = os.path.dirname(os.path.abspath(__file__))
+    root = os.path.dirname(here)
+    for rings, expect_refusals in ((0, False), (16, True)):
+        envv = dict(os.environ)
+        envv["PYTHONPATH"] = os.pathsep.join([root, os.path.join(root, "fast-ctc-decode_b200"), here])
+        if rings:
+            envv["FCTC_DUPLEX_RINGS"] = str(rings)
+        r = subprocess.run([sys.executable, "-c", RING_SCRIPT], env=envv, capture_output=True, text=True, timeout=900)
+        assert r.returncode == 0, r.stderr[-2000:]
+        out = json.loads(r.stdout.strip().splitlines()[-1])
+        assert out["0"] and out["1"], f"rings={rings}: host results differ from the oracle"
+        assert set(out["device_status"]) <= {0, 4}
+        assert (4 in out["device_status"]) == expect_refusals, f"rings={rings}: device statuses {out['device_status']}"
+
+
 @pytest.mark.parametrize("case", CASES[:5], ids=lambda c: "N{}_T{}x{}_C{}_b{}_thr{}_c{}_w{}".format(*c))
 def test_cuda_exp_mode_tolerance(dec, oracle, case):
     """exp_mode 2 (CUDA's expf / log1pf): last-bit differences may flip a near-tie in a few pairs."""
