@@ -133,7 +133,7 @@ def test_beam_search_full_batches(dec, oracle, N, T, beam, thr, gib):
         assert (lab_np[o:o + ln] >= 1).all() and (lab_np[o:o + ln] < Cn).all()
         assert (np.diff(pth_np[o:o + ln]) > 0).all() and (ln == 0 or (0 <= pth_np[o] and pth_np[o + ln - 1] < T))
     # identical to the oracle on sampled reads
-    sample = np.linspace(0, N - 1, 192 if beam > 8 else 4096).astype(np.int64)
+    sample = np.linspace(0, N - 1, 1024 if beam > 8 else 4096).astype(np.int64)
     sub = post[torch.from_numpy(sample).to(dev)].cpu().numpy()
     ol, op, olen, ost, _ = oracle.beam_search_batch(sub, beam, thr, True)
     for j, n in enumerate(sample):
