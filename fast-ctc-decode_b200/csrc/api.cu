@@ -810,18 +810,35 @@ int beam_search_batch_any(fctc_handle* h, const void* post_host_any, int in_f16,
                                 collapse_repeats, 0, out))
         return rc;
     if (!out.overflow) {
-        // reads whose trie outgrew the default pool: decode again, one at a time, with the hard
-        // bound of (n_labels-1)*beam_size proposals per row
+        // reads whose trie outgrew the default pool: gathered into one array and decoded again in one pass (groups of
+        // at most 256 MiB of posteriors) with the hard bound of (n_labels-1)*beam_size proposals per row
         const int32_t bound = std::max<int32_t>(1, (n_labels - 1) * beam_size);
-        for (int64_t n = 0; n < n_reads && !out.overflow; ++n) {
-            if (status[n] != FCTC_NODE_POOL_OVERFLOW) continue;
-            HostOut one{labels, nullptr, 1, path, pool_capacity, offsets + n, lens + n, status + n};
-            one.used = out.used;
-            if (int rc = beam_host_pass(h, post_host + n * n_rows * n_labels * (in_f16 ? 2 : 4), in_f16, 1, n_rows, n_labels,
-                                        beam_size, beam_cut_threshold, collapse_repeats, bound, one))
+        const int64_t read_bytes = n_rows * int64_t(n_labels) * (in_f16 ? 2 : 4);
+        std::vector<int64_t> again;
+        for (int64_t n = 0; n < n_reads; ++n)
+            if (status[n] == FCTC_NODE_POOL_OVERFLOW) again.push_back(n);
+        const int64_t group = std::max<int64_t>(1, (int64_t(256) << 20) / std::max<int64_t>(read_bytes, 1));
+        std::vector<unsigned char> gathered;
+        std::vector<int64_t> off2;
+        std::vector<int32_t> len2, st2;
+        for (size_t g0 = 0; g0 < again.size() && !out.overflow; g0 += size_t(group)) {
+            const int64_t k = std::min<int64_t>(group, int64_t(again.size() - g0));
+            gathered.resize(size_t(std::max<int64_t>(k * read_bytes, 16)));
+            for (int64_t i = 0; i < k; ++i)
+                memcpy(gathered.data() + i * read_bytes, post_host + again[g0 + i] * read_bytes, size_t(read_bytes));
+            off2.assign(size_t(k), 0); len2.assign(size_t(k), 0); st2.assign(size_t(k), 0);
+            HostOut two{labels, nullptr, 1, path, pool_capacity, off2.data(), len2.data(), st2.data()};
+            two.used = out.used;
+            if (int rc = beam_host_pass(h, gathered.data(), in_f16, k, n_rows, n_labels, beam_size, beam_cut_threshold,
+                                        collapse_repeats, bound, two))
                 return rc;
-            out.used = one.used;
-            out.overflow = one.overflow;
+            out.used = two.used;
+            out.overflow = two.overflow;
+            if (!two.overflow)
+                for (int64_t i = 0; i < k; ++i) {
+                    const int64_t n = again[g0 + i];
+                    offsets[n] = off2[size_t(i)]; lens[n] = len2[size_t(i)]; status[n] = st2[size_t(i)];
+                }
         }
     }
     if (pool_used) *pool_used = out.used;

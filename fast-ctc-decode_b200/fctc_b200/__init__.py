@@ -55,6 +55,12 @@ _SIGNATURES = {
     "fctc_beam_search_batch_f16": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _i32, _f32, _i32, _vp, _vp, _i64, _vp, _vp,
                                              _vp, _vp]),
     "fctc_beam_search": (C.c_int, [_vp, _vp, _i64, _i32, _i64, _i64, _i32, _f32, _i32, _vp, _vp, _i64, _vp]),
+    "fctc_viterbi_batch_multi": (C.c_int, [_vp, _i32, _vp, _i64, _i64, _i32, _i32, _f32, _f32, _i32, _vp, _vp, _i32, _vp, _i64,
+                                           _vp, _vp, _vp, _vp]),
+    "fctc_beam_search_batch_multi": (C.c_int, [_vp, _i32, _vp, _i64, _i64, _i32, _i32, _f32, _i32, _vp, _vp, _i64, _vp, _vp,
+                                               _vp, _vp]),
+    "fctc_multi_last_error": (C.c_char_p, []),
+    "fctc_multi_release": (None, []),
     "fctc_duplex_scratch_bytes": (_i64, [_vp, _i64, _i64, _i64, _i32, _i32, _i32, _i32]),
     "fctc_beam_search_duplex_batch_device": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i64, _i32, _vp, _i32, _i32, _f32,
                                                        _i32, _i32, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _i64, _i32,
@@ -446,6 +452,45 @@ class Decoder:
                                                       path.ctypes.data, cap, C.byref(n)))
         k = n.value
         return status, labels[:k].copy(), path[:k].copy()
+
+
+def _multi_check(rc):
+    if rc < 0:
+        raise FctcError(rc, (lib().fctc_multi_last_error() or b"").decode())
+
+
+def viterbi_batch_multi(devices, post, qstring=False, qscale=1.0, qbias=0.0, collapse_repeats=True, qual_bytes=1):
+    """fctc_viterbi_batch_multi: reads [g*N/G, (g+1)*N/G) of post [N, T, C] on devices[g], one host thread each;
+    results in read order (slot form).  Returns dict(labels, quals, path, offsets, lens, status, used)."""
+    post = _as_f32_3d(post)
+    N, T, Cn = post.shape
+    cap = N * round_up32(T)
+    dev = np.ascontiguousarray(devices, dtype=np.int32)
+    labels, path = np.empty(cap, np.uint8), np.empty(cap, np.int32)
+    quals = np.empty(cap, np.uint8 if qual_bytes == 1 else np.uint32) if qstring else None
+    offsets, lens, status = np.empty(N, np.int64), np.empty(N, np.int32), np.empty(N, np.int32)
+    used = _i64(0)
+    _multi_check(lib().fctc_viterbi_batch_multi(dev.ctypes.data, dev.size, post.ctypes.data, N, T, Cn, int(qstring), qscale,
+                                                qbias, int(collapse_repeats), labels.ctypes.data, _np_ptr(quals), qual_bytes,
+                                                path.ctypes.data, cap, offsets.ctypes.data, lens.ctypes.data,
+                                                status.ctypes.data, C.byref(used)))
+    return dict(labels=labels, quals=quals, path=path, offsets=offsets, lens=lens, status=status, used=used.value)
+
+
+def beam_search_batch_multi(devices, post, beam_size=5, beam_cut_threshold=0.0, collapse_repeats=True):
+    """fctc_beam_search_batch_multi: as viterbi_batch_multi for the beam search (packed pool per device range)."""
+    post = _as_f32_3d(post)
+    N, T, Cn = post.shape
+    cap = N * max(round_up32(T), 32)
+    dev = np.ascontiguousarray(devices, dtype=np.int32)
+    labels, path = np.empty(cap, np.uint8), np.empty(cap, np.int32)
+    offsets, lens, status = np.empty(N, np.int64), np.empty(N, np.int32), np.empty(N, np.int32)
+    used = _i64(0)
+    _multi_check(lib().fctc_beam_search_batch_multi(dev.ctypes.data, dev.size, post.ctypes.data, N, T, Cn, beam_size,
+                                                    beam_cut_threshold, int(collapse_repeats), labels.ctypes.data,
+                                                    path.ctypes.data, cap, offsets.ctypes.data, lens.ctypes.data,
+                                                    status.ctypes.data, C.byref(used)))
+    return dict(labels=labels, path=path, offsets=offsets, lens=lens, status=status, used=used.value)
 
 
 def _as_f32_3d(a):

@@ -211,6 +211,30 @@ int fctc_beam_search(fctc_handle* h, const float* post_host, int64_t n_rows, int
                      uint8_t* labels, int64_t* path, int64_t capacity, int64_t* out_len);
 
 /* ------------------------------------------------------------------------------------------
+ * Several GPUs in one call — the batched form of the reference's threading affordance: its functions release
+ * the GIL (src/lib.rs:199, :353) so that callers decode reads on several threads; here the reads of ONE host array
+ * are cut into n_devices contiguous ranges [g*N/G, (g+1)*N/G), range g is decoded on devices[g] by its own host
+ * thread (the library keeps one handle per device ordinal for these calls, created on first use), and the
+ * results land in the caller's arrays in read order.  Reads are independent: no data moves between devices.
+ * A device may be listed more than once (its ranges then run one after the other).  Arguments and per-read
+ * results as fctc_viterbi_batch / fctc_beam_search_batch; pool_capacity must be n_reads * round_up(n_rows, 32).
+ * Viterbi results are in slot form (offsets[n] = n * round_up(n_rows, 32)); beam-search range g fills the pool
+ * from entry lo_g * round_up(n_rows, 32) on, *pool_used is the number of entries handed out over all ranges.
+ * Failures: < 0 with the text in fctc_multi_last_error() (per calling thread).  fctc_multi_release() destroys
+ * the cached handles (optional; call it when no multi call is running).
+ * ------------------------------------------------------------------------------------------ */
+int fctc_viterbi_batch_multi(const int32_t* devices, int32_t n_devices, const float* post_host, int64_t n_reads,
+                             int64_t n_rows, int32_t n_labels, int32_t qstring, float qscale, float qbias,
+                             int32_t collapse_repeats, uint8_t* labels, void* quals, int32_t qual_bytes, int32_t* path,
+                             int64_t pool_capacity, int64_t* offsets, int32_t* lens, int32_t* status, int64_t* pool_used);
+int fctc_beam_search_batch_multi(const int32_t* devices, int32_t n_devices, const float* post_host, int64_t n_reads,
+                                 int64_t n_rows, int32_t n_labels, int32_t beam_size, float beam_cut_threshold,
+                                 int32_t collapse_repeats, uint8_t* labels, int32_t* path, int64_t pool_capacity,
+                                 int64_t* offsets, int32_t* lens, int32_t* status, int64_t* pool_used);
+const char* fctc_multi_last_error(void);
+void fctc_multi_release(void);
+
+/* ------------------------------------------------------------------------------------------
  * 2-D ("duplex") beam search — replaces duplex::beam_search, src/duplex.rs:443-650, with LogSpace
  * (:7-80; fastexp src/fastexp.rs), ProbPair/SearchPoint/SecondaryProbs (:84-210), build_/
  * extend_secondary_probs (:212-249, :338-387) and root_probs (:389-409), as called from
