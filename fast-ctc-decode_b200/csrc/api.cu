@@ -117,6 +117,22 @@ int check_common(fctc_handle* h, int64_t n_reads, int64_t n_rows, int32_t n_labe
 
 int roundup32(int64_t v) { return int((v + 31) & ~int64_t(31)); }
 
+// The internal "in_f16" argument of the batch paths carries a whole FCTC_IN_* input kind: element type in the low
+// four bits (0 f32, 1 binary16, 2 bfloat16), softmax mode above (FCTC_IN_LOGITS_EXACT / FCTC_IN_LOGITS_FAST).
+template <class Params>
+void set_input(Params& p, int kind) {
+    p.in_f16 = (kind & 0xf) != 0;
+    p.in_bf16 = (kind & 0xf) == 2;
+    p.softmax = (kind >> 4) & 3;
+}
+
+int check_input_kind(fctc_handle* h, int kind) {
+    if (!h) return FCTC_E_ARGUMENT;
+    if ((kind & 0xf) > 2 || (kind >> 4) > 2 || kind < 0)
+        return fail(h, FCTC_E_ARGUMENT, "input_kind must be FCTC_IN_F32 / _F16 / _BF16, optionally or-ed with FCTC_IN_LOGITS_EXACT or _FAST");
+    return 0;
+}
+
 }  // namespace
 
 // All fctc_* definitions below take C linkage from their declarations in include/fctc.h.
@@ -227,7 +243,7 @@ int viterbi_batch_device_any(fctc_handle* h, const void* post_dev, int in_f16, i
                     (long long)pool_capacity, (long long)(n_reads * stride));
     FCTC_CUDA(h, cudaSetDevice(h->device));
     fctc::ViterbiParams p{};
-    p.post = static_cast<const float*>(post_dev); p.in_f16 = in_f16; p.N = n_reads; p.T = n_rows; p.C = n_labels;
+    p.post = static_cast<const float*>(post_dev); set_input(p, in_f16); p.N = n_reads; p.T = n_rows; p.C = n_labels;
     p.qstring = qstring; p.qscale = qscale; p.qbias = qbias; p.collapse = collapse_repeats;
     p.labels = labels_dev; p.quals = quals_dev; p.qual_bytes = qual_bytes; p.path = path_dev;
     p.slot_stride = stride; p.offset_base = 0; p.offsets = offsets_dev; p.lens = lens_dev; p.status = status_dev;
@@ -393,7 +409,7 @@ int viterbi_batch_any(fctc_handle* h, const void* post_host_any, int in_f16, int
                       uint8_t* labels, void* quals, int32_t qual_bytes, int32_t* path, int64_t pool_capacity,
                       int64_t* offsets, int32_t* lens, int32_t* status, int64_t* pool_used) {
     const unsigned char* post_host = static_cast<const unsigned char*>(post_host_any);
-    const int elem_bytes = in_f16 ? 2 : 4;
+    const int elem_bytes = (in_f16 & 0xf) ? 2 : 4;
     if (int rc = check_common(h, n_reads, n_rows, n_labels)) return rc;
     if (n_rows == 0) return fail(h, FCTC_E_ARGUMENT, "n_rows must be >= 1 (the reference asserts a non-empty matrix)");
     if (!post_host || !labels || !path || !offsets || !lens || !status)
@@ -433,7 +449,7 @@ int viterbi_batch_any(fctc_handle* h, const void* post_host_any, int in_f16, int
         FCTC_CUDA(h, cudaMemcpyAsync(s.post.p, post_host + first * read_bytes, size_t(cnt * read_bytes),
                                      cudaMemcpyHostToDevice, s.stream));
         fctc::ViterbiParams p{};
-        p.post = static_cast<const float*>(s.post.p); p.in_f16 = in_f16; p.N = cnt; p.T = n_rows; p.C = n_labels;
+        p.post = static_cast<const float*>(s.post.p); set_input(p, in_f16); p.N = cnt; p.T = n_rows; p.C = n_labels;
         p.qstring = qstring; p.qscale = qscale; p.qbias = qbias; p.collapse = collapse_repeats;
         p.labels = static_cast<uint8_t*>(s.labels.p); p.quals = s.quals.p; p.qual_bytes = qual_bytes;
         p.path = static_cast<int32_t*>(s.path.p); p.slot_stride = stride; p.offset_base = first * stride;
@@ -465,7 +481,7 @@ int viterbi_batch_packed_any(fctc_handle* h, const void* post_host, int in_f16, 
                              int32_t n_labels, int32_t qstring, float qscale, float qbias, int32_t collapse_repeats,
                              uint8_t* labels, void* quals, int32_t qual_bytes, int32_t* path, int64_t pool_capacity,
                              int64_t* offsets, int32_t* lens, int32_t* status, int64_t* pool_used) {
-    const int elem_bytes = in_f16 ? 2 : 4;
+    const int elem_bytes = (in_f16 & 0xf) ? 2 : 4;
     if (int rc = check_common(h, n_reads, n_rows, n_labels)) return rc;
     if (n_rows == 0) return fail(h, FCTC_E_ARGUMENT, "n_rows must be >= 1 (the reference asserts a non-empty matrix)");
     if (!post_host || !labels || !path || !offsets || !lens || !status)
@@ -492,7 +508,7 @@ int viterbi_batch_packed_any(fctc_handle* h, const void* post_host, int in_f16, 
     HostOut out{labels, qstring ? quals : nullptr, qual_bytes, path, pool_capacity, offsets, lens, status};
     auto launch = [&](Slot& s, int64_t cnt) -> int {
         fctc::ViterbiParams p{};
-        p.post = static_cast<const float*>(s.post.p); p.in_f16 = in_f16; p.N = cnt; p.T = n_rows; p.C = n_labels;
+        p.post = static_cast<const float*>(s.post.p); set_input(p, in_f16); p.N = cnt; p.T = n_rows; p.C = n_labels;
         p.qstring = qstring; p.qscale = qscale; p.qbias = qbias; p.collapse = collapse_repeats;
         p.labels = static_cast<uint8_t*>(s.slot_labels.p); p.quals = s.slot_quals.p; p.qual_bytes = qual_bytes;
         p.path = static_cast<int32_t*>(s.slot_path.p); p.slot_stride = stride; p.offset_base = 0;
@@ -589,6 +605,27 @@ int stage_single(fctc_handle* h, const float* post_host, int64_t n_rows, int32_t
 }
 
 }  // namespace
+
+int fctc_viterbi_batch_device_in(fctc_handle* h, const void* in_dev, int32_t input_kind, int64_t n_reads, int64_t n_rows,
+                                 int32_t n_labels, int32_t qstring, float qscale, float qbias, int32_t collapse_repeats,
+                                 uint8_t* labels_dev, void* quals_dev, int32_t qual_bytes, int32_t* path_dev,
+                                 int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev, int32_t* status_dev,
+                                 void* stream) {
+    if (int rc = check_input_kind(h, input_kind)) return rc;
+    return viterbi_batch_device_any(h, in_dev, input_kind, n_reads, n_rows, n_labels, qstring, qscale, qbias, collapse_repeats,
+                                    labels_dev, quals_dev, qual_bytes, path_dev, pool_capacity, offsets_dev, lens_dev,
+                                    status_dev, stream);
+}
+
+int fctc_viterbi_batch_in(fctc_handle* h, const void* in_host, int32_t input_kind, int64_t n_reads, int64_t n_rows,
+                          int32_t n_labels, int32_t qstring, float qscale, float qbias, int32_t collapse_repeats,
+                          uint8_t* labels, void* quals, int32_t qual_bytes, int32_t* path, int64_t pool_capacity,
+                          int64_t* offsets, int32_t* lens, int32_t* status, int64_t* pool_used) {
+    if (int rc = check_input_kind(h, input_kind)) return rc;
+    return viterbi_batch_packed_any(h, in_host, input_kind, n_reads, n_rows, n_labels, qstring, qscale, qbias,
+                                    collapse_repeats, labels, quals, qual_bytes, path, pool_capacity, offsets, lens, status,
+                                    pool_used);
+}
 
 int fctc_viterbi_search(fctc_handle* h, const float* post_host, int64_t n_rows, int32_t n_labels,
                         int64_t stride_row, int64_t stride_label, int32_t qstring, float qscale, float qbias,
@@ -709,7 +746,7 @@ int beam_search_batch_device_any(fctc_handle* h, const void* post_dev, int in_f1
     if (scratch_bytes < need)
         return fail(h, FCTC_E_CAPACITY, "beam scratch too small: %lld bytes given, %lld needed", (long long)scratch_bytes,
                     (long long)need);
-    p.post = static_cast<const float*>(post_dev); p.in_f16 = in_f16; p.N = n_reads; p.T = n_rows; p.C = n_labels;
+    p.post = static_cast<const float*>(post_dev); set_input(p, in_f16); p.N = n_reads; p.T = n_rows; p.C = n_labels;
     p.beam_size = beam_size;
     p.threshold = beam_cut_threshold; p.collapse = collapse_repeats; p.labels = labels_dev; p.path = path_dev;
     p.pool_cap = pool_capacity; p.offsets = offsets_dev; p.lens = lens_dev; p.status = status_dev;
@@ -746,7 +783,7 @@ namespace {
 
 int beam_host_pass(fctc_handle* h, const void* post_host, int in_f16, int64_t n_reads, int64_t n_rows, int32_t n_labels,
                    int32_t beam_size, float thr, int32_t collapse, int32_t nodes_per_row, HostOut& out) {
-    const int elem_bytes = in_f16 ? 2 : 4;
+    const int elem_bytes = (in_f16 & 0xf) ? 2 : 4;
     const int64_t slot_entries = std::max<int64_t>(roundup32(n_rows), 32);
     // The search keeps one read per resident warp busy for the read's whole length, so a chunk must hold
     // several reads per warp slot (a 64 MiB chunk would leave most of the GPU idle); capped at 2 GiB.
@@ -776,7 +813,7 @@ int beam_host_pass(fctc_handle* h, const void* post_host, int in_f16, int64_t n_
     auto launch = [&](Slot& s, int64_t cnt) -> int {
         fctc::BeamParams p{};
         fctc::beam_scratch_bytes(h->sm_count, cnt, n_rows, n_labels, beam_size, nodes_per_row, need, &p.nodes_per_slot, &p.n_slots);
-        p.post = static_cast<const float*>(s.post.p); p.in_f16 = in_f16; p.N = cnt; p.T = n_rows; p.C = n_labels;
+        p.post = static_cast<const float*>(s.post.p); set_input(p, in_f16); p.N = cnt; p.T = n_rows; p.C = n_labels;
         p.beam_size = beam_size; p.threshold = thr; p.collapse = collapse;
         p.labels = static_cast<uint8_t*>(s.labels.p); p.path = static_cast<int32_t*>(s.path.p);
         p.pool_cap = cnt * slot_entries; p.offsets = static_cast<int64_t*>(s.offsets.p);
@@ -813,7 +850,7 @@ int beam_search_batch_any(fctc_handle* h, const void* post_host_any, int in_f16,
         // reads whose trie outgrew the default pool: gathered into one array and decoded again in one pass (groups of
         // at most 256 MiB of posteriors) with the hard bound of (n_labels-1)*beam_size proposals per row
         const int32_t bound = std::max<int32_t>(1, (n_labels - 1) * beam_size);
-        const int64_t read_bytes = n_rows * int64_t(n_labels) * (in_f16 ? 2 : 4);
+        const int64_t read_bytes = n_rows * int64_t(n_labels) * ((in_f16 & 0xf) ? 2 : 4);
         std::vector<int64_t> again;
         for (int64_t n = 0; n < n_reads; ++n)
             if (status[n] == FCTC_NODE_POOL_OVERFLOW) again.push_back(n);
@@ -863,6 +900,27 @@ int fctc_beam_search_batch_f16(fctc_handle* h, const void* post_host_f16, int64_
                                uint8_t* labels, int32_t* path, int64_t pool_capacity, int64_t* offsets, int32_t* lens,
                                int32_t* status, int64_t* pool_used) {
     return beam_search_batch_any(h, post_host_f16, 1, n_reads, n_rows, n_labels, beam_size, beam_cut_threshold,
+                                 collapse_repeats, labels, path, pool_capacity, offsets, lens, status, pool_used);
+}
+
+int fctc_beam_search_batch_device_in(fctc_handle* h, const void* in_dev, int32_t input_kind, int64_t n_reads,
+                                     int64_t n_rows, int32_t n_labels, int32_t beam_size, float beam_cut_threshold,
+                                     int32_t collapse_repeats, uint8_t* labels_dev, int32_t* path_dev,
+                                     int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev, int32_t* status_dev,
+                                     unsigned long long* pool_used_dev, void* scratch_dev, int64_t scratch_bytes,
+                                     int32_t nodes_per_row, void* stream) {
+    if (int rc = check_input_kind(h, input_kind)) return rc;
+    return beam_search_batch_device_any(h, in_dev, input_kind, n_reads, n_rows, n_labels, beam_size, beam_cut_threshold,
+                                        collapse_repeats, labels_dev, path_dev, pool_capacity, offsets_dev, lens_dev,
+                                        status_dev, pool_used_dev, scratch_dev, scratch_bytes, nodes_per_row, stream);
+}
+
+int fctc_beam_search_batch_in(fctc_handle* h, const void* in_host, int32_t input_kind, int64_t n_reads, int64_t n_rows,
+                              int32_t n_labels, int32_t beam_size, float beam_cut_threshold, int32_t collapse_repeats,
+                              uint8_t* labels, int32_t* path, int64_t pool_capacity, int64_t* offsets, int32_t* lens,
+                              int32_t* status, int64_t* pool_used) {
+    if (int rc = check_input_kind(h, input_kind)) return rc;
+    return beam_search_batch_any(h, in_host, input_kind, n_reads, n_rows, n_labels, beam_size, beam_cut_threshold,
                                  collapse_repeats, labels, path, pool_capacity, offsets, lens, status, pool_used);
 }
 

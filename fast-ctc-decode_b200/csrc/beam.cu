@@ -27,6 +27,7 @@
 #include <cuda_fp16.h>
 
 #include "device_utils.cuh"
+#include "input.cuh"
 #include "kernels.h"
 
 #include <atomic>
@@ -87,9 +88,14 @@ __device__ __forceinline__ BeamView beam_view(unsigned char* base, int B) {
 // CT = compile-time label count (0 = read it from the parameters): with CT = 5, the nanopore
 // alphabet, every per-label loop unrolls and the slot arithmetic becomes constant.
 // HALF (plain search only): the posteriors are binary16, widened exactly to f32 as they are fetched.
+static __constant__ uint64_t c_beam_exp2f[32] = FCTC_EXP2F_TAB;
+
 template <bool CRF, int CT, bool HALF>
 __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParams p, const BeamLayout L) {
     extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ uint64_t s_xt[32];  // glibc expf's table, for the exact softmax of logits (input.cuh)
+    if (threadIdx.x < 32) s_xt[threadIdx.x] = c_beam_exp2f[threadIdx.x];
+    __syncthreads();
     const int lane = threadIdx.x & 31;
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);  // tells the compiler it is warp-uniform
     const int slot = blockIdx.x * BM_WARPS + warp;
@@ -132,8 +138,9 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
         if (ticket >= (unsigned long long)p.N) break;
         const long long n = (long long)ticket;
         const float* rd = p.post + n * T * C * S;
-        const __half* rdh = reinterpret_cast<const __half*>(p.post) + n * T * C;  // the same rows when HALF
-        auto fetch = [&](long long e) -> float { return HALF ? __half2float(__ldg(rdh + e)) : __ldg(rd + e); };
+        const uint16_t* rdh = reinterpret_cast<const uint16_t*>(p.post) + n * T * C;  // the same rows when HALF
+        const bool bf16 = p.in_bf16 != 0;
+        auto fetch = [&](long long e) -> float { return HALF ? widen16(__ldg(rdh + e), bf16) : __ldg(rd + e); };
 
         int cur = 0;
         BeamView bv = beam_view(ws, B);
@@ -191,6 +198,10 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
             }
             __syncwarp();
             const int rows_here = int((T - t0 < R) ? (T - t0) : R);
+            if (!CRF && p.softmax != 0) {  // logits: every staged row becomes its softmax (input.cuh), one row per lane
+                for (int r = lane; r < rows_here; r += 32) softmax_row(rows + r * C, C, p.softmax, s_xt);
+                __syncwarp();
+            }
 
             for (int rr = 0; rr < rows_here && status == FCTC_OK; ++rr) {
                 const long long t = t0 + rr;

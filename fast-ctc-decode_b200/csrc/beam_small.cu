@@ -22,6 +22,7 @@
 #include <cuda_fp16.h>
 
 #include "device_utils.cuh"
+#include "input.cuh"
 #include "kernels.h"
 
 #include <cstdlib>
@@ -44,9 +45,14 @@ constexpr int BS_WARP_SMEM = 2 * BS_ROWBUF * 4 + 16 + 128;  // row buffers, the 
 #define BS_MINBLOCKS 8
 #endif
 // HALF (plain search only): the posteriors are binary16, widened exactly to f32 as they are fetched.
+static __constant__ uint64_t c_beam_exp2f[32] = FCTC_EXP2F_TAB;
+
 template <bool CRF, int CT, bool HALF>
 __global__ void __launch_bounds__(BS_THREADS, BS_MINBLOCKS) beam_small_kernel(const BeamParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ uint64_t s_xt[32];  // glibc expf's table, for the exact softmax of logits (input.cuh)
+    if (threadIdx.x < 32) s_xt[threadIdx.x] = c_beam_exp2f[threadIdx.x];
+    __syncthreads();
     const int lane = threadIdx.x & 31;
     const int warp = __shfl_sync(FULL, threadIdx.x >> 5, 0);  // tells the compiler it is warp-uniform
     const int slot = blockIdx.x * BS_WARPS + warp;
@@ -80,8 +86,9 @@ __global__ void __launch_bounds__(BS_THREADS, BS_MINBLOCKS) beam_small_kernel(co
         if (ticket >= (unsigned long long)p.N) break;
         const long long n = (long long)ticket;
         const float* rd = p.post + n * T * C * S;
-        const __half* rdh = reinterpret_cast<const __half*>(p.post) + n * T * C;  // the same rows when HALF
-        auto fetch = [&](long long e) -> float { return HALF ? __half2float(__ldg(rdh + e)) : __ldg(rd + e); };
+        const uint16_t* rdh = reinterpret_cast<const uint16_t*>(p.post) + n * T * C;  // the same rows when HALF
+        const bool bf16 = p.in_bf16 != 0;
+        auto fetch = [&](long long e) -> float { return HALF ? widen16(__ldg(rdh + e), bf16) : __ldg(rd + e); };
 
         // the hypothesis of my lane group (src/search.rs:170-175: one root hypothesis, gap_prob 1)
         int nd = ROOT, par = -2, dep = 0, tip = -1, skp = ROOT, st = 0;
@@ -132,6 +139,10 @@ __global__ void __launch_bounds__(BS_THREADS, BS_MINBLOCKS) beam_small_kernel(co
             }
             __syncwarp();
             const int rows_here = int((T - t0 < R) ? (T - t0) : R);
+            if (!CRF && p.softmax != 0) {  // logits: every staged row becomes its softmax (input.cuh), one row per lane
+                for (int r = lane; r < rows_here; r += 32) softmax_row(rows + r * C, C, p.softmax, s_xt);
+                __syncwarp();
+            }
 
             for (int rr = 0; rr < rows_here; ++rr) {
                 const long long t = t0 + rr;

@@ -25,7 +25,9 @@ int env_knob(const char* name);
 
 struct ViterbiParams {
     const float* post;  // [N, T, C] contiguous, device (binary16 values behind the same pointer when in_f16)
-    int in_f16;         // 1: the posteriors are IEEE binary16; every value is widened exactly to f32 before use
+    int in_f16;         // 1: the values are 16 bits wide (IEEE binary16, or bfloat16 with in_bf16); widened exactly to f32 before use
+    int in_bf16;        // with in_f16: the 16-bit values are bfloat16
+    int softmax;        // 0: the input holds posteriors; 1 / 2: logits, softmax in the load stage (input.cuh: exact / fast)
     int64_t N, T;
     int C;
     int qstring;
@@ -70,7 +72,9 @@ cudaError_t launch_pack(const PackParams& p, int sm_count, cudaStream_t stream);
 
 struct BeamParams {
     const float* post;  // [N, T, C] (binary16 values behind the same pointer when in_f16)
-    int in_f16;         // 1: binary16 posteriors, widened exactly to f32 as they are fetched (plain search only)
+    int in_f16;         // 1: 16-bit values (binary16, or bfloat16 with in_bf16), widened exactly to f32 as they are fetched (plain search only)
+    int in_bf16;
+    int softmax;        // 0 posteriors; 1 / 2: logits, softmax applied to every staged row (input.cuh: exact / fast)
     int64_t N, T;
     int C;
     int beam_size;

@@ -24,11 +24,13 @@
 //     MUFU.LG2 fast path whose result is only trusted when it is provably on the same side of
 //     every rounding boundary as glibc's log10f, else the exact binary64 re-evaluation of glibc's
 //     algorithm (phred.cuh) decides.
+#include <cuda_bf16.h>
 #include <cuda_fp16.h>
 
 #include <cstdlib>
 
 #include "device_utils.cuh"
+#include "input.cuh"
 #include "kernels.h"
 #include "phred.cuh"
 
@@ -54,6 +56,7 @@ constexpr int VT_SMEM_LIMIT = 227 * 1024;
 
 __constant__ double c_logf_invc[16] = FCTC_LOGF_INVC;
 __constant__ double c_logf_logc[16] = FCTC_LOGF_LOGC;
+__constant__ uint64_t c_vit_exp2f[32] = FCTC_EXP2F_TAB;  // glibc expf's table, for the exact softmax of logits (input.cuh)
 
 // ---------------------------------------------------------------------------------------------
 // Quality character.  Fast path: q from MUFU.LG2; it differs from the reference's float
@@ -146,17 +149,21 @@ __device__ __forceinline__ P* keep_in_register(P* ptr) {  // stops the compiler 
 // ------------------------------------------------------------------------------------------
 // FAST5: five labels, RPL == 4 and every tile 16-byte aligned (the nanopore case), so that all the
 // tile geometry is a compile-time constant.
-// HALF (with FAST5 only): the posteriors are binary16, 10 bytes per row; a lane's four rows are five
-// 8-byte shared loads, widened to f32 in registers.  Everything after the load is the f32 code.
-template <typename QT, int RPL, bool COLLAPSE, bool QSTRING, bool FAST5, bool HALF>
+// HALF (with FAST5 only): the values are 16 bits wide (binary16, or bfloat16 when p.in_bf16), 10 bytes per row; a
+// lane's four rows are five 8-byte shared loads, widened to f32 in registers.  Everything after the load is the f32 code.
+// LOGITS (with FAST5 only): the rows hold logits; each is turned into its softmax (input.cuh, p.softmax = 1 exact /
+// 2 fast) right after the load, in registers, and the rest of the kernel sees posteriors.
+template <typename QT, int RPL, bool COLLAPSE, bool QSTRING, bool FAST5, bool HALF, bool LOGITS>
 __global__ void __launch_bounds__(VW_THREADS, QSTRING ? VW_MINBLOCKS_Q : VW_MINBLOCKS_NOQ) viterbi_stream_kernel(const ViterbiParams p, const WarpLayout L) {
     static_assert(!FAST5 || RPL == 4, "the five-label fast path is written for four rows per lane");
-    static_assert(!HALF || FAST5, "binary16 input is only staged by the five-label fast path");
+    static_assert(!HALF || FAST5, "16-bit input is only staged by the five-label fast path");
+    static_assert(!LOGITS || FAST5, "the fused softmax is only built into the five-label fast path");
     constexpr int EB = HALF ? 2 : 4;  // bytes per posterior
     constexpr int TILE = 32 * RPL;
     extern __shared__ __align__(128) unsigned char smem[];
     double* s_invc = reinterpret_cast<double*>(smem);
     double* s_logc = s_invc + 16;
+    uint64_t* s_xt = reinterpret_cast<uint64_t*>(s_logc + 16);
     const int lane = threadIdx.x & 31;
     const int warp = __shfl_sync(FULLMASK, threadIdx.x >> 5, 0);  // tells the compiler it is warp-uniform
     unsigned char* ws = smem + L.cta_fixed + (size_t)warp * L.warp_bytes;
@@ -215,6 +222,7 @@ __global__ void __launch_bounds__(VW_THREADS, QSTRING ? VW_MINBLOCKS_Q : VW_MINB
         s_invc[threadIdx.x] = c_logf_invc[threadIdx.x];
         s_logc[threadIdx.x] = c_logf_logc[threadIdx.x];
     }
+    if (LOGITS && threadIdx.x < 32) s_xt[threadIdx.x] = c_vit_exp2f[threadIdx.x];
     if (lane == 0) {
         for (int s = 0; s < nstage; ++s) mbar_init_a(bar0 + 8 * s, 1);
         mbar_init_fence();
@@ -248,15 +256,20 @@ __global__ void __launch_bounds__(VW_THREADS, QSTRING ? VW_MINBLOCKS_Q : VW_MINB
                     uint32_t hw[10];
 #pragma unroll
                     for (int v = 0; v < 5; ++v) lds_v2(r_stage + 40 * lane + 8 * v, hw[2 * v], hw[2 * v + 1]);
+                    const bool bf16 = p.in_bf16 != 0;
 #pragma unroll
                     for (int j = 0; j < 10; ++j) {
-                        const float2 w = __half22float2(*reinterpret_cast<const __half2*>(&hw[j]));
+                        const float2 w = widen16x2(hw[j], bf16);
                         f[2 * j] = w.x;
                         f[2 * j + 1] = w.y;
                     }
                 } else {
 #pragma unroll
                     for (int v = 0; v < 5; ++v) lds_f4(r_stage + 80 * lane + 16 * v, f + 4 * v);
+                }
+                if (LOGITS) {
+#pragma unroll
+                    for (int r = 0; r < RPL; ++r) softmax_row(f + 5 * (r & 3), 5, p.softmax, s_xt);
                 }
 #pragma unroll
                 for (int r = 0; r < RPL; ++r) argmax_row5(f + 5 * (r & 3), lab[r], pr[r]);
@@ -482,19 +495,43 @@ struct TileShared {  // double-buffered by tile parity so that one tile needs on
     RunCarry carry[2];
     double invc[16];
     double logc[16];
+    uint64_t xt[32];
     int flag;
 };
 
 __device__ __forceinline__ float widen(float v) { return v; }
 __device__ __forceinline__ float widen(__half v) { return __half2float(v); }
+__device__ __forceinline__ float widen(__nv_bfloat16 v) { return __bfloat162float(v); }
 
+// sm = 0: the row holds posteriors.  sm = 1 / 2: logits; the argmax runs over the row's softmax (input.cuh), formed
+// on the fly in three passes over the row (maximum, sum of exponentials, quotients) since the row is not kept.
 template <typename IN>
-__device__ __forceinline__ void argmax_global(const IN* row, int C, int& arg, float& best) {
-    best = widen(row[0]);
-    arg = 0;
+__device__ __forceinline__ void argmax_global(const IN* row, int C, int sm, const uint64_t* xt, int& arg, float& best) {
+    if (sm == 0) {
+        best = widen(row[0]);
+        arg = 0;
+        for (int c = 1; c < C; ++c) {
+            const float v = widen(row[c]);
+            if (v > best) { best = v; arg = c; }
+        }
+        return;
+    }
+    float m = widen(row[0]);
     for (int c = 1; c < C; ++c) {
         const float v = widen(row[c]);
-        if (v > best) { best = v; arg = c; }
+        if (v > m) m = v;
+    }
+    float S = 0.0f;
+    for (int c = 0; c < C; ++c) {
+        const float e = softmax_exp(__fadd_rn(widen(row[c]), -m), sm, xt);
+        S = (c == 0) ? e : __fadd_rn(S, e);
+    }
+    const float inv = __frcp_rn(S);
+    for (int c = 0; c < C; ++c) {
+        const float e = softmax_exp(__fadd_rn(widen(row[c]), -m), sm, xt);
+        const float v = (sm == 1) ? __fdiv_rn(e, S) : __fmul_rn(e, inv);
+        if (c == 0) { best = v; arg = 0; }
+        else if (v > best) { best = v; arg = c; }
     }
 }
 
@@ -511,6 +548,7 @@ __global__ void __launch_bounds__(VG_THREADS) viterbi_generic_kernel(const Viter
         S.invc[tid] = c_logf_invc[tid];
         S.logc[tid] = c_logf_logc[tid];
     }
+    if (tid < 32) S.xt[tid] = c_vit_exp2f[tid];
     __syncthreads();
     int buf = 0;
     for (long long n = blockIdx.x; n < p.N; n += gridDim.x) {
@@ -531,7 +569,7 @@ __global__ void __launch_bounds__(VG_THREADS) viterbi_generic_kernel(const Viter
                 const long long row = row0 + VG_RPT * tid + r;
                 int arg = 0;
                 float best = 0.0f;
-                if (row < T) argmax_global(rd + row * C, C, arg, best);
+                if (row < T) argmax_global(rd + row * C, C, p.softmax, S.xt, arg, best);
                 pr[r] = best;
                 lab4 |= uint32_t(arg) << (8 * r);
             }
@@ -640,13 +678,13 @@ static bool plan_stream(const ViterbiParams& p, WarpLayout* L) {
     L->off_queue = int(L->off_stage + ns * stage);
     L->off_open = L->off_queue + (TILE + 1) * 8;
     L->warp_bytes = (L->off_open + 16 + 127) & ~127;
-    L->cta_fixed = 256;
+    L->cta_fixed = 512;  // logf tables (2 x 16 doubles) + expf table (32 x 8 bytes)
     return L->cta_fixed + VW_WARPS * L->warp_bytes <= VT_SMEM_LIMIT;
 }
 
-template <typename QT, int RPL, bool COLLAPSE, bool QSTRING, bool FAST5, bool HALF>
+template <typename QT, int RPL, bool COLLAPSE, bool QSTRING, bool FAST5, bool HALF, bool LOGITS>
 static cudaError_t launch_stream(const ViterbiParams& p, const WarpLayout& L, int sm_count, cudaStream_t stream) {
-    auto kernel = viterbi_stream_kernel<QT, RPL, COLLAPSE, QSTRING, FAST5, HALF>;
+    auto kernel = viterbi_stream_kernel<QT, RPL, COLLAPSE, QSTRING, FAST5, HALF, LOGITS>;
     const int smem = L.cta_fixed + VW_WARPS * L.warp_bytes;
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
@@ -661,14 +699,14 @@ static cudaError_t launch_stream(const ViterbiParams& p, const WarpLayout& L, in
     return cudaGetLastError();
 }
 
-template <typename QT, int RPL, bool FAST5, bool HALF>
+template <typename QT, int RPL, bool FAST5, bool HALF, bool LOGITS = false>
 static cudaError_t launch_stream_flags(const ViterbiParams& p, const WarpLayout& L, int sm_count, cudaStream_t stream) {
     if (p.collapse) {
-        return p.qstring ? launch_stream<QT, RPL, true, true, FAST5, HALF>(p, L, sm_count, stream)
-                         : launch_stream<QT, RPL, true, false, FAST5, HALF>(p, L, sm_count, stream);
+        return p.qstring ? launch_stream<QT, RPL, true, true, FAST5, HALF, LOGITS>(p, L, sm_count, stream)
+                         : launch_stream<QT, RPL, true, false, FAST5, HALF, LOGITS>(p, L, sm_count, stream);
     }
-    return p.qstring ? launch_stream<QT, RPL, false, true, FAST5, HALF>(p, L, sm_count, stream)
-                     : launch_stream<QT, RPL, false, false, FAST5, HALF>(p, L, sm_count, stream);
+    return p.qstring ? launch_stream<QT, RPL, false, true, FAST5, HALF, LOGITS>(p, L, sm_count, stream)
+                     : launch_stream<QT, RPL, false, false, FAST5, HALF, LOGITS>(p, L, sm_count, stream);
 }
 
 template <typename QT>
@@ -676,19 +714,33 @@ static cudaError_t launch_viterbi_t(const ViterbiParams& p, int sm_count, cudaSt
     WarpLayout L;
     long long grid = (long long)sm_count * 8;
     if (grid > p.N) grid = p.N;
+    // Logits: the fast softmax keeps the order of the values, so without quality strings (no probability is used) the
+    // rows are decoded as they are; otherwise the five-label streaming kernel has the softmax built in and every other
+    // shape takes the generic kernel.
+    const bool logits = p.softmax == 1 || (p.softmax == 2 && p.qstring);
     if (p.in_f16) {
-        // binary16 rows are 10 bytes at five labels: reads (and so every 128-row tile) start 16-byte aligned when T % 8 == 0
+        // 16-bit rows are 10 bytes at five labels: reads (and so every 128-row tile) start 16-byte aligned when T % 8 == 0
         if (p.C == 5 && (p.T & 7) == 0 && plan_stream<4>(p, &L)) {
             if (which) *which = 0;
-            return launch_stream_flags<QT, 4, true, true>(p, L, sm_count, stream);
+            return logits ? launch_stream_flags<QT, 4, true, true, true>(p, L, sm_count, stream)
+                          : launch_stream_flags<QT, 4, true, true>(p, L, sm_count, stream);
         }
         if (which) *which = 1;
-        viterbi_generic_kernel<QT, __half><<<dim3((unsigned)grid), VG_THREADS, 0, stream>>>(p);
+        ViterbiParams q = p;
+        q.softmax = logits ? p.softmax : 0;
+        if (p.in_bf16) viterbi_generic_kernel<QT, __nv_bfloat16><<<dim3((unsigned)grid), VG_THREADS, 0, stream>>>(q);
+        else viterbi_generic_kernel<QT, __half><<<dim3((unsigned)grid), VG_THREADS, 0, stream>>>(q);
+        return cudaGetLastError();
+    }
+    const bool fast5 = p.C == 5 && ((p.T * 5) & 3) == 0;  // every read (hence every tile) starts 16-byte aligned
+    if (logits && !(fast5 && plan_stream<4>(p, &L))) {
+        if (which) *which = 1;
+        viterbi_generic_kernel<QT, float><<<dim3((unsigned)grid), VG_THREADS, 0, stream>>>(p);
         return cudaGetLastError();
     }
     if (p.C <= 16 && plan_stream<4>(p, &L)) {
         if (which) *which = 0;
-        const bool fast5 = p.C == 5 && ((p.T * 5) & 3) == 0;  // every read (hence every tile) starts 16-byte aligned
+        if (logits) return launch_stream_flags<QT, 4, true, false, true>(p, L, sm_count, stream);
         return fast5 ? launch_stream_flags<QT, 4, true, false>(p, L, sm_count, stream)
                      : launch_stream_flags<QT, 4, false, false>(p, L, sm_count, stream);
     }
@@ -697,7 +749,9 @@ static cudaError_t launch_viterbi_t(const ViterbiParams& p, int sm_count, cudaSt
         return launch_stream_flags<QT, 1, false, false>(p, L, sm_count, stream);
     }
     if (which) *which = 1;
-    viterbi_generic_kernel<QT, float><<<dim3((unsigned)grid), VG_THREADS, 0, stream>>>(p);
+    ViterbiParams q = p;
+    q.softmax = 0;  // (fast softmax without quality strings: order-preserving, rows decoded as they are)
+    viterbi_generic_kernel<QT, float><<<dim3((unsigned)grid), VG_THREADS, 0, stream>>>(q);
     return cudaGetLastError();
 }
 

@@ -16,6 +16,28 @@ LIB_PATH = os.environ.get("FCTC_LIB") or os.path.join(os.path.dirname(_HERE), "l
 OK, RAN_OUT_OF_BEAM, INCOMPARABLE_VALUES, INVALID_ENVELOPE, NODE_POOL_OVERFLOW, OUTPUT_OVERFLOW, INVALID_QUALITY_CHAR, \
     REFERENCE_PANIC = range(8)
 E_CUDA, E_ARGUMENT, E_NOMEM, E_UNSUPPORTED, E_CAPACITY = -1, -2, -3, -4, -5
+IN_F32, IN_F16, IN_BF16, IN_LOGITS_EXACT, IN_LOGITS_FAST = 0, 1, 2, 0x10, 0x20
+
+
+def to_bf16_bits(a):
+    """float32 array -> bfloat16 bit patterns (uint16), round to nearest even; NaNs stay NaNs."""
+    u = np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+    r = ((u + 0x7FFF + ((u >> 16) & 1)) >> 16).astype(np.uint16)
+    nan = np.isnan(a)
+    if nan.any():
+        r = np.where(nan, np.uint16(0x7FC0), r)
+    return r
+
+
+def from_bf16_bits(b):
+    return (np.ascontiguousarray(b, dtype=np.uint16).astype(np.uint32) << 16).view(np.float32)
+
+
+def _elem_kind(arr, kind):
+    want = {1: np.float16, 2: np.uint16}.get(kind & 0xF, np.float32)  # an unknown kind is the library's to refuse
+    if not isinstance(arr, np.ndarray) or arr.dtype != want or arr.ndim != 3 or not arr.flags.c_contiguous:
+        raise TypeError(f"input_kind {kind:#x} needs a C-contiguous {np.dtype(want).name} array of shape [N, T, C]")
+    return arr
 
 _lib = None
 
@@ -41,6 +63,14 @@ _SIGNATURES = {
                                             _vp, _vp, _vp, _vp]),
     "fctc_viterbi_batch_packed_f16": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _i32, _f32, _f32, _i32, _vp, _vp, _i32, _vp,
                                                 _i64, _vp, _vp, _vp, _vp]),
+    "fctc_viterbi_batch_device_in": (C.c_int, [_vp, _vp, _i32, _i64, _i64, _i32, _i32, _f32, _f32, _i32, _vp, _vp, _i32, _vp,
+                                               _i64, _vp, _vp, _vp, _vp]),
+    "fctc_viterbi_batch_in": (C.c_int, [_vp, _vp, _i32, _i64, _i64, _i32, _i32, _f32, _f32, _i32, _vp, _vp, _i32, _vp, _i64,
+                                        _vp, _vp, _vp, _vp]),
+    "fctc_beam_search_batch_device_in": (C.c_int, [_vp, _vp, _i32, _i64, _i64, _i32, _i32, _f32, _i32, _vp, _vp, _i64, _vp,
+                                                   _vp, _vp, _vp, _vp, _i64, _i32, _vp]),
+    "fctc_beam_search_batch_in": (C.c_int, [_vp, _vp, _i32, _i64, _i64, _i32, _i32, _f32, _i32, _vp, _vp, _i64, _vp, _vp,
+                                            _vp, _vp]),
     "fctc_viterbi_search": (C.c_int, [_vp, _vp, _i64, _i32, _i64, _i64, _i32, _f32, _f32, _i32, _vp, _vp, _vp, _i64,
                                       _vp]),
     "fctc_beam_scratch_bytes": (_i64, [_vp, _i64, _i64, _i32, _i32, _i32]),
@@ -307,6 +337,52 @@ class Decoder:
                        labels.ctypes.data, path.ctypes.data, labels.size, offsets.ctypes.data, lens.ctypes.data,
                        status.ctypes.data, C.byref(used)))
         return dict(labels=labels, path=path, offsets=offsets, lens=lens, status=status, used=used.value)
+
+    def viterbi_batch_in(self, arr, input_kind, qstring=False, qscale=1.0, qbias=0.0, collapse_repeats=True, qual_bytes=1):
+        """fctc_viterbi_batch_in: [N, T, C] float32 / float16 / bfloat16 bits (uint16), posteriors or logits
+        (IN_* | IN_LOGITS_*); packed results as viterbi_batch(packed=True)."""
+        arr = _elem_kind(arr, input_kind)
+        N, T, Cn = arr.shape
+        cap = N * round_up32(T)
+        labels, path = np.empty(cap, np.uint8), np.empty(cap, np.int32)
+        quals = np.empty(cap, np.uint8 if qual_bytes == 1 else np.uint32) if qstring else None
+        offsets, lens, status = np.empty(N, np.int64), np.empty(N, np.int32), np.empty(N, np.int32)
+        used = _i64(0)
+        self._check(self._L.fctc_viterbi_batch_in(self._h, arr.ctypes.data, input_kind, N, T, Cn, int(qstring), qscale, qbias,
+                                                  int(collapse_repeats), labels.ctypes.data, _np_ptr(quals), qual_bytes,
+                                                  path.ctypes.data, cap, offsets.ctypes.data, lens.ctypes.data,
+                                                  status.ctypes.data, C.byref(used)))
+        return dict(labels=labels, quals=quals, path=path, offsets=offsets, lens=lens, status=status, used=used.value)
+
+    def beam_search_batch_in(self, arr, input_kind, beam_size=5, beam_cut_threshold=0.0, collapse_repeats=True):
+        """fctc_beam_search_batch_in: as beam_search_batch for any input kind."""
+        arr = _elem_kind(arr, input_kind)
+        N, T, Cn = arr.shape
+        cap = N * max(round_up32(T), 32)
+        labels, path = np.empty(cap, np.uint8), np.empty(cap, np.int32)
+        offsets, lens, status = np.empty(N, np.int64), np.empty(N, np.int32), np.empty(N, np.int32)
+        used = _i64(0)
+        self._check(self._L.fctc_beam_search_batch_in(self._h, arr.ctypes.data, input_kind, N, T, Cn, beam_size,
+                                                      beam_cut_threshold, int(collapse_repeats), labels.ctypes.data,
+                                                      path.ctypes.data, cap, offsets.ctypes.data, lens.ctypes.data,
+                                                      status.ctypes.data, C.byref(used)))
+        return dict(labels=labels, path=path, offsets=offsets, lens=lens, status=status, used=used.value)
+
+    def viterbi_batch_device_in(self, in_ptr, input_kind, n_reads, n_rows, n_labels, qstring, qscale, qbias, collapse_repeats,
+                                labels_ptr, quals_ptr, qual_bytes, path_ptr, pool_capacity, offsets_ptr, lens_ptr,
+                                status_ptr, stream=0):
+        self._check(self._L.fctc_viterbi_batch_device_in(self._h, in_ptr, input_kind, n_reads, n_rows, n_labels, int(qstring),
+                                                         qscale, qbias, int(collapse_repeats), labels_ptr, quals_ptr or None,
+                                                         qual_bytes, path_ptr, pool_capacity, offsets_ptr, lens_ptr,
+                                                         status_ptr, stream or None))
+
+    def beam_search_batch_device_in(self, in_ptr, input_kind, n_reads, n_rows, n_labels, beam_size, beam_cut_threshold,
+                                    collapse_repeats, labels_ptr, path_ptr, pool_capacity, offsets_ptr, lens_ptr, status_ptr,
+                                    pool_used_ptr, scratch_ptr, scratch_bytes, nodes_per_row=0, stream=0):
+        self._check(self._L.fctc_beam_search_batch_device_in(self._h, in_ptr, input_kind, n_reads, n_rows, n_labels, beam_size,
+                                                             beam_cut_threshold, int(collapse_repeats), labels_ptr, path_ptr,
+                                                             pool_capacity, offsets_ptr, lens_ptr, status_ptr, pool_used_ptr,
+                                                             scratch_ptr, scratch_bytes, nodes_per_row, stream or None))
 
     def beam_search_duplex_batch(self, post1, post2, envelope=None, beam_size=5, beam_cut_threshold=0.0,
                                  collapse_repeats=True, exp_mode=0):

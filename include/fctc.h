@@ -138,6 +138,49 @@ int fctc_viterbi_batch_packed_f16(fctc_handle* h, const void* post_host_f16, int
                                   uint8_t* labels, void* quals, int32_t qual_bytes, int32_t* path, int64_t pool_capacity,
                                   int64_t* offsets, int32_t* lens, int32_t* status, int64_t* pool_used);
 
+/* ------------------------------------------------------------------------------------------
+ * Other input kinds — SURVEY.md section 8(f) rank 2; no counterpart in the reference, whose functions take float32
+ * posteriors only (src/lib.rs:171-188) although the caller's previous step is a softmax over the labels.
+ * input_kind = element type | what the values are:
+ *   FCTC_IN_F32 / FCTC_IN_F16 (IEEE binary16) / FCTC_IN_BF16 (bfloat16): 16-bit values are widened exactly to
+ *     float32 as they are fetched, so results equal the reference's on the widened array at half the traffic;
+ *   | FCTC_IN_LOGITS_EXACT or | FCTC_IN_LOGITS_FAST: the array holds logits (or log-probabilities), and the softmax
+ *     over the label axis is applied in the kernels' load stage instead of by a kernel of the caller's.  The recipe
+ *     is fixed — m = first maximum of the row, e_c = exp(z_c - m), S = e_0 + e_1 + ... in index order, p_c = e_c / S,
+ *     all float32.  EXACT evaluates exp as glibc's expf does and divides with IEEE rounding, so p is bit for bit
+ *     what the recipe gives on a glibc host and the decode equals the reference's on that host-side softmax; FAST
+ *     uses the hardware's 2^x and one reciprocal (a few ulp off, far cheaper; a Viterbi decode without quality
+ *     strings then needs no softmax at all, since it keeps the order of the values).
+ * The four calls below are fctc_viterbi_batch_device, fctc_viterbi_batch_packed (packed results),
+ * fctc_beam_search_batch_device and fctc_beam_search_batch with that extra argument; everything else is unchanged.
+ * The streaming Viterbi kernel takes five labels with n_rows % 4 == 0 (float32) or % 8 == 0 (16-bit); other shapes
+ * run a slower generic kernel.
+ * ------------------------------------------------------------------------------------------ */
+#define FCTC_IN_F32 0
+#define FCTC_IN_F16 1
+#define FCTC_IN_BF16 2
+#define FCTC_IN_LOGITS_EXACT 0x10
+#define FCTC_IN_LOGITS_FAST 0x20
+int fctc_viterbi_batch_device_in(fctc_handle* h, const void* in_dev, int32_t input_kind, int64_t n_reads, int64_t n_rows,
+                                 int32_t n_labels, int32_t qstring, float qscale, float qbias, int32_t collapse_repeats,
+                                 uint8_t* labels_dev, void* quals_dev, int32_t qual_bytes, int32_t* path_dev,
+                                 int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev, int32_t* status_dev,
+                                 void* stream);
+int fctc_viterbi_batch_in(fctc_handle* h, const void* in_host, int32_t input_kind, int64_t n_reads, int64_t n_rows,
+                          int32_t n_labels, int32_t qstring, float qscale, float qbias, int32_t collapse_repeats,
+                          uint8_t* labels, void* quals, int32_t qual_bytes, int32_t* path, int64_t pool_capacity,
+                          int64_t* offsets, int32_t* lens, int32_t* status, int64_t* pool_used);
+int fctc_beam_search_batch_device_in(fctc_handle* h, const void* in_dev, int32_t input_kind, int64_t n_reads,
+                                     int64_t n_rows, int32_t n_labels, int32_t beam_size, float beam_cut_threshold,
+                                     int32_t collapse_repeats, uint8_t* labels_dev, int32_t* path_dev,
+                                     int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev, int32_t* status_dev,
+                                     unsigned long long* pool_used_dev, void* scratch_dev, int64_t scratch_bytes,
+                                     int32_t nodes_per_row, void* stream);
+int fctc_beam_search_batch_in(fctc_handle* h, const void* in_host, int32_t input_kind, int64_t n_reads, int64_t n_rows,
+                              int32_t n_labels, int32_t beam_size, float beam_cut_threshold, int32_t collapse_repeats,
+                              uint8_t* labels, int32_t* path, int64_t pool_capacity, int64_t* offsets, int32_t* lens,
+                              int32_t* status, int64_t* pool_used);
+
 /* fctc_viterbi_search: one read, any strides (in elements) — the shape of the pyo3 entry point
  *   src/lib.rs:171-212.  labels/quals/path hold `capacity` entries (n_rows always suffices).
  *   Returns the decode status; n_rows == 0 or n_labels == 0 gives FCTC_E_ARGUMENT (the reference

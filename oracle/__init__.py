@@ -44,6 +44,8 @@ def lib():
         for name in ("oracle_expf_n", "oracle_log1pf_n"):
             getattr(L, name).restype = None
             getattr(L, name).argtypes = [vp, vp, i64]
+        L.oracle_softmax_rows.restype = None
+        L.oracle_softmax_rows.argtypes = [vp, vp, i64, i64]
         L.oracle_fastexp_as_shipped.restype = C.c_float
         L.oracle_fastexp_as_shipped.argtypes = [C.c_float]
         L.oracle_logadd.restype = C.c_float
@@ -90,6 +92,14 @@ def _f32(a):
     if a.dtype != np.float32:
         raise TypeError("posteriors must be float32")
     return a
+
+
+def softmax(logits):
+    """float32 softmax over the last axis by the recipe of the logits entry points (input.cuh), with the system libm."""
+    z = np.ascontiguousarray(_f32(logits))
+    out = np.empty_like(z)
+    lib().oracle_softmax_rows(_ptr(z), _ptr(out), z.size // z.shape[-1], z.shape[-1])
+    return out
 
 
 def hardware_threads():

@@ -739,6 +739,24 @@ void oracle_log10f_n(const float* x, float* y, int64_t n) { for (int64_t i = 0; 
 
 void oracle_logf_n(const float* x, float* y, int64_t n) { for (int64_t i = 0; i < n; ++i) y[i] = logf(x[i]); }
 // the system libm's expf / log1pf: what Rust's f32::exp / f32::ln_1p call in LogSpace '+' (src/duplex.rs:45-52)
+// The softmax recipe of the logits entry points (fast-ctc-decode_b200/csrc/input.cuh), with the system libm: m = first
+// maximum, e_c = expf(z_c - m), S summed in index order, p_c = e_c / S, all float32.  Not part of the reference (its
+// callers hand it posteriors); decoding p with the reference algorithms is what the GPU path must reproduce.
+void oracle_softmax_rows(const float* z, float* p, int64_t n_rows, int64_t C) {
+    for (int64_t r = 0; r < n_rows; ++r) {
+        const float* zr = z + r * C;
+        float* pr = p + r * C;
+        float m = zr[0];
+        for (int64_t c = 1; c < C; ++c)
+            if (zr[c] > m) m = zr[c];
+        float S = 0.0f;
+        for (int64_t c = 0; c < C; ++c) {
+            pr[c] = expf(zr[c] - m);
+            S = (c == 0) ? pr[c] : S + pr[c];
+        }
+        for (int64_t c = 0; c < C; ++c) pr[c] = pr[c] / S;
+    }
+}
 void oracle_expf_n(const float* x, float* y, int64_t n) { for (int64_t i = 0; i < n; ++i) y[i] = expf(x[i]); }
 void oracle_log1pf_n(const float* x, float* y, int64_t n) { for (int64_t i = 0; i < n; ++i) y[i] = log1pf(x[i]); }
 
