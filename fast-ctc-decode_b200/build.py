@@ -11,7 +11,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libfctc_b200.so")
-SOURCES = ["api.cu", "viterbi.cu", "beam.cu", "beam_small.cu", "duplex.cu", "duplex_packed.cu", "crf.cu", "fastq.cu", "pack.cu", "multi.cu", "synth.cu"]
+SOURCES = ["api.cu", "viterbi.cu", "beam.cu", "beam_small.cu", "duplex.cu", "duplex_packed.cu", "crf.cu", "fastq.cu", "align.cu", "pack.cu", "multi.cu", "synth.cu"]
 HEADERS = ["kernels.h", "device_utils.cuh", "phred.cuh", "duplex_common.cuh", os.path.join("..", "..", "include", "fctc.h")]
 
 NVCC_FLAGS = [

@@ -1003,6 +1003,61 @@ int fctc_duplex_envelope_device(fctc_handle* h, const int32_t* path1_dev, const 
     return 0;
 }
 
+int64_t fctc_align_scratch_bytes(const fctc_handle* h, int64_t n_pairs, int64_t max_bases, int32_t band_bases) {
+    if (!h || n_pairs < 0 || max_bases < 0 || band_bases < 1) return 0;
+    return fctc::align_scratch_bytes(h->sm_count, n_pairs, max_bases, band_bases, 0, nullptr, nullptr);
+}
+
+int fctc_duplex_envelope_aligned_device(fctc_handle* h, const uint8_t* labels1_dev, const int32_t* path1_dev,
+                                        const int64_t* offsets1_dev, const int32_t* lens1_dev, const uint8_t* labels2_dev,
+                                        const int32_t* path2_dev, const int64_t* offsets2_dev, const int32_t* lens2_dev,
+                                        int64_t n_pairs, int64_t n_rows_1, int64_t n_rows_2, int32_t band_bases,
+                                        int32_t pad_rows, int64_t* envelope_dev, int32_t* max_window_dev,
+                                        int32_t* partner_dev, void* scratch_dev, int64_t scratch_bytes, void* stream) {
+    if (!h) return FCTC_E_ARGUMENT;
+    if (n_pairs < 0 || n_rows_1 <= 0 || n_rows_2 <= 0 || pad_rows < 0)
+        return fail(h, FCTC_E_ARGUMENT, "n_pairs >= 0, n_rows_1 > 0, n_rows_2 > 0 and pad_rows >= 0 are required");
+    if (band_bases < 1 || band_bases > 127) return fail(h, FCTC_E_ARGUMENT, "band_bases must lie in 1..127");
+    if (!labels1_dev || !path1_dev || !offsets1_dev || !lens1_dev || !labels2_dev || !path2_dev || !offsets2_dev || !lens2_dev ||
+        !envelope_dev || !partner_dev || !scratch_dev)
+        return fail(h, FCTC_E_ARGUMENT, "null device pointer");
+    FCTC_CUDA(h, cudaSetDevice(h->device));
+    fctc::AlignParams a{};
+    a.labels1 = labels1_dev; a.offsets1 = offsets1_dev; a.lens1 = lens1_dev;
+    a.labels2 = labels2_dev; a.offsets2 = offsets2_dev; a.lens2 = lens2_dev;
+    a.N = n_pairs; a.band = band_bases; a.partner = partner_dev; a.dirs = static_cast<uint8_t*>(scratch_dev);
+    // a read emits at most one base per row: n_rows_1 bounds read 1's length
+    fctc::align_scratch_bytes(h->sm_count, n_pairs, n_rows_1, band_bases, scratch_bytes, &a.n_slots, &a.dir_bytes_per_slot);
+    if (n_pairs > 0 && a.n_slots < 1)
+        return fail(h, FCTC_E_CAPACITY, "alignment scratch too small: %lld bytes given, one pair needs %lld (fctc_align_scratch_bytes)",
+                    (long long)scratch_bytes, (long long)a.dir_bytes_per_slot);
+    FCTC_CUDA(h, fctc::launch_align(a, static_cast<cudaStream_t>(stream)));
+    fctc::EnvelopeParams p{};
+    p.path1 = path1_dev; p.offsets1 = offsets1_dev; p.lens1 = lens1_dev;
+    p.path2 = path2_dev; p.offsets2 = offsets2_dev; p.lens2 = lens2_dev;
+    p.N = n_pairs; p.T1 = n_rows_1; p.T2 = n_rows_2; p.pad = pad_rows;
+    p.env = reinterpret_cast<long long*>(envelope_dev);
+    p.max_window = max_window_dev;
+    p.partner = partner_dev;
+    FCTC_CUDA(h, fctc::launch_envelope(p, static_cast<cudaStream_t>(stream)));
+    return 0;
+}
+
+int fctc_move_table_device(fctc_handle* h, const int32_t* path_dev, const int64_t* offsets_dev, const int32_t* lens_dev,
+                           const int32_t* status_dev, int64_t n_reads, int64_t n_rows, uint8_t* moves_dev,
+                           int32_t* dwell_dev, void* stream) {
+    if (!h) return FCTC_E_ARGUMENT;
+    if (n_reads < 0 || n_rows <= 0) return fail(h, FCTC_E_ARGUMENT, "n_reads >= 0 and n_rows > 0 are required");
+    if (!path_dev || !offsets_dev || !lens_dev || !status_dev || (!moves_dev && !dwell_dev))
+        return fail(h, FCTC_E_ARGUMENT, "null device pointer (at least one of moves_dev / dwell_dev must be given)");
+    FCTC_CUDA(h, cudaSetDevice(h->device));
+    fctc::MovesParams p{};
+    p.path = path_dev; p.offsets = offsets_dev; p.lens = lens_dev; p.status = status_dev;
+    p.N = n_reads; p.T = n_rows; p.moves = moves_dev; p.dwell = dwell_dev;
+    FCTC_CUDA(h, fctc::launch_moves(p, h->sm_count, static_cast<cudaStream_t>(stream)));
+    return 0;
+}
+
 // ---------------------------------------------------------------------------------------------
 // Synthetic input + host test hooks
 // ---------------------------------------------------------------------------------------------

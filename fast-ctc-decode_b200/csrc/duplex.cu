@@ -784,13 +784,14 @@ namespace {
 
 // One synchronous pass over pairs [first, first+cnt) of host arrays.  Results are appended to the
 // host pool at *used.
-int dx_host_chunk(fctc_handle* h, const float* post1, const float* post2, const int64_t* env, int64_t cnt, int64_t T1,
+int dx_host_chunk(fctc_handle* h, const void* post1, const void* post2, int in_f16, const int64_t* env, int64_t cnt, int64_t T1,
                   int64_t T2, int32_t C, int W, int32_t beam, float thr, int32_t collapse, int32_t exp_mode,
                   int32_t nodes_per_row, uint8_t* labels, int64_t pool_cap, int64_t* offsets, int32_t* lens,
                   int32_t* status, int64_t* used) {
     cudaStream_t st = fctc::handle_stream(h);
     const int64_t stride = (T1 + 31) & ~int64_t(31);
-    const size_t b1 = size_t(cnt) * T1 * C * 4, b2 = size_t(cnt) * T2 * C * 4, be = size_t(cnt) * T1 * 16;
+    const size_t eb = in_f16 ? 2 : 4;
+    const size_t b1 = size_t(cnt) * T1 * C * eb, b2 = size_t(cnt) * T2 * C * eb, be = size_t(cnt) * T1 * 16;
     float* d1 = static_cast<float*>(fctc::handle_device_buffer(h, 0, b1));
     float* d2 = static_cast<float*>(fctc::handle_device_buffer(h, 1, std::max<size_t>(b2, 16)));
     long long* de = env ? static_cast<long long*>(fctc::handle_device_buffer(h, 2, be)) : nullptr;
@@ -816,7 +817,7 @@ int dx_host_chunk(fctc_handle* h, const float* post1, const float* post2, const 
     if (b2) DX_CUDA(cudaMemcpyAsync(d2, post2, b2, cudaMemcpyHostToDevice, st));
     if (env) DX_CUDA(cudaMemcpyAsync(de, env, be, cudaMemcpyHostToDevice, st));
     DX_CUDA(cudaMemsetAsync(dcur, 0, 8, st));
-    p.post1 = d1; p.post2 = d2; p.env = de; p.N = cnt; p.T1 = int(T1); p.T2 = int(T2); p.C = C; p.beam_size = beam;
+    p.post1 = d1; p.post2 = d2; p.in_f16 = in_f16; p.env = de; p.N = cnt; p.T1 = int(T1); p.T2 = int(T2); p.C = C; p.beam_size = beam;
     p.threshold = thr; p.collapse = collapse; p.exp_mode = exp_mode; p.labels = dl; p.pool_cap = cnt * stride;
     p.offsets = doff; p.lens = dlen; p.status = dst; p.cursor = dcur; p.scratch = scratch;
     p.ticket = static_cast<unsigned long long*>(scratch);
@@ -838,12 +839,15 @@ int dx_host_chunk(fctc_handle* h, const float* post1, const float* post2, const 
 
 }  // namespace
 
-extern "C" int fctc_beam_search_duplex_batch(fctc_handle* h, const float* post1_host, const float* post2_host,
-                                             int64_t n_pairs, int64_t n_rows_1, int64_t n_rows_2, int32_t n_labels,
-                                             const int64_t* envelope_host, int32_t beam_size, float beam_cut_threshold,
-                                             int32_t collapse_repeats, int32_t exp_mode, uint8_t* labels,
-                                             int64_t pool_capacity, int64_t* offsets, int32_t* lens, int32_t* status,
-                                             int64_t* pool_used) {
+static int dx_batch_host_any(fctc_handle* h, const void* post1_any, const void* post2_any, int in_f16,
+                             int64_t n_pairs, int64_t n_rows_1, int64_t n_rows_2, int32_t n_labels,
+                             const int64_t* envelope_host, int32_t beam_size, float beam_cut_threshold,
+                             int32_t collapse_repeats, int32_t exp_mode, uint8_t* labels,
+                             int64_t pool_capacity, int64_t* offsets, int32_t* lens, int32_t* status,
+                             int64_t* pool_used) {
+    const unsigned char* post1_host = static_cast<const unsigned char*>(post1_any);
+    const unsigned char* post2_host = static_cast<const unsigned char*>(post2_any);
+    const int64_t eb = in_f16 ? 2 : 4;
     if (int rc = dx_check(h, n_pairs, n_rows_1, n_rows_2, n_labels, beam_size, beam_cut_threshold)) return rc;
     if (!post1_host || (!post2_host && n_rows_2 > 0) || !labels || !offsets || !lens || !status)
         return fctc::handle_fail(h, FCTC_E_ARGUMENT, "null host pointer");
@@ -864,7 +868,7 @@ extern "C" int fctc_beam_search_duplex_batch(fctc_handle* h, const float* post1_
         }
     }
     const int W = int(wmax + 1);
-    const int64_t pair_bytes = (n_rows_1 + n_rows_2) * int64_t(n_labels) * 4;
+    const int64_t pair_bytes = (n_rows_1 + n_rows_2) * int64_t(n_labels) * eb;
     // a chunk is a whole number of rounds of the pairs in flight (a partial round costs a full one), as many as 2 GiB
     // of posteriors hold, at least one
     const int64_t in_flight = int64_t(fctc::handle_sm_count(h)) *
@@ -875,8 +879,8 @@ extern "C" int fctc_beam_search_duplex_batch(fctc_handle* h, const float* post1_
     int64_t used = 0;
     for (int64_t first = 0; first < n_pairs; first += chunk) {
         const int64_t cnt = std::min(chunk, n_pairs - first);
-        if (int rc = dx_host_chunk(h, post1_host + first * n_rows_1 * n_labels, post2_host + first * n_rows_2 * n_labels,
-                                   envelope_host ? envelope_host + first * n_rows_1 * 2 : nullptr, cnt, n_rows_1, n_rows_2,
+        if (int rc = dx_host_chunk(h, post1_host + first * n_rows_1 * n_labels * eb, post2_host + first * n_rows_2 * n_labels * eb,
+                                   in_f16, envelope_host ? envelope_host + first * n_rows_1 * 2 : nullptr, cnt, n_rows_1, n_rows_2,
                                    n_labels, W, beam_size, beam_cut_threshold, collapse_repeats, exp_mode, 0, labels,
                                    pool_capacity, offsets + first, lens + first, status + first, &used))
             return rc;
@@ -885,14 +889,36 @@ extern "C" int fctc_beam_search_duplex_batch(fctc_handle* h, const float* post1_
     const int32_t bound = std::max<int32_t>(1, (n_labels - 1) * beam_size);
     for (int64_t n = 0; n < n_pairs; ++n) {
         if (status[n] != FCTC_NODE_POOL_OVERFLOW) continue;
-        if (int rc = dx_host_chunk(h, post1_host + n * n_rows_1 * n_labels, post2_host + n * n_rows_2 * n_labels,
-                                   envelope_host ? envelope_host + n * n_rows_1 * 2 : nullptr, 1, n_rows_1, n_rows_2, n_labels, W,
+        if (int rc = dx_host_chunk(h, post1_host + n * n_rows_1 * n_labels * eb, post2_host + n * n_rows_2 * n_labels * eb,
+                                   in_f16, envelope_host ? envelope_host + n * n_rows_1 * 2 : nullptr, 1, n_rows_1, n_rows_2, n_labels, W,
                                    beam_size, beam_cut_threshold, collapse_repeats, exp_mode, bound, labels, pool_capacity,
                                    offsets + n, lens + n, status + n, &used))
             return rc;
     }
     if (pool_used) *pool_used = used;
     return 0;
+}
+
+extern "C" int fctc_beam_search_duplex_batch(fctc_handle* h, const float* post1_host, const float* post2_host,
+                                             int64_t n_pairs, int64_t n_rows_1, int64_t n_rows_2, int32_t n_labels,
+                                             const int64_t* envelope_host, int32_t beam_size, float beam_cut_threshold,
+                                             int32_t collapse_repeats, int32_t exp_mode, uint8_t* labels,
+                                             int64_t pool_capacity, int64_t* offsets, int32_t* lens, int32_t* status,
+                                             int64_t* pool_used) {
+    return dx_batch_host_any(h, post1_host, post2_host, 0, n_pairs, n_rows_1, n_rows_2, n_labels, envelope_host, beam_size,
+                             beam_cut_threshold, collapse_repeats, exp_mode, labels, pool_capacity, offsets, lens, status,
+                             pool_used);
+}
+
+extern "C" int fctc_beam_search_duplex_batch_f16(fctc_handle* h, const void* post1_host_f16, const void* post2_host_f16,
+                                                 int64_t n_pairs, int64_t n_rows_1, int64_t n_rows_2, int32_t n_labels,
+                                                 const int64_t* envelope_host, int32_t beam_size,
+                                                 float beam_cut_threshold, int32_t collapse_repeats, int32_t exp_mode,
+                                                 uint8_t* labels, int64_t pool_capacity, int64_t* offsets, int32_t* lens,
+                                                 int32_t* status, int64_t* pool_used) {
+    return dx_batch_host_any(h, post1_host_f16, post2_host_f16, 1, n_pairs, n_rows_1, n_rows_2, n_labels, envelope_host,
+                             beam_size, beam_cut_threshold, collapse_repeats, exp_mode, labels, pool_capacity, offsets, lens,
+                             status, pool_used);
 }
 
 extern "C" int fctc_beam_search_duplex(fctc_handle* h, const float* post1_host, int64_t n_rows_1, int64_t stride_row_1,

@@ -214,6 +214,11 @@ __device__ __forceinline__ long long env_center(const EnvelopeParams& p, long lo
         const long long first = b[0];
         return prop < first ? prop : first;
     }
+    if (p.partner) {  // aligned anchor (launch_align), kept inside read 2
+        int j = p.partner[p.offsets1[n] + k - 1];
+        j = j < 0 ? 0 : (j >= L2 ? L2 - 1 : j);
+        return b[j];
+    }
     return b[(long long)(k - 1) * L2 / L1];
 }
 

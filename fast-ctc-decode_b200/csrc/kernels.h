@@ -186,7 +186,40 @@ struct EnvelopeParams {
     int64_t pad;             // half-width of the window, in network-2 rows
     long long* env;          // [N, T1, 2]
     int* max_window;         // optional: receives the widest window (hi - lo) of the whole batch
+    const int32_t* partner;  // optional, read 1's slot layout: base k of read 1 is anchored to base partner[k] of read 2
+                             // (launch_align); null = the proportional anchor k * L2 / L1
 };
+
+// banded alignment of the pairs' label strings (align.cu)
+struct AlignParams {
+    const uint8_t* labels1;   // slot-form labels of read 1 / read 2
+    const int64_t* offsets1;
+    const int32_t* lens1;
+    const uint8_t* labels2;
+    const int64_t* offsets2;
+    const int32_t* lens2;
+    int64_t N;
+    int band;                 // half-width of the band, in bases
+    int32_t* partner;         // out, read 1's slot layout
+    uint8_t* dirs;            // scratch: n_slots x dir_bytes_per_slot move bytes
+    int64_t dir_bytes_per_slot;
+    int n_slots;
+};
+int64_t align_scratch_bytes(int sm_count, int64_t N, int64_t max_len, int band, int64_t budget_bytes, int* n_slots,
+                            int64_t* dir_bytes_per_slot);
+cudaError_t launch_align(const AlignParams& p, cudaStream_t stream);
+
+// move table / dwells from the emission rows (align.cu)
+struct MovesParams {
+    const int32_t* path;
+    const int64_t* offsets;
+    const int32_t* lens;
+    const int32_t* status;
+    int64_t N, T;
+    uint8_t* moves;  // optional [N, T]
+    int32_t* dwell;  // optional, same layout as path
+};
+cudaError_t launch_moves(const MovesParams& p, int sm_count, cudaStream_t stream);
 cudaError_t launch_envelope(const EnvelopeParams& p, cudaStream_t stream);
 cudaError_t launch_poison_smem(int sm_count, int byte, unsigned int* sink, cudaStream_t stream);
 cudaError_t launch_synth(float* post, int64_t N, int64_t T, int C, int kind, uint64_t seed, int64_t first_read,

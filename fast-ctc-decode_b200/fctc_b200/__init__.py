@@ -100,6 +100,8 @@ _SIGNATURES = {
                                                            _vp]),
     "fctc_beam_search_duplex_batch": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i64, _i32, _vp, _i32, _f32, _i32, _i32,
                                                 _vp, _i64, _vp, _vp, _vp, _vp]),
+    "fctc_beam_search_duplex_batch_f16": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i64, _i32, _vp, _i32, _f32, _i32, _i32,
+                                                    _vp, _i64, _vp, _vp, _vp, _vp]),
     "fctc_beam_search_duplex": (C.c_int, [_vp, _vp, _i64, _i64, _i64, _vp, _i64, _i64, _i64, _i32, _vp, _i64, _i64,
                                           _i32, _f32, _i32, _i32, _vp, _i64, _vp]),
     "fctc_crf_greedy_batch_device": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i32, _i32, _i32, _i32, _f32, _f32, _vp, _vp,
@@ -118,6 +120,10 @@ _SIGNATURES = {
     "fctc_fastq_records_device": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, C.c_char_p, _i32, C.c_char_p, _i64, _vp,
                                             _i64, _vp, _vp, _i64, _vp]),
     "fctc_duplex_envelope_device": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i32, _vp, _vp, _vp]),
+    "fctc_align_scratch_bytes": (_i64, [_vp, _i64, _i64, _i32]),
+    "fctc_duplex_envelope_aligned_device": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i32,
+                                                      _i32, _vp, _vp, _vp, _vp, _i64, _vp]),
+    "fctc_move_table_device": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _vp, _vp, _vp]),
     "fctc_synth_posteriors_device": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _i32, _u64, _i64, _vp]),
     "fctc_test_poison_shared_memory": (C.c_int, [_vp, _i32]),
     "fctc_host_phred": (C.c_uint32, [_f32, _f32, _f32]),
@@ -215,6 +221,25 @@ class Decoder:
         self._check(self._L.fctc_duplex_envelope_device(self._h, path1_ptr, offsets1_ptr, lens1_ptr, path2_ptr,
                                                         offsets2_ptr, lens2_ptr, n_pairs, n_rows_1, n_rows_2, pad_rows,
                                                         envelope_ptr, max_window_ptr or None, stream or None))
+
+    def align_scratch_bytes(self, n_pairs, max_bases, band_bases):
+        return int(self._L.fctc_align_scratch_bytes(self._h, n_pairs, max_bases, band_bases))
+
+    def duplex_envelope_aligned_device(self, labels1_ptr, path1_ptr, offsets1_ptr, lens1_ptr, labels2_ptr, path2_ptr,
+                                       offsets2_ptr, lens2_ptr, n_pairs, n_rows_1, n_rows_2, band_bases, pad_rows,
+                                       envelope_ptr, max_window_ptr, partner_ptr, scratch_ptr, scratch_bytes, stream=0):
+        """Envelope from a banded alignment of the two reads' Viterbi label strings (fctc_duplex_envelope_aligned_device)."""
+        self._check(self._L.fctc_duplex_envelope_aligned_device(self._h, labels1_ptr, path1_ptr, offsets1_ptr, lens1_ptr,
+                                                                labels2_ptr, path2_ptr, offsets2_ptr, lens2_ptr, n_pairs,
+                                                                n_rows_1, n_rows_2, band_bases, pad_rows, envelope_ptr,
+                                                                max_window_ptr or None, partner_ptr, scratch_ptr,
+                                                                scratch_bytes, stream or None))
+
+    def move_table_device(self, path_ptr, offsets_ptr, lens_ptr, status_ptr, n_reads, n_rows, moves_ptr=0, dwell_ptr=0,
+                          stream=0):
+        """uint8 move table [n_reads, n_rows] and / or int32 dwells (path layout) from the emission rows."""
+        self._check(self._L.fctc_move_table_device(self._h, path_ptr, offsets_ptr, lens_ptr, status_ptr, n_reads, n_rows,
+                                                   moves_ptr or None, dwell_ptr or None, stream or None))
 
     def poison_shared_memory(self, byte=0xFF):
         """Test hook: every SM's shared memory is filled with `byte` before the next kernel starts."""
@@ -386,8 +411,12 @@ class Decoder:
 
     def beam_search_duplex_batch(self, post1, post2, envelope=None, beam_size=5, beam_cut_threshold=0.0,
                                  collapse_repeats=True, exp_mode=0):
-        """post1 [N,T1,C], post2 [N,T2,C] float32 C-contiguous; envelope int64 [N,T1,2] or None."""
-        post1, post2 = _as_f32_3d(post1), _as_f32_3d(post2)
+        """post1 [N,T1,C], post2 [N,T2,C] float32 (or both float16) C-contiguous; envelope int64 [N,T1,2] or None."""
+        f16 = getattr(post1, "dtype", None) == np.float16 and getattr(post2, "dtype", None) == np.float16
+        if f16:
+            post1, post2 = np.ascontiguousarray(post1), np.ascontiguousarray(post2)
+        else:
+            post1, post2 = _as_f32_3d(post1), _as_f32_3d(post2)
         N, T1, Cn = post1.shape
         T2 = post2.shape[1]
         if post2.shape[0] != N or post2.shape[2] != Cn:
@@ -403,7 +432,8 @@ class Decoder:
         lens = np.empty(N, np.int32)
         status = np.empty(N, np.int32)
         used = _i64(0)
-        self._check(self._L.fctc_beam_search_duplex_batch(self._h, post1.ctypes.data, post2.ctypes.data, N, T1, T2, Cn,
+        fn = self._L.fctc_beam_search_duplex_batch_f16 if f16 else self._L.fctc_beam_search_duplex_batch
+        self._check(fn(self._h, post1.ctypes.data, post2.ctypes.data, N, T1, T2, Cn,
                                                           _np_ptr(env), beam_size, beam_cut_threshold,
                                                           int(collapse_repeats), exp_mode, labels.ctypes.data, cap,
                                                           offsets.ctypes.data, lens.ctypes.data, status.ctypes.data,

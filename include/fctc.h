@@ -321,6 +321,13 @@ int fctc_beam_search_duplex_batch(fctc_handle* h, const float* post1_host, const
                                   int32_t beam_size, float beam_cut_threshold, int32_t collapse_repeats,
                                   int32_t exp_mode, uint8_t* labels, int64_t pool_capacity, int64_t* offsets,
                                   int32_t* lens, int32_t* status, int64_t* pool_used);
+/* The host batch call for binary16 posteriors (both networks; widened exactly as they are read): half the PCIe bytes.
+ * No counterpart in the reference. */
+int fctc_beam_search_duplex_batch_f16(fctc_handle* h, const void* post1_host_f16, const void* post2_host_f16,
+                                      int64_t n_pairs, int64_t n_rows_1, int64_t n_rows_2, int32_t n_labels,
+                                      const int64_t* envelope_host, int32_t beam_size, float beam_cut_threshold,
+                                      int32_t collapse_repeats, int32_t exp_mode, uint8_t* labels, int64_t pool_capacity,
+                                      int64_t* offsets, int32_t* lens, int32_t* status, int64_t* pool_used);
 /* One pair, any strides (elements) — the shape of the pyo3 entry point src/lib.rs:402-488;
  * envelope is the reference's usize array [n_rows_1, 2] (strides in elements) or NULL. */
 int fctc_beam_search_duplex(fctc_handle* h, const float* post1_host, int64_t n_rows_1, int64_t stride_row_1,
@@ -414,6 +421,38 @@ int fctc_duplex_envelope_device(fctc_handle* h, const int32_t* path1_dev, const 
                                 const int32_t* lens1_dev, const int32_t* path2_dev, const int64_t* offsets2_dev,
                                 const int32_t* lens2_dev, int64_t n_pairs, int64_t n_rows_1, int64_t n_rows_2,
                                 int32_t pad_rows, int64_t* envelope_dev, int32_t* max_window_dev, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Duplex envelope from a banded alignment of the two reads' Viterbi label strings — SURVEY.md section 8(f) rank 4 as
+ * written; no counterpart in the reference (src/lib.rs:376-378 leaves the envelope to the caller, src/duplex.rs:484-488
+ * only checks it).  fctc_duplex_envelope_device above anchors base k of read 1 to base k*L2/L1 of read 2, which
+ * drifts by as many bases as one read has lost or gained up to that point and forces wide windows (the 2-D
+ * search's cost is linear in the window).  Here the label strings are aligned first (unit-cost edit distance inside
+ * a band of +-band_bases around the proportional diagonal, ties diagonal > up > left), base k is anchored to its
+ * aligned partner, and the window rule is the same as above.  Inputs: the slot-form labels / path / offsets / lens
+ * of fctc_viterbi_batch_device on both networks.  partner_dev: int32, read 1's pool layout (entry offsets1[n] + k =
+ * index in read 2 of the partner of base k), also an output.  scratch_dev: fctc_align_scratch_bytes(h, n_pairs,
+ * n_rows_1, band_bases) bytes for all pairs in flight; less is accepted (fewer pairs at a time), below one pair's
+ * worth FCTC_E_CAPACITY.  Pairs whose lengths differ by more than the band keep the proportional anchor.
+ * ------------------------------------------------------------------------------------------ */
+int64_t fctc_align_scratch_bytes(const fctc_handle* h, int64_t n_pairs, int64_t max_bases, int32_t band_bases);
+int fctc_duplex_envelope_aligned_device(fctc_handle* h, const uint8_t* labels1_dev, const int32_t* path1_dev,
+                                        const int64_t* offsets1_dev, const int32_t* lens1_dev, const uint8_t* labels2_dev,
+                                        const int32_t* path2_dev, const int64_t* offsets2_dev, const int32_t* lens2_dev,
+                                        int64_t n_pairs, int64_t n_rows_1, int64_t n_rows_2, int32_t band_bases,
+                                        int32_t pad_rows, int64_t* envelope_dev, int32_t* max_window_dev,
+                                        int32_t* partner_dev, void* scratch_dev, int64_t scratch_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Move table and dwells from the emission rows — SURVEY.md section 8(f) rank 3, second half; no counterpart in the
+ * reference, which returns the rows (`path`, src/search.rs:378-380) and leaves derived formats to the caller.
+ * moves_dev (optional): uint8 [n_reads, n_rows], 1 where the row emitted a base (the basecallers' "move table");
+ * dwell_dev (optional): int32 in the layout of path_dev, rows from a base's emission to the next one (to the end of
+ * the read for the last base).  Reads whose status is not FCTC_OK give an all-zero move row and no dwells.
+ * ------------------------------------------------------------------------------------------ */
+int fctc_move_table_device(fctc_handle* h, const int32_t* path_dev, const int64_t* offsets_dev, const int32_t* lens_dev,
+                           const int32_t* status_dev, int64_t n_reads, int64_t n_rows, uint8_t* moves_dev,
+                           int32_t* dwell_dev, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Synthetic posterior generator used by bench.py and the tests (no reference counterpart; it

@@ -225,6 +225,20 @@ def test_single_pair_with_envelope_and_strides(dec, oracle):
     assert st == ost == 0 and labels.tolist() == ol.tolist()
 
 
+def test_f16_posteriors_host_batch(dec, oracle):
+    """fctc_beam_search_duplex_batch_f16: identical to the oracle on the exactly widened arrays, both exp modes."""
+    rng = np.random.default_rng(556)
+    p1, p2 = duplex_pairs(rng, 10, 260, 250, 5)
+    h1, h2 = p1.astype(np.float16), p2.astype(np.float16)
+    env = band_envelope(10, 260, 250, 9)
+    for mode in (0, 1):
+        res = dec.beam_search_duplex_batch(h1, h2, env, 5, 0.0, True, exp_mode=mode)
+        ol, olen, ost = oracle.beam_search_duplex_batch(h1.astype(np.float32), h2.astype(np.float32), env.astype(np.uint64),
+                                                        5, 0.0, True, exp_mode=mode)
+        assert res["status"].tolist() == ost.tolist()
+        assert seqs(res) == [ol[n, :olen[n]].tolist() for n in range(10)]
+
+
 def test_f16_posteriors_device_batch(dec, oracle):
     """Binary16 posteriors through the device entry point: identical to the oracle on the exactly widened
     arrays (max-plus mode, which is bit-exact)."""
