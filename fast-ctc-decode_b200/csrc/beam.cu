@@ -90,6 +90,11 @@ __device__ __forceinline__ BeamView beam_view(unsigned char* base, int B) {
 // HALF (plain search only): the posteriors are binary16, widened exactly to f32 as they are fetched.
 static __constant__ uint64_t c_beam_exp2f[32] = FCTC_EXP2F_TAB;
 
+// Out of line, so that the posterior-input path (the common one) keeps its register allocation.
+static __device__ __noinline__ void softmax_staged_rows(float* rows, int n_rows, int C, int mode, const uint64_t* xt, int lane) {
+    for (int r = lane; r < n_rows; r += 32) softmax_row(rows + r * C, C, mode, xt);
+}
+
 template <bool CRF, int CT, bool HALF>
 __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParams p, const BeamLayout L) {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -199,7 +204,7 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
             __syncwarp();
             const int rows_here = int((T - t0 < R) ? (T - t0) : R);
             if (!CRF && p.softmax != 0) {  // logits: every staged row becomes its softmax (input.cuh), one row per lane
-                for (int r = lane; r < rows_here; r += 32) softmax_row(rows + r * C, C, p.softmax, s_xt);
+                softmax_staged_rows(rows, rows_here, C, p.softmax, s_xt, lane);
                 __syncwarp();
             }
 

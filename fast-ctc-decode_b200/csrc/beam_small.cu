@@ -47,6 +47,11 @@ constexpr int BS_WARP_SMEM = 2 * BS_ROWBUF * 4 + 16 + 128;  // row buffers, the 
 // HALF (plain search only): the posteriors are binary16, widened exactly to f32 as they are fetched.
 static __constant__ uint64_t c_beam_exp2f[32] = FCTC_EXP2F_TAB;
 
+// Out of line, so that the posterior-input path (the common one) keeps its register allocation.
+static __device__ __noinline__ void softmax_staged_rows(float* rows, int n_rows, int C, int mode, const uint64_t* xt, int lane) {
+    for (int r = lane; r < n_rows; r += 32) softmax_row(rows + r * C, C, mode, xt);
+}
+
 template <bool CRF, int CT, bool HALF>
 __global__ void __launch_bounds__(BS_THREADS, BS_MINBLOCKS) beam_small_kernel(const BeamParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -140,7 +145,7 @@ __global__ void __launch_bounds__(BS_THREADS, BS_MINBLOCKS) beam_small_kernel(co
             __syncwarp();
             const int rows_here = int((T - t0 < R) ? (T - t0) : R);
             if (!CRF && p.softmax != 0) {  // logits: every staged row becomes its softmax (input.cuh), one row per lane
-                for (int r = lane; r < rows_here; r += 32) softmax_row(rows + r * C, C, p.softmax, s_xt);
+                softmax_staged_rows(rows, rows_here, C, p.softmax, s_xt, lane);
                 __syncwarp();
             }
 
