@@ -485,8 +485,9 @@ def measure_workload(name, w, args, steps, ctx):
                   "reads_per_step_per_gpu": ne, "ms_per_step": dt * 1e3,
                   "h2d_gbs_per_gpu": h2d / dt / 1e9, "d2h_gbs_per_gpu": d2h / dt / 1e9,
                   "note": "fctc_*_batch (host pointers, pinned memory); every rank streams its own shard, max over ranks"}
-    if rank == 0:
-        # ---- CPU baseline on a bounded sample of the same bytes ------------------------------------------
+    if rank == 0 and world == 1:
+        # ---- CPU baseline on a bounded sample of the same bytes (N = 1 only: under torchrun the ranks share the host
+        #      cores, and rank 0 is pinned to its share of them; the reference arm gives the CPU figure there) --------
         import oracle
         oracle.build()
         nc = min(w["cpu_sample"], ne)
