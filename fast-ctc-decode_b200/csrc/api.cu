@@ -1079,6 +1079,14 @@ int fctc_test_poison_shared_memory(fctc_handle* h, int32_t byte) {
     return 0;
 }
 
+int fctc_test_libm_device(fctc_handle* h, const float* x_dev, const float* y_dev, float* out_dev, int64_t n, int32_t which,
+                          void* stream) {
+    if (!h || !x_dev || !out_dev || which < 0 || which > 4 || (which == 4 && !y_dev)) return FCTC_E_ARGUMENT;
+    FCTC_CUDA(h, cudaSetDevice(h->device));
+    FCTC_CUDA(h, fctc::launch_libm_probe(x_dev, y_dev, out_dev, n, which, static_cast<cudaStream_t>(stream)));
+    return 0;
+}
+
 uint32_t fctc_host_phred(float prob, float qscale, float qbias) {
     static const double invc[16] = FCTC_LOGF_INVC;
     static const double logc[16] = FCTC_LOGF_LOGC;

@@ -221,6 +221,7 @@ struct MovesParams {
 };
 cudaError_t launch_moves(const MovesParams& p, int sm_count, cudaStream_t stream);
 cudaError_t launch_envelope(const EnvelopeParams& p, cudaStream_t stream);
+cudaError_t launch_libm_probe(const float* x, const float* y, float* out, long long n, int which, cudaStream_t stream);
 cudaError_t launch_poison_smem(int sm_count, int byte, unsigned int* sink, cudaStream_t stream);
 cudaError_t launch_synth(float* post, int64_t N, int64_t T, int C, int kind, uint64_t seed, int64_t first_read,
                          cudaStream_t stream);

@@ -1,7 +1,9 @@
 // synth.cu — synthetic posterior generator (bench + tests input).  Not part of the
 // decode path.  Counter-based: every row is a pure function of (seed, read, row), so any shard
 // of any size regenerates the same bytes.
+#include "duplex_common.cuh"
 #include "kernels.h"
+#include "phred.cuh"
 
 namespace fctc {
 
@@ -93,6 +95,39 @@ cudaError_t launch_poison_smem(int sm_count, int byte, unsigned int* sink, cudaS
     if (e != cudaSuccess) return e;
     const unsigned int b = (unsigned int)(byte & 0xff);
     poison_smem_kernel<<<sm_count * 2, 1024, bytes, stream>>>(b * 0x01010101u, bytes, sink);
+    return cudaGetLastError();
+}
+
+
+// Test hook: the DEVICE builds of the libm restatements over an array (which: 0 expf on x <= 0, 1 log1pf on [0, 1],
+// 2 logf, 3 log10f, 4 LogSpace '+' of (x, y) in exact-exp mode), so that the arithmetic the kernels run — fused
+// operations, the branch-free division, the table in shared memory — is compared with the host's libm directly,
+// not only through decode results.
+__global__ void __launch_bounds__(256) libm_probe_kernel(const float* x, const float* y, float* out, long long n, int which) {
+    __shared__ uint64_t xt[32];
+    __shared__ double invc[16], logc[16];
+    static const uint64_t tab[32] = FCTC_EXP2F_TAB;
+    static const double ic[16] = FCTC_LOGF_INVC, lc[16] = FCTC_LOGF_LOGC;
+    if (threadIdx.x < 32) xt[threadIdx.x] = tab[threadIdx.x];
+    if (threadIdx.x < 16) { invc[threadIdx.x] = ic[threadIdx.x]; logc[threadIdx.x] = lc[threadIdx.x]; }
+    __syncthreads();
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const float v = x[i];
+        float r;
+        if (which == 0) r = glibc_expf_nonpos(v, xt);
+        else if (which == 1) r = glibc_log1pf_unit(v);
+        else if (which == 2) r = glibc_logf(v, invc, logc);
+        else if (which == 3) r = glibc_log10f(v, invc, logc);
+        else r = lg_add(v, y[i], 0, xt);
+        out[i] = r;
+    }
+}
+
+cudaError_t launch_libm_probe(const float* x, const float* y, float* out, long long n, int which, cudaStream_t stream) {
+    if (n <= 0) return cudaSuccess;
+    long long blocks = (n + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    libm_probe_kernel<<<(unsigned)blocks, 256, 0, stream>>>(x, y, out, n, which);
     return cudaGetLastError();
 }
 

@@ -126,6 +126,7 @@ _SIGNATURES = {
     "fctc_move_table_device": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _vp, _vp, _vp]),
     "fctc_synth_posteriors_device": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _i32, _u64, _i64, _vp]),
     "fctc_test_poison_shared_memory": (C.c_int, [_vp, _i32]),
+    "fctc_test_libm_device": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i32, _vp]),
     "fctc_host_phred": (C.c_uint32, [_f32, _f32, _f32]),
     "fctc_host_log10f": (None, [_vp, _vp, _i64]),
     "fctc_host_logf": (None, [_vp, _vp, _i64]),
@@ -240,6 +241,10 @@ class Decoder:
         """uint8 move table [n_reads, n_rows] and / or int32 dwells (path layout) from the emission rows."""
         self._check(self._L.fctc_move_table_device(self._h, path_ptr, offsets_ptr, lens_ptr, status_ptr, n_reads, n_rows,
                                                    moves_ptr or None, dwell_ptr or None, stream or None))
+
+    def libm_device(self, x_ptr, y_ptr, out_ptr, n, which, stream=0):
+        """Test hook: the device builds of the libm restatements over an array (fctc_test_libm_device)."""
+        self._check(self._L.fctc_test_libm_device(self._h, x_ptr, y_ptr or None, out_ptr, n, which, stream or None))
 
     def poison_shared_memory(self, byte=0xFF):
         """Test hook: every SM's shared memory is filled with `byte` before the next kernel starts."""

@@ -469,6 +469,12 @@ int fctc_synth_posteriors_device(fctc_handle* h, float* post_dev, int64_t n_read
  * The GPU test-suite runs every test behind it: no kernel may depend on stale shared memory. */
 int fctc_test_poison_shared_memory(fctc_handle* h, int32_t byte);
 
+/* Test hook (replaces nothing): runs the DEVICE builds of the libm restatements over an array — which = 0 expf (x <= 0),
+ * 1 log1pf (0 <= x <= 1), 2 logf, 3 log10f, 4 LogSpace '+' of (x[i], y[i]) in exact-exp mode — so that tests compare the
+ * arithmetic the kernels execute with the host's libm directly.  y_dev may be NULL unless which == 4. */
+int fctc_test_libm_device(fctc_handle* h, const float* x_dev, const float* y_dev, float* out_dev, int64_t n, int32_t which,
+                          void* stream);
+
 /* Host instantiation of the device phred()/log10f code (same source, compiled for the host), so
  * that CPU tests can compare it with glibc without a GPU.  Replaces nothing; test hook. */
 uint32_t fctc_host_phred(float prob, float qscale, float qbias);

@@ -13,18 +13,19 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 OUT = os.path.join(ROOT, "profiles")
 GO = os.path.join(ROOT, "gpurun_out")
-tag = sys.argv[1] if len(sys.argv) > 1 else "r01"
+tag = sys.argv[1] if len(sys.argv) > 1 else "r02"
 
 # report file, profile name, work units of the profiled launch (for per-unit instruction counts), what a unit is
+# the captures of tools/profile_round.sh
 REPORTS = [
-    ("bench_vit_r01b.ncu-rep", "viterbi_stream", 65536 * 4000 / 128, "128-row tile (65,536 reads x 4000 rows, qstring)"),
-    ("beam32_g.ncu-rep", "beam_wide_b32", 3552 * 2000, "posterior row (3,552 reads x 2000 rows, beam 32)"),
-    ("beam5_i.ncu-rep", "beam_small_b5", 18944 * 2000, "posterior row (18,944 reads x 2000 rows, beam 5, threshold 0.1)"),
-    ("duplex_b.ncu-rep", "duplex", 3552 * 1000, "network-1 row (3,552 pairs x 1000 rows, band +-32, beam 5, exact exp)"),
+    ("r02_viterbi.ncu-rep", "viterbi_stream", 65536 * 4000 / 128, "128-row tile (65,536 reads x 4000 rows, qstring)"),
+    ("r02_beam32.ncu-rep", "beam_wide_b32", 3552 * 2000, "posterior row (3,552 reads x 2000 rows, beam 32)"),
+    ("r02_beam5.ncu-rep", "beam_small_b5", 18944 * 2000, "posterior row (18,944 reads x 2000 rows, beam 5, threshold 0.1)"),
+    ("r02_duplex.ncu-rep", "duplex", 9472 * 500, "network-1 row (9,472 pairs x 500 rows, band +-32, beam 5, exact exp; four pairs per warp)"),
 ]
 # profile name -> (bench.py workload, posterior rows of the profiled launch)
 WORKLOAD_OF = {"viterbi_stream": ("viterbi", 65536 * 4000), "beam_wide_b32": ("beam32", 3552 * 2000),
-               "beam_small_b5": ("beam5", 18944 * 2000), "duplex": ("duplex", 3552 * 1000)}
+               "beam_small_b5": ("beam5", 18944 * 2000), "duplex": ("duplex", 9472 * 500)}
 
 
 def run(cmd):
@@ -68,6 +69,6 @@ for rep, name, units, what in REPORTS:
         json.dump(d, open(tj, "w"), indent=1)
         print("traffic per read", traffic / 65536)
 
-launches = os.path.join(GO, "launches_r01.csv")
+launches = os.path.join(GO, f"launches_{tag}.csv")
 if os.path.exists(launches):
     shutil.copy(launches, os.path.join(OUT, f"{tag}_bench_launches.csv"))
