@@ -13,6 +13,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <stdexcept>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -24,8 +25,26 @@ namespace {
 
 int g_exp_mode = 0;  // 0 = exact exp (--no-default-features semantics), 1 = default build (fastexp == 0), 2 = CUDA libm
 
-struct Handle {  // lives as long as its thread; not destroyed at exit (the CUDA runtime may be gone by then)
+// One handle per host thread at a time (src/lib.rs releases the GIL the same way).  A thread that ends hands its handle
+// (streams, pinned staging, device buffers) to a pool from which the next new thread takes it, so that programs
+// which decode from short-lived threads hold as many handles as they ever had threads at once, not one per thread
+// ever started.  Nothing is destroyed at exit (the CUDA runtime may be gone by then); the pool itself is never freed.
+struct HandlePool {
+    std::mutex lock;
+    std::vector<fctc_handle*> idle;
+};
+HandlePool& handle_pool() {
+    static HandlePool* pool = new HandlePool();
+    return *pool;
+}
+struct Handle {
     fctc_handle* h = nullptr;
+    ~Handle() {
+        if (!h) return;
+        HandlePool& pool = handle_pool();
+        std::lock_guard<std::mutex> lk(pool.lock);
+        pool.idle.push_back(h);
+    }
 };
 
 // Rust's Display for f32 prints the shortest decimal that round-trips (src/lib.rs:346-349 formats
@@ -40,8 +59,17 @@ std::string rust_f32(float v) {
 }
 
 fctc_handle* handle() {
-    thread_local Handle th;  // one handle per host thread (src/lib.rs releases the GIL the same way)
+    thread_local Handle th;
     if (!th.h) {
+        {
+            HandlePool& pool = handle_pool();
+            std::lock_guard<std::mutex> lk(pool.lock);
+            if (!pool.idle.empty()) {
+                th.h = pool.idle.back();
+                pool.idle.pop_back();
+                return th.h;
+            }
+        }
         const char* dev = std::getenv("FCTC_DEVICE");
         int rc = fctc_create(dev ? std::atoi(dev) : 0, &th.h);
         if (rc != 0) throw std::runtime_error(std::string("fast_ctc_decode (B200): ") + fctc_last_error(nullptr));

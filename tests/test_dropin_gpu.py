@@ -159,3 +159,31 @@ def test_batched_calls_match_single_calls(fcd):
     assert got == [fcd.beam_search(x, ALPHABET, 5, 0.1) for x in batch]
     got = fcd.beam_search_duplex_batch(batch[:3], batch[3:], ALPHABET)
     assert got == [fcd.beam_search_duplex(x, y, ALPHABET) for x, y in zip(batch[:3], batch[3:])]
+
+
+def test_short_lived_threads_reuse_handles(fcd):
+    """The module keeps one library handle per live thread; a thread that ends returns its handle for the next one.
+    Forty threads in a row must not grow device memory use beyond the first few."""
+    import threading
+
+    import torch
+    rng = np.random.default_rng(10)
+    post = unit_rows(rng, 400)
+    want = fcd.viterbi_search(post, ALPHABET)
+    results = []
+
+    def work():
+        results.append(fcd.viterbi_search(post, ALPHABET) == want and fcd.beam_search(post, ALPHABET) is not None)
+
+    def run(n):
+        for _ in range(n):
+            t = threading.Thread(target=work)
+            t.start()
+            t.join()
+    run(4)
+    torch.cuda.synchronize()
+    free_before = torch.cuda.mem_get_info(0)[0]
+    run(40)
+    torch.cuda.synchronize()
+    assert all(results) and len(results) == 44
+    assert free_before - torch.cuda.mem_get_info(0)[0] < (8 << 20), "threads that ended left their device buffers behind"
