@@ -40,7 +40,7 @@ namespace fctc {
 
 constexpr int BM_WARPS = 4;  // warps (= reads in flight) per CTA
 constexpr int BM_THREADS = BM_WARPS * 32;
-constexpr int BM_ROWBUF = 256;  // floats per prefetch buffer
+constexpr int BM_ROWBUF = 160;  // floats per prefetch buffer (32 rows of five labels; 7 CTAs of 4 warps fit one SM at beam 32)
 constexpr unsigned FULL = 0xffffffffu;
 constexpr int ROOT = -1;
 
@@ -589,7 +589,18 @@ int64_t beam_scratch_bytes(int sm_count, int64_t N, int64_t T, int C, int beam_s
     if (nodes_per_row > bound) nodes_per_row = int(bound > 0 ? bound : 1);
     // The kernel is latency-bound (sequential per read), so throughput follows the number of resident
     // warps: 24 per SM is what registers and shared memory allow.  One trie pool per resident warp.
+    // as many 4-warp CTAs as one SM's shared memory holds (7 at beam 32 with five labels: 28 warps), 32 warps at most
     int per_sm = 24;
+    {
+        BeamLayout L;
+        if (plan_beam(beam_size, C, &L)) {
+            const long long cta = (long long)L.warp_bytes * BM_WARPS + 256 + 1024;  // + static table + the per-CTA reserve
+            long long ctas = (227LL * 1024) / cta;
+            if (ctas > 8) ctas = 8;
+            if (ctas < 1) ctas = 1;
+            per_sm = int(ctas) * BM_WARPS;
+        }
+    }
     static const int per_sm_knob = env_knob("FCTC_BEAM_WARPS_PER_SM");  // tuning knob
     if (per_sm_knob > 0) per_sm = per_sm_knob;
     if (beam_small_eligible(beam_size, C, T)) per_sm = beam_small_warps_per_sm();  // narrow beams: lighter warps
