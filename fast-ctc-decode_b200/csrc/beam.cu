@@ -55,8 +55,8 @@ __host__ __device__ inline size_t beam_slot_bytes(long long cap, int NL) {
 }
 
 struct BeamLayout {  // per-warp shared memory plan, in bytes from the warp's base
-    int beam_stride;  // one beam buffer: 6 arrays of B words
-    int off_newcnt, off_fold, off_key, off_node, off_lp, off_gp, off_src, off_sel, off_srec, off_rows, off_root;
+    int beam_stride;  // one beam buffer: 6 arrays of B words (the crf search's state arrays live at off_st)
+    int off_newcnt, off_fold, off_key, off_node, off_lp, off_gp, off_src, off_sel, off_srec, off_rows, off_root, off_st;
     int warp_bytes;
     int rows_per_chunk;
 };
@@ -70,15 +70,15 @@ struct BeamView {  // one beam buffer
     float* gp;
     int* st;  // crf transition state (src/search.rs:11-12); unused by the plain search
 };
-__device__ __forceinline__ BeamView beam_view(unsigned char* base, int B) {
+__device__ __forceinline__ BeamView beam_view(unsigned char* ws, const BeamLayout& L, int buf, int B) {
     BeamView v;
-    v.nd = reinterpret_cast<int*>(base);
+    v.nd = reinterpret_cast<int*>(ws + buf * L.beam_stride);
     v.par = v.nd + B;
     v.dep = v.par + B;
     v.tip = v.dep + B;
     v.lp = reinterpret_cast<float*>(v.tip + B);
     v.gp = v.lp + B;
-    v.st = reinterpret_cast<int*>(v.gp + B);
+    v.st = reinterpret_cast<int*>(ws + L.off_st) + buf * B;  // only planned (and only touched) by the crf search
     return v;
 }
 
@@ -148,11 +148,11 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
         auto fetch = [&](long long e) -> float { return HALF ? widen16(__ldg(rdh + e), bf16) : __ldg(rd + e); };
 
         int cur = 0;
-        BeamView bv = beam_view(ws, B);
+        BeamView bv = beam_view(ws, L, 0, B);
         int status = FCTC_OK;
         if (lane == 0) {  // src/search.rs:170-175
             bv.nd[0] = ROOT; bv.par[0] = -2; bv.dep[0] = 0; bv.tip[0] = -1; bv.lp[0] = 0.0f; bv.gp[0] = 1.0f;
-            bv.st[0] = 0;
+            if (CRF) bv.st[0] = 0;
             if (CRF) {  // src/search.rs:54-59: label_prob = max(init), gap_prob = init[0], state = argmax(init)
                 const float* init = p.init + n * p.n_init;
                 float best = init[0];
@@ -212,7 +212,7 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
                 const long long t = t0 + rr;
                 const float* pr_shared = rows + rr * C;
                 const float* pr_time = rd + t * S * C;  // crf: [S][C] block of this time step
-                BeamView nb = beam_view(ws + (cur ^ 1) * L.beam_stride, B);
+                BeamView nb = beam_view(ws, L, cur ^ 1, B);
 
                 // The child rows of the beam's nodes are needed in phase B1; with four labels a row is one
                 // 16-byte load, issued here so that its latency hides behind phase A (beams of <= 32).
@@ -263,7 +263,7 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
                     const int s0 = b * C;
                     cnode[s0] = node;
                     clp[s0] = s_lp;
-                    cgp[s0] = s_gp;
+                    cgp[b] = s_gp;  // one per hypothesis: a child candidate's gap probability is always 0 (src/search.rs:213,230)
                     ckey[s0] = has_self ? 1u : 0u;  // real key is filled in after the merge
                 }
                 __syncwarp();
@@ -297,7 +297,6 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
                                 const float v = repeat ? __fmul_rn(gp, pl) : __fmul_rn(__fadd_rn(lp, gp), pl);
                                 cnode[s] = x;
                                 clp[s] = v;
-                                cgp[s] = 0.0f;
                                 key = 1u;
                             }
                         }
@@ -345,7 +344,7 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
                             if (node == ROOT) root_child[l] = id;
                             else child[(size_t)node * NL + l] = id;
                         }
-                        const float tot = __fadd_rn(__fadd_rn(clp[s], cgp[s]), 0.0f);  // probability(), -0 -> +0
+                        const float tot = __fadd_rn(__fadd_rn(clp[s], sl == 0 ? cgp[b] : 0.0f), 0.0f);  // probability(), -0 -> +0
                         if (tot != tot) any_nan = true;
                         ckey[s] = (tot != tot) ? 1u : order_key(tot);
                         ++n_cand;
@@ -486,17 +485,19 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
 
                 // ---- new beam, renormalised by the top score (src/search.rs:278-282) -----------------
                 const int i0 = sel[0];
-                const float top = __fadd_rn(clp[i0], cgp[i0]);
+                const float top = __fadd_rn(clp[i0], (i0 % C == 0) ? cgp[i0 / C] : 0.0f);
                 for (int r = lane; r < n_keep; r += 32) {
                     const int i = sel[r];
                     const int b = i / C, sl = i - b * C;
                     nb.nd[r] = cnode[i];
                     nb.lp[r] = div_keep_zero(clp[i], top);
-                    nb.gp[r] = div_keep_zero(cgp[i], top);
-                    if (sl == 0) { nb.par[r] = bv.par[b]; nb.dep[r] = bv.dep[b]; nb.tip[r] = bv.tip[b]; nb.st[r] = bv.st[b]; }
-                    else {
+                    nb.gp[r] = div_keep_zero(sl == 0 ? cgp[b] : 0.0f, top);
+                    if (sl == 0) {
+                        nb.par[r] = bv.par[b]; nb.dep[r] = bv.dep[b]; nb.tip[r] = bv.tip[b];
+                        if (CRF) nb.st[r] = bv.st[b];
+                    } else {
                         nb.par[r] = bv.nd[b]; nb.dep[r] = bv.dep[b] + 1; nb.tip[r] = sl - 1;
-                        nb.st[r] = CRF ? int(((long long)bv.st[b] * NL) % S) + (sl - 1) : 0;  // src/search.rs:97
+                        if (CRF) nb.st[r] = int(((long long)bv.st[b] * NL) % S) + (sl - 1);  // src/search.rs:97
                     }
                 }
                 bool bad_state = false;
@@ -545,11 +546,11 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
     }
 }
 
-static bool plan_beam(int B, int C, BeamLayout* L) {
+static bool plan_beam(int B, int C, bool crf, BeamLayout* L) {
     const int NL = C - 1;
     auto up = [](long long v, int a) { return (v + a - 1) / a * a; };
     long long o = 0;
-    L->beam_stride = int(up(7LL * 4 * B, 16));
+    L->beam_stride = int(up(6LL * 4 * B, 16));
     o = 2LL * L->beam_stride;
     L->off_newcnt = int(o); o = up(o + 4LL * B, 16);
     L->off_fold = int(o);   o = up(o + (long long)B * (NL > 0 ? NL : 1), 16);
@@ -557,12 +558,13 @@ static bool plan_beam(int B, int C, BeamLayout* L) {
     L->off_key = int(o);    o = up(o + 4 * nc, 16);
     L->off_node = int(o);   o = up(o + 4 * nc, 16);
     L->off_lp = int(o);     o = up(o + 4 * nc, 16);
-    L->off_gp = int(o);     o = up(o + 4 * nc, 16);
+    L->off_gp = int(o);     o = up(o + 4LL * B, 16);  // own continuations only
     L->off_src = int(o);
     L->off_sel = int(o);    o = up(o + 4LL * B, 16);
     L->off_srec = int(o);   o = up(o + 8LL * 32 * (C + 1), 16);
     L->off_rows = int(o);   o = up(o + 2LL * BM_ROWBUF * 4, 16);
     L->off_root = int(o);   o = up(o + 4LL * (NL > 0 ? NL : 1), 16);
+    L->off_st = int(o);     if (crf) o = up(o + 2LL * 4 * B, 16);  // transition states of the two beam buffers
     L->warp_bytes = int(up(o, 128));
     int R = BM_ROWBUF / C;
     if (R > 32) R = 32;
@@ -593,7 +595,7 @@ int64_t beam_scratch_bytes(int sm_count, int64_t N, int64_t T, int C, int beam_s
     int per_sm = 24;
     {
         BeamLayout L;
-        if (plan_beam(beam_size, C, &L)) {
+        if (plan_beam(beam_size, C, false, &L)) {
             const long long cta = (long long)L.warp_bytes * BM_WARPS + 256 + 1024;  // + static table + the per-CTA reserve
             long long ctas = (227LL * 1024) / cta;
             if (ctas > 8) ctas = 8;
@@ -635,7 +637,7 @@ cudaError_t launch_beam(const BeamParams& p, int sm_count, cudaStream_t stream) 
     if (p.N <= 0) return cudaSuccess;
     if (beam_small_eligible(p.beam_size, p.C, p.T)) return launch_beam_small(p, stream);
     BeamLayout L;
-    if (!plan_beam(p.beam_size, p.C, &L)) return cudaErrorInvalidConfiguration;
+    if (!plan_beam(p.beam_size, p.C, p.S > 0, &L)) return cudaErrorInvalidConfiguration;
     const int smem = L.warp_bytes * BM_WARPS;
     const bool crf = p.S > 0;
     if (crf && p.in_f16) return cudaErrorInvalidValue;  // the crf search reads its state-dependent rows directly: f32 only
@@ -655,7 +657,7 @@ cudaError_t launch_beam(const BeamParams& p, int sm_count, cudaStream_t stream) 
 
 bool beam_shape_supported(int beam_size, int C) {
     BeamLayout L;
-    return plan_beam(beam_size, C, &L);
+    return plan_beam(beam_size, C, true, &L);
 }
 
 }  // namespace fctc
