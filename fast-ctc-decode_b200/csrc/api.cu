@@ -785,10 +785,16 @@ int beam_host_pass(fctc_handle* h, const void* post_host, int in_f16, int64_t n_
                    int32_t beam_size, float thr, int32_t collapse, int32_t nodes_per_row, HostOut& out) {
     const int elem_bytes = (in_f16 & 0xf) ? 2 : 4;
     const int64_t slot_entries = std::max<int64_t>(roundup32(n_rows), 32);
-    // The search keeps one read per resident warp busy for the read's whole length, so a chunk must hold
-    // several reads per warp slot (a 64 MiB chunk would leave most of the GPU idle); capped at 2 GiB.
+    // The search keeps one read per resident warp busy for the read's whole length, so a chunk is a whole number of
+    // rounds of the resident warps (a 64 MiB chunk would leave most of the GPU idle), capped at 2 GiB.  How many
+    // rounds: the narrow-beam kernel on float32 rows is about as fast as the link (copy-bound end to end), and small
+    // chunks keep more of the copies under the kernels — one round (beam 5, 65,536 reads: 2.08e9 -> 2.23e9 rows/s);
+    // every other case is kernel-bound and loses time between kernels — three rounds (beam 32: 4.9e8 vs 5.5e8).
     const int64_t read_bytes = std::max<int64_t>(n_rows * int64_t(n_labels) * elem_bytes, 1);
-    int64_t chunk = std::max<int64_t>(default_chunk_reads(read_bytes), int64_t(h->sm_count) * 24 * 4);
+    int round_reads = 0;
+    fctc::beam_scratch_bytes(h->sm_count, n_reads, n_rows, n_labels, beam_size, nodes_per_row, 0, nullptr, &round_reads);
+    const int rounds = (elem_bytes == 4 && fctc::beam_small_eligible(beam_size, n_labels, n_rows)) ? 1 : 3;
+    int64_t chunk = std::max<int64_t>(default_chunk_reads(read_bytes), int64_t(std::max(round_reads, 1)) * rounds);
     chunk = std::min<int64_t>(chunk, std::max<int64_t>((int64_t(2) << 30) / read_bytes, 1));
     static const int chunk_knob = fctc::env_knob("FCTC_BEAM_CHUNK_READS");  // tuning knob
     if (chunk_knob > 0) chunk = chunk_knob;
