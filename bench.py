@@ -435,7 +435,8 @@ def measure_workload(name, w, args, steps, ctx):
     if w["kind"] == "duplex":
         hpost2 = torch.empty((ne, w["T2"], Cn), dtype=torch.float32).pin_memory()
         hpost2.copy_(post2[:ne])
-        henv = band_envelope_np(ne, T, w["T2"], w["band"])
+        henv_t = torch.from_numpy(band_envelope_np(ne, T, w["T2"], w["band"])).pin_memory()  # pinned like the posteriors
+        henv = henv_t.numpy()
         hnp2 = hpost2.numpy()
         outd = None
     else:
