@@ -90,6 +90,13 @@ __device__ __forceinline__ DpSlot dp_slot(unsigned char* base, long long cap, lo
     return s;
 }
 
+// Out-of-line copies for the once-per-row steps (a dozen call sites): inlined everywhere the kernel was 100 KB of code
+// and a quarter of its instruction fetches missed the cache (ncu: sm__icc_request_hit_rate 74 %, "no instruction" the
+// leading stall).  The cell loop of phase B2 keeps its inlined LogSpace '+'.
+template <int MODE>
+__device__ __noinline__ float lga_t(float a, float b, const uint64_t* exp2f_tab) { return lg_add(a, b, MODE, exp2f_tab); }
+__device__ __noinline__ float logf_call(float x, const double* invc, const double* logc) { return glibc_logf(x, invc, logc); }
+
 struct PackedLayout {
     int beam_stride;  // bytes of one beam buffer (8 arrays of B words)
     int off_fold, off_key, off_node, off_lab, off_gap, off_p2, off_sel, off_row, off_root, off_info;
@@ -98,7 +105,10 @@ struct PackedLayout {
     int warp_bytes;
 };
 
+// MODE = exp_mode as a compile-time constant: each instantiation carries one flavour of LogSpace '+' only.
+template <int MODE>
 __global__ void __launch_bounds__(32, DP_MIN_CTAS) duplex_packed_kernel(const DuplexParams p, const PackedLayout L) {
+    auto lga = [](float a, float b, int, const uint64_t* tab) { return lga_t<MODE>(a, b, tab); };
     extern __shared__ __align__(16) unsigned char smem[];
     double* s_invc = reinterpret_cast<double*>(smem);
     double* s_logc = s_invc + 16;
@@ -115,7 +125,7 @@ __global__ void __launch_bounds__(32, DP_MIN_CTAS) duplex_packed_kernel(const Du
     const unsigned gmask = 0xFFu << (g * DP_GROUP);
     const int B = p.beam_size, C = p.C, NL = C - 1;
     const int T1 = p.T1, T2 = p.T2, W = p.W;
-    const int mode = p.exp_mode;
+    constexpr int mode = MODE;
     const bool collapse = p.collapse != 0;
     const bool half_in = p.in_f16 != 0;
     const float NEG = dx_neg_inf();
@@ -143,7 +153,7 @@ __global__ void __launch_bounds__(32, DP_MIN_CTAS) duplex_packed_kernel(const Du
     int* root_child = reinterpret_cast<int*>(gs + L.off_root);
     int* info = reinterpret_cast<int*>(gs + L.off_info);
 
-    const float thr = glibc_logf(p.threshold, s_invc, s_logc);  // src/duplex.rs:454
+    const float thr = logf_call(p.threshold, s_invc, s_logc);  // src/duplex.rs:454
 
     for (;;) {
         // ---- every group that owns a scratch slot draws its own pair ---------------------------------------
@@ -162,11 +172,13 @@ __global__ void __launch_bounds__(32, DP_MIN_CTAS) duplex_packed_kernel(const Du
         const __half* rh2 = reinterpret_cast<const __half*>(p.post2) + n0 * (long long)T2 * C;
         const long long* env = p.env ? p.env + n0 * (long long)T1 * 2 : nullptr;
 
+#pragma unroll 1
         for (int i = bl; i < B * (NL > 0 ? NL : 1); i += DP_GROUP) fold[i] = 0;
         // network 2 in log space (src/duplex.rs:453)
         if (status == FCTC_OK)
+#pragma unroll 1
             for (int i = bl; i < T2 * C; i += DP_GROUP)
-                S.logp2[i] = glibc_logf(half_in ? __half2float(rh2[i]) : rd2[i], s_invc, s_logc);
+                S.logp2[i] = logf_call(half_in ? __half2float(rh2[i]) : rd2[i], s_invc, s_logc);
         // root vector over envelope[(0,1)] rows (src/duplex.rs:476-477, 389-409), and its probability()
         const unsigned long long ub0 = env ? (unsigned long long)env[1] : (unsigned long long)T2;
         if (status == FCTC_OK && ub0 > (unsigned long long)T2) status = FCTC_INVALID_ENVELOPE;  // the reference would panic
@@ -177,6 +189,7 @@ __global__ void __launch_bounds__(32, DP_MIN_CTAS) duplex_packed_kernel(const Du
             if (bl == 0) {
                 float run = 0.0f;
                 S.rootv[0] = run;
+#pragma unroll 1
                 for (int i = 0; i < int(ub0); ++i) {
                     run = __fadd_rn(run, S.logp2[(size_t)i * C]);
                     S.rootv[i + 1] = run;
@@ -185,7 +198,8 @@ __global__ void __launch_bounds__(32, DP_MIN_CTAS) duplex_packed_kernel(const Du
         }
         __syncwarp();
         if (status == FCTC_OK)
-            for (int i = bl; i < root_len; i += DP_GROUP) S.roott[i] = lg_add(NEG, S.rootv[i], mode, XT);
+#pragma unroll 1
+            for (int i = bl; i < root_len; i += DP_GROUP) S.roott[i] = lga(NEG, S.rootv[i], mode, XT);
         int cur = 0;
         {
             DxBeam b0 = dx_beam(gs, B);
@@ -194,6 +208,7 @@ __global__ void __launch_bounds__(32, DP_MIN_CTAS) duplex_packed_kernel(const Du
                 b0.lab[0] = NEG; b0.gap[0] = 0.0f; b0.p2[0] = 0.0f; b0.st[0] = 0;
             }
         }
+#pragma unroll 1
         for (int l = bl; l < NL; l += DP_GROUP) root_child[l] = -1;
         int nbeam = 1;
         int n_nodes = 0;
@@ -218,8 +233,9 @@ __global__ void __launch_bounds__(32, DP_MIN_CTAS) duplex_packed_kernel(const Du
                 ok = status == FCTC_OK;
             }
             if (ok)
+#pragma unroll 1
                 for (int c = bl; c < C; c += DP_GROUP)
-                    lp1[c] = glibc_logf(half_in ? __half2float(rh1[(size_t)t * C + c]) : rd1[(size_t)t * C + c], s_invc, s_logc);
+                    lp1[c] = logf_call(half_in ? __half2float(rh1[(size_t)t * C + c]) : rd1[(size_t)t * C + c], s_invc, s_logc);
 
             // ---- extend the vectors of the beam's nodes (src/duplex.rs:490-522) ----------------------------
             const bool ext = ok && hi > last_hi;
@@ -229,6 +245,7 @@ __global__ void __launch_bounds__(32, DP_MIN_CTAS) duplex_packed_kernel(const Du
                 if (bl < nbeam) {
                     const int me = bv.nd[bl];
                     int r = 0;
+#pragma unroll 1
                     for (int k = 0; k < nbeam; ++k) r += (bv.nd[k] < me) ? 1 : 0;
                     nb.nd[r] = me; nb.par[r] = bv.par[bl]; nb.tip[r] = bv.tip[bl]; nb.dep[r] = bv.dep[bl];
                     nb.lab[r] = bv.lab[bl]; nb.gap[r] = bv.gap[bl]; nb.p2[r] = bv.p2[bl]; nb.st[r] = 0;
@@ -267,6 +284,7 @@ __global__ void __launch_bounds__(32, DP_MIN_CTAS) duplex_packed_kernel(const Du
                         bool rescan = (old_lo > b0) || (e0 <= b0);
                         if (!rescan) {
                             int sl = dx_mod(old_lo, W);
+#pragma unroll 1
                             for (int i = old_lo; i < b0; ++i) {
                                 if (vd[sl].y >= mx) rescan = true;
                                 if (++sl == W) sl = 0;
@@ -275,6 +293,7 @@ __global__ void __launch_bounds__(32, DP_MIN_CTAS) duplex_packed_kernel(const Du
                         if (rescan) {
                             mx = NEG;
                             int sl = dx_mod(b0, W);
+#pragma unroll 1
                             for (int i = b0; i < e0; ++i) {
                                 mx = lg_max(mx, vd[sl].y);
                                 if (++sl == W) sl = 0;
@@ -292,6 +311,7 @@ __global__ void __launch_bounds__(32, DP_MIN_CTAS) duplex_packed_kernel(const Du
                     const int plab = (my_par >= 0) ? int(S.nlab[my_par]) : -1;
                     repeat = (plab == my_lab);
                     bool par_in_beam = false;
+#pragma unroll 1
                     for (int k = 0; k < nbeam; ++k) par_in_beam |= (bv.nd[k] == my_par);
                     par_end = (my_par >= 0) ? (par_in_beam ? hi : S.vend[my_par]) : 0;
                 }
@@ -302,6 +322,7 @@ __global__ void __launch_bounds__(32, DP_MIN_CTAS) duplex_packed_kernel(const Du
                 if (ext) imin = __reduce_min_sync(gmask, active ? v_end : hi);
                 const int steps = __reduce_max_sync(DXFULL, ext ? hi - imin : 0);
                 int sl_w = dx_mod(imin, W), sl_p = dx_mod(imin - 1, W);
+#pragma unroll 1
                 for (int k = 0; k < steps; ++k) {  // lockstep over the network-2 row index
                     const int i = imin + k;
                     if (active && i < hi && v_end <= i) {
@@ -316,8 +337,8 @@ __global__ void __launch_bounds__(32, DP_MIN_CTAS) duplex_packed_kernel(const Du
                         }
                         DxCell c;
                         c.gap = __fadd_rn(last.total, S.logp2[(size_t)i * C]);
-                        c.label = __fadd_rn(S.logp2[(size_t)i * C + my_lab + 1], lg_add(last.label, repeat ? pgap : ptot, mode, XT));
-                        c.total = lg_add(c.label, c.gap, mode, XT);
+                        c.label = __fadd_rn(S.logp2[(size_t)i * C + my_lab + 1], lga(last.label, repeat ? pgap : ptot, mode, XT));
+                        c.total = lga(c.label, c.gap, mode, XT);
                         vd[sl_w] = make_float2(c.gap, c.total);
                         mx = lg_max(mx, c.total);
                         last = c;
@@ -345,7 +366,7 @@ __global__ void __launch_bounds__(32, DP_MIN_CTAS) duplex_packed_kernel(const Du
                 bool has_self = false;
                 float s_lab = NEG, s_gap = NEG;
                 if (p_blank > thr) {  // src/duplex.rs:529-534
-                    s_gap = __fadd_rn(lg_add(lab, gap, mode, XT), p_blank);
+                    s_gap = __fadd_rn(lga(lab, gap, mode, XT), p_blank);
                     has_self = true;
                 }
                 if (collapse && tip >= 0) {  // :540-544
@@ -358,6 +379,7 @@ __global__ void __launch_bounds__(32, DP_MIN_CTAS) duplex_packed_kernel(const Du
                 if (has_self && node != DXROOT) {
                     const int mypar = bv.par[b];
                     int r = -1;
+#pragma unroll 1
                     for (int k = 0; k < nbeam; ++k)
                         if (bv.nd[k] == mypar) r = k;
                     if (r >= 0) {
@@ -365,8 +387,8 @@ __global__ void __launch_bounds__(32, DP_MIN_CTAS) duplex_packed_kernel(const Du
                         if (!(pt < thr)) {
                             float c;
                             if (collapse && bv.tip[r] == tip) c = __fadd_rn(bv.gap[r], pt);      // :563-568
-                            else c = __fadd_rn(lg_add(bv.lab[r], bv.gap[r], mode, XT), pt);       // :586-590
-                            s_lab = lg_add(s_lab, c, mode, XT);                                   // :604
+                            else c = __fadd_rn(lga(bv.lab[r], bv.gap[r], mode, XT), pt);       // :586-590
+                            s_lab = lga(s_lab, c, mode, XT);                                   // :604
                             fold[r * NL + tip] = 1;
                         }
                     }
@@ -387,6 +409,7 @@ __global__ void __launch_bounds__(32, DP_MIN_CTAS) duplex_packed_kernel(const Du
                 const int node = bv.nd[b];
                 const float lab = bv.lab[b], gap = bv.gap[b];
                 const int tip = bv.tip[b];
+#pragma unroll 1
                 for (int l = 0; l < NL; ++l) {
                     const int s = b * C + 1 + l;
                     const float pl = lp1[l + 1];
@@ -404,7 +427,7 @@ __global__ void __launch_bounds__(32, DP_MIN_CTAS) duplex_packed_kernel(const Du
                         }
                         if (take) {
                             cnode[s] = x;
-                            clab[s] = repeat ? __fadd_rn(gap, pl) : __fadd_rn(lg_add(lab, gap, mode, XT), pl);
+                            clab[s] = repeat ? __fadd_rn(gap, pl) : __fadd_rn(lga(lab, gap, mode, XT), pl);
                             cgap[s] = NEG;
                             cp2[s] = bv.p2[b];
                             key = 1u;
@@ -430,6 +453,7 @@ __global__ void __launch_bounds__(32, DP_MIN_CTAS) duplex_packed_kernel(const Du
             const int dmin = __reduce_min_sync(gmask, (ok && bl < nbeam) ? bv.dep[bl] : 0x7fffffff);
             bool ring_busy = false;
             if (ok && bl < nbeam)
+#pragma unroll 1
                 for (int k = 0; k < n_new; ++k) {
                     const int id = n_nodes + my_base + k;
                     if (id > ring_mask && S.rdepth[id & ring_mask] >= dmin - 1) ring_busy = true;
@@ -446,6 +470,7 @@ __global__ void __launch_bounds__(32, DP_MIN_CTAS) duplex_packed_kernel(const Du
             const int n_jobs = c0 + c1 + c2 + c3;
             if (ok && bl < nbeam) {
                 int k = 0;
+#pragma unroll 1
                 for (int l = 0; l < NL; ++l) {
                     const int s = bl * C + 1 + l;
                     if (ckey[s] != 0u && cnode[s] <= -2) {
@@ -537,6 +562,7 @@ __global__ void __launch_bounds__(32, DP_MIN_CTAS) duplex_packed_kernel(const Du
                         JS.voff[id] = jlo;
                         JS.vlo[id] = jlo;
                         JS.vlast[id] = label_prev;
+#pragma unroll 1
                         for (int q = 0; q < NL; ++q) JS.child[(size_t)id * NL + q] = -1;
                         if (pnode == DXROOT) reinterpret_cast<int*>(js + L.off_root)[jl] = id;
                         else JS.child[(size_t)pnode * NL + jl] = id;
@@ -553,12 +579,13 @@ __global__ void __launch_bounds__(32, DP_MIN_CTAS) duplex_packed_kernel(const Du
             bool any_nan = false;
             int n_cand = 0;
             if (ok && bl < nbeam) {
+#pragma unroll 1
                 for (int sl = 0; sl < C; ++sl) {
                     const int s = bl * C + sl;
                     if (ckey[s] == 0u) continue;
                     const int node = cnode[s];
                     if (node >= 0) cp2[s] = S.vmx[node];
-                    const float tot = __fadd_rn(__fadd_rn(lg_add(clab[s], cgap[s], mode, XT), cp2[s]), 0.0f);
+                    const float tot = __fadd_rn(__fadd_rn(lga(clab[s], cgap[s], mode, XT), cp2[s]), 0.0f);
                     if (tot != tot) any_nan = true;
                     ckey[s] = (tot != tot) ? 1u : order_key(tot);
                     ++n_cand;
@@ -581,6 +608,7 @@ __global__ void __launch_bounds__(32, DP_MIN_CTAS) duplex_packed_kernel(const Du
             int best_i = -1;
             auto rescan = [&]() {
                 best_hi = 0; best_lo = 0; best_i = -1;
+#pragma unroll 1
                 for (int i = bl; i < n_slots_c; i += DP_GROUP) {
                     const uint32_t k = ckey[i];
                     if (k == 0u) continue;
@@ -589,6 +617,7 @@ __global__ void __launch_bounds__(32, DP_MIN_CTAS) duplex_packed_kernel(const Du
                 }
             };
             if (ok) rescan();
+#pragma unroll 1
             for (int r = 0; r < rounds; ++r) {
                 if (r < n_keep) {
                     const uint32_t m1 = __reduce_max_sync(gmask, best_hi);
@@ -635,6 +664,7 @@ __global__ void __launch_bounds__(32, DP_MIN_CTAS) duplex_packed_kernel(const Du
                 } else {
                     off = (long long)o;
                     int node = bv.nd[0];
+#pragma unroll 1
                     for (int k = len - 1; k >= 0; --k) {
                         p.labels[off + k] = uint8_t(S.nlab[node] + 1);
                         node = S.parent[node];
@@ -707,14 +737,15 @@ cudaError_t launch_duplex_packed(const DuplexParams& p, cudaStream_t stream) {
     PackedLayout L;
     if (!plan_packed(p.beam_size, p.C, &L)) return cudaErrorInvalidConfiguration;
     const int smem = DP_FIXED + L.warp_bytes;
-    cudaError_t e = cudaFuncSetAttribute(duplex_packed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    auto kernel = p.exp_mode == 0 ? duplex_packed_kernel<0> : p.exp_mode == 1 ? duplex_packed_kernel<1> : duplex_packed_kernel<2>;
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
     e = cudaMemsetAsync(p.ticket, 0, sizeof(unsigned long long), stream);
     if (e != cudaSuccess) return e;
     e = cudaMemsetAsync(p.cursor, 0, sizeof(unsigned long long), stream);  // the pool fills from entry 0 on every call
     if (e != cudaSuccess) return e;
     const int grid = (p.n_slots + DP_PAIRS - 1) / DP_PAIRS;
-    duplex_packed_kernel<<<grid, 32, smem, stream>>>(p, L);
+    kernel<<<grid, 32, smem, stream>>>(p, L);
     return cudaGetLastError();
 }
 

@@ -53,6 +53,6 @@ for n in sorted(counts, key=lambda k: -total[k]):
         continue
     reg, sh = usage.get(n, (0, 0))
     d = demangle(n)
-    d = re.sub(r"\(.*$", "", d)
+    d = re.sub(r"\((?!anonymous namespace).*$", "", d)
     print(f"\n{d}\n  instructions {total[n]}, registers {reg}, static shared {sh} B")
     print("  " + ", ".join(f"{w} {counts[n][w]}" for w in WATCH if counts[n][w]))
