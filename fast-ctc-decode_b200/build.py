@@ -10,11 +10,12 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-OUT = os.path.join(HERE, "libfctc_b200.so")
+OUT = os.environ.get("FCTC_BUILD_OUT") or os.path.join(HERE, "libfctc_b200.so")  # (a second library for A/B runs)
 SOURCES = ["api.cu", "viterbi.cu", "beam.cu", "beam_small.cu", "duplex.cu", "duplex_packed.cu", "crf.cu", "fastq.cu", "align.cu", "pack.cu", "multi.cu", "synth.cu"]
 HEADERS = ["kernels.h", "device_utils.cuh", "phred.cuh", "duplex_common.cuh", os.path.join("..", "..", "include", "fctc.h")]
 
-NVCC_FLAGS = [
+EXTRA = os.environ.get("FCTC_NVCC_EXTRA", "").split()  # e.g. -DDP_CTAS_EXACT=20 (development)
+NVCC_FLAGS = EXTRA + [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-std=c++17", "-lineinfo",
     # bit-exact parity with the reference's f32 arithmetic: no FMA contraction, IEEE div/sqrt,
@@ -23,7 +24,7 @@ NVCC_FLAGS = [
     "-Xcompiler", "-fPIC,-ffp-contract=off,-fno-fast-math",
 ]
 LINK_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-cudart", "static"]
-OBJ_DIR = os.path.join(HERE, "build")
+OBJ_DIR = os.path.join(HERE, "build" + ("_" + os.path.basename(OUT).replace(".so", "") if os.environ.get("FCTC_BUILD_OUT") else ""))
 
 
 def needs_build():

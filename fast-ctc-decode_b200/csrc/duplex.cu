@@ -624,7 +624,7 @@ int64_t duplex_scratch_bytes(int sm_count, int64_t N, int T1, int T2, int C, int
     if (n_rings) *n_rings = rings;
     const long long per_slot = packed ? (long long)duplex_packed_slot_bytes(cap, rings, T2, C, W)
                                       : (long long)dx_slot_bytes(cap, T2, C, W);
-    int per_sm = packed ? duplex_packed_slots_per_sm() : 24;  // latency-bound, sequential per pair: throughput follows the resident warps
+    int per_sm = packed ? duplex_packed_slots_per_sm(-1) : 24;  // latency-bound, sequential per pair: throughput follows the resident warps
     static const int per_sm_knob = env_knob("FCTC_DUPLEX_WARPS_PER_SM");  // tuning knob
     if (per_sm_knob > 0) per_sm = per_sm_knob;
     long long slots = (long long)sm_count * per_sm;
@@ -639,7 +639,7 @@ int64_t duplex_scratch_bytes(int sm_count, int64_t N, int T1, int T2, int C, int
     }
     // every pair of a batch takes about the same time, so the pairs run in rounds of `slots`: even the rounds out
     // (16,384 pairs over 9,472 slots would run 9,472 + 6,912; two rounds of 8,192 keep every warp as busy)
-    if (N > slots) {
+    if (N > slots && !packed) {
         const long long rounds = (N + slots - 1) / slots;
         long long even = (N + rounds - 1) / rounds;
         even = (even + DX_WARPS - 1) / DX_WARPS * DX_WARPS;
@@ -872,7 +872,7 @@ static int dx_batch_host_any(fctc_handle* h, const void* post1_any, const void* 
     // a chunk is a whole number of rounds of the pairs in flight (a partial round costs a full one), as many as 2 GiB
     // of posteriors hold, at least one
     const int64_t in_flight = int64_t(fctc::handle_sm_count(h)) *
-                              (fctc::duplex_packed_shape(beam_size, n_labels, 0) ? fctc::duplex_packed_slots_per_sm() : 24);
+                              (fctc::duplex_packed_shape(beam_size, n_labels, 0) ? fctc::duplex_packed_slots_per_sm(exp_mode) : 24);
     int64_t chunk = std::max<int64_t>((int64_t(2) << 30) / std::max<int64_t>(pair_bytes, 1), 1);
     if (chunk > in_flight) chunk = chunk / in_flight * in_flight;
     chunk = std::max<int64_t>(1, std::min<int64_t>(chunk, n_pairs));

@@ -44,9 +44,15 @@ constexpr int DP_GROUP = 8;   // lanes per pair
 constexpr int DP_PAIRS = 4;   // pairs per warp
 constexpr int DP_SLOTS = 16;  // node-build jobs per pass (two lanes each)
 constexpr int DP_FIXED = 512; // logf tables (2 x 16 doubles) + expf table (32 x 8 bytes)
-#ifndef DP_MIN_CTAS
-#define DP_MIN_CTAS 16        // one-warp CTAs per SM the register allocation aims at (16 -> at most 128 registers)
+// One-warp CTAs per SM the register allocation aims at, by flavour of LogSpace '+' (measured, 1000-row pairs): the exact
+// flavour runs best with 128 registers and 16 CTAs, the cheap ones (max-plus, CUDA libm) with more, lighter CTAs.
+#ifndef DP_CTAS_EXACT
+#define DP_CTAS_EXACT 16
 #endif
+#ifndef DP_CTAS_OTHER
+#define DP_CTAS_OTHER 24
+#endif
+constexpr int dp_min_ctas(int mode) { return mode == 0 ? DP_CTAS_EXACT : DP_CTAS_OTHER; }
 
 // Scratch of one pair (all sections 256-byte aligned).
 struct DpSlot {
@@ -107,7 +113,7 @@ struct PackedLayout {
 
 // MODE = exp_mode as a compile-time constant: each instantiation carries one flavour of LogSpace '+' only.
 template <int MODE>
-__global__ void __launch_bounds__(32, DP_MIN_CTAS) duplex_packed_kernel(const DuplexParams p, const PackedLayout L) {
+__global__ void __launch_bounds__(32, dp_min_ctas(MODE)) duplex_packed_kernel(const DuplexParams p, const PackedLayout L) {
     auto lga = [](float a, float b, int, const uint64_t* tab) { return lga_t<MODE>(a, b, tab); };
     extern __shared__ __align__(16) unsigned char smem[];
     double* s_invc = reinterpret_cast<double*>(smem);
@@ -727,7 +733,10 @@ int64_t duplex_packed_slot_bytes(int64_t cap, int64_t rings, int T2, int C, int 
     return int64_t(dp_slot_bytes(cap, rings, T2, C, W));
 }
 
-int duplex_packed_slots_per_sm() { return 4 * DP_MIN_CTAS; }  // DP_MIN_CTAS warps of four pairs
+int duplex_packed_slots_per_sm(int exp_mode) {  // resident warps of four pairs
+    if (exp_mode < 0) return DP_PAIRS * (DP_CTAS_EXACT > DP_CTAS_OTHER ? DP_CTAS_EXACT : DP_CTAS_OTHER);
+    return DP_PAIRS * dp_min_ctas(exp_mode);
+}
 
 bool duplex_packed_eligible(const DuplexParams& p) {
     return duplex_packed_shape(p.beam_size, p.C, p.S > 0);
@@ -744,8 +753,24 @@ cudaError_t launch_duplex_packed(const DuplexParams& p, cudaStream_t stream) {
     if (e != cudaSuccess) return e;
     e = cudaMemsetAsync(p.cursor, 0, sizeof(unsigned long long), stream);  // the pool fills from entry 0 on every call
     if (e != cudaSuccess) return e;
-    const int grid = (p.n_slots + DP_PAIRS - 1) / DP_PAIRS;
-    kernel<<<grid, 32, smem, stream>>>(p, L);
+    // pairs in flight: what the scratch holds, at most what this flavour keeps resident, in even rounds (every pair
+    // of a batch takes about the same time: 16,384 pairs over 9,472 slots run as two rounds of 8,192)
+    int dev = 0, sms = 0;
+    if ((e = cudaGetDevice(&dev)) != cudaSuccess) return e;
+    if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
+    long long slots = p.n_slots;
+    const long long resident = (long long)sms * duplex_packed_slots_per_sm(p.exp_mode);
+    if (slots > resident) slots = resident;
+    if (p.N > slots) {
+        const long long rounds = (p.N + slots - 1) / slots;
+        long long even = (p.N + rounds - 1) / rounds;
+        even = (even + DP_PAIRS - 1) / DP_PAIRS * DP_PAIRS;
+        if (even < slots) slots = even;
+    }
+    DuplexParams q = p;
+    q.n_slots = int(slots);
+    const int grid = int((slots + DP_PAIRS - 1) / DP_PAIRS);
+    kernel<<<grid, 32, smem, stream>>>(q, L);
     return cudaGetLastError();
 }
 

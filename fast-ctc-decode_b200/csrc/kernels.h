@@ -153,7 +153,7 @@ bool duplex_packed_eligible(const DuplexParams& p);
 bool duplex_packed_shape(int beam_size, int C, int crf);
 int64_t duplex_packed_rings(int64_t cap, int nodes_per_row, int64_t bound);
 int64_t duplex_packed_slot_bytes(int64_t cap, int64_t rings, int T2, int C, int W);
-int duplex_packed_slots_per_sm();
+int duplex_packed_slots_per_sm(int exp_mode);  // exp_mode < 0: the largest over the modes (scratch planning)
 cudaError_t launch_duplex_packed(const DuplexParams& p, cudaStream_t stream);
 
 // FASTQ record assembly from the Viterbi slot form (fastq.cu)
