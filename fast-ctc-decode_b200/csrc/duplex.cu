@@ -80,6 +80,7 @@ __device__ __forceinline__ DxCell dx_step(const DxCell& last, float pgap, float 
 #ifndef DX_MINBLOCKS
 #define DX_MINBLOCKS 6
 #endif
+// (Loops that run once per row are kept rolled: unrolled, the kernel outgrew the instruction cache; see duplex_packed.cu.)
 template <bool CRF>
 __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel(const DuplexParams p, const DuplexLayout L) {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -120,6 +121,7 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
                              cap, T2, C, W);
     const float thr = glibc_logf(p.threshold, s_invc, s_logc);  // src/duplex.rs:454
 
+#pragma unroll 1
     for (int i = lane; i < B * (NL > 0 ? NL : 1); i += 32) fold[i] = 0;
 
     for (;;) {
@@ -144,18 +146,21 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
 
         // network 2 in log space (src/duplex.rs:453)
         if (!CRF)
+#pragma unroll 1
             for (int i = lane; i < T2 * C; i += 32)
                 S.logp2[i] = glibc_logf(half_in ? __half2float(rh2[i]) : rd2[i], s_invc, s_logc);
         int init_state_1 = 0, init_state_2 = 0;
         if (CRF) {  // argmax of the initial state scores (src/duplex.rs:679, 691); NaN aborts the reference
             bool bad = false;
             if (lane == 0) {
+#pragma unroll 1
                 for (int which = 0; which < 2; ++which) {
                     const float* init = which ? p.init2 + n * p.n_init2 : p.init1 + n * p.n_init1;
                     const int ni = which ? p.n_init2 : p.n_init1;
                     float best = init[0];
                     int arg = 0;
                     bad = bad || (best != best);
+#pragma unroll 1
                     for (int i = 1; i < ni; ++i) {
                         const float v = init[i];
                         bad = bad || (v != v);
@@ -180,6 +185,7 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
                 float cur = 0.0f;
                 S.rootv[0] = cur;
                 int rs = init_state_2;  // crf_root_probs walks the blank transitions (src/duplex.rs:430-438)
+#pragma unroll 1
                 for (int i = 0; i < int(ub0); ++i) {
                     cur = __fadd_rn(cur, lp2(i, rs, 0));
                     S.rootv[i + 1] = cur;
@@ -194,6 +200,7 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
             bv.lab[0] = NEG; bv.gap[0] = 0.0f; bv.p2[0] = 0.0f;
             bv.st[0] = init_state_1;
         }
+#pragma unroll 1
         for (int l = lane; l < NL; l += 32) root_child[l] = -1;
         int nbeam = 1;
         long long n_nodes = 0;
@@ -215,6 +222,7 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
                 break;
             }
             if (!CRF)
+#pragma unroll 1
                 for (int c = lane; c < C; c += 32)
                     lp1[c] = glibc_logf(half_in ? __half2float(rh1[(size_t)t * C + c]) : rd1[(size_t)t * C + c], s_invc, s_logc);
             // network-1 value of this row for a hypothesis in state s_, column c
@@ -230,6 +238,7 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
                 if (lane < nbeam) {
                     const int me = bv.nd[lane];
                     int r = 0;
+#pragma unroll 1
                     for (int k = 0; k < nbeam; ++k) r += (bv.nd[k] < me) ? 1 : 0;
                     nb.nd[r] = me; nb.par[r] = bv.par[lane]; nb.tip[r] = bv.tip[lane]; nb.dep[r] = bv.dep[lane];
                     nb.lab[r] = bv.lab[lane]; nb.gap[r] = bv.gap[lane]; nb.p2[r] = bv.p2[lane];
@@ -270,6 +279,7 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
                         bool rescan = (old_lo > b0) || (e0 <= b0);
                         if (!rescan) {
                             int sl = dx_mod(old_lo, W);
+#pragma unroll 1
                             for (int i = old_lo; i < b0; ++i) {
                                 if (vd[W + sl] >= mx) rescan = true;
                                 if (++sl == W) sl = 0;
@@ -278,6 +288,7 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
                         if (rescan) {
                             mx = NEG;
                             int sl = dx_mod(b0, W);
+#pragma unroll 1
                             for (int i = b0; i < e0; ++i) {
                                 mx = lg_max(mx, vd[W + sl]);
                                 if (++sl == W) sl = 0;
@@ -294,6 +305,7 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
                     const int plab = (my_par >= 0) ? int(S.nlab[my_par]) : -1;
                     repeat = !CRF && (plab == my_lab);
                     bool par_in_beam = false;
+#pragma unroll 1
                     for (int k = 0; k < nbeam; ++k) par_in_beam |= (bv.nd[k] == my_par);
                     par_end = (my_par >= 0) ? ((par_in_beam) ? hi : S.vend[my_par]) : 0;
                 }
@@ -307,6 +319,7 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
                     imin = o < imin ? o : imin;
                 }
                 int sl_w = dx_mod(imin, W), sl_p = dx_mod(imin - 1, W);
+#pragma unroll 1
                 for (int i = imin; i < hi; ++i) {  // lockstep over the network-2 row index
                     if (active && v_end <= i) {
                         float pgap, ptot;
@@ -357,6 +370,7 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
                 if (has_self && node != DXROOT) {
                     const int mypar = bv.par[b];
                     int r = -1;
+#pragma unroll 1
                     for (int k = 0; k < nbeam; ++k)
                         if (bv.nd[k] == mypar) r = k;
                     if (r >= 0) {
@@ -386,6 +400,7 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
                 const int node = bv.nd[b];
                 const float lab = bv.lab[b], gap = bv.gap[b];
                 const int tip = bv.tip[b];
+#pragma unroll 1
                 for (int l = 0; l < NL; ++l) {
                     const int s = b * C + 1 + l;
                     const float pl = row1(bv.st[b], l + 1);
@@ -422,6 +437,7 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
             // list the new nodes in creation order (beam rank major, label minor)
             if (lane < nbeam) {
                 int k = 0;
+#pragma unroll 1
                 for (int l = 0; l < NL; ++l) {
                     const int s = lane * C + 1 + l;
                     if (ckey[s] != 0u && cnode[s] <= -2) {
@@ -434,6 +450,7 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
             __syncwarp();
 
             // ---- phase B2: build the new nodes' vectors, one lane per node (src/duplex.rs:212-249) ----
+#pragma unroll 1
             for (int j0 = 0; j0 < total_new; j0 += 32) {
                 const int j = j0 + lane;
                 if (j < total_new) {
@@ -466,6 +483,7 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
                     S.vlast[id] = last.label;
                     S.vend[id] = hi;
                     S.vmx[id] = mx;
+#pragma unroll 1
                     for (int q = 0; q < NL; ++q) S.child[(size_t)id * NL + q] = -1;
                     if (pnode == DXROOT) root_child[l] = id;
                     else S.child[(size_t)pnode * NL + l] = id;
@@ -478,6 +496,7 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
             bool any_nan = false;
             int n_cand = 0;
             if (lane < nbeam) {
+#pragma unroll 1
                 for (int sl = 0; sl < C; ++sl) {
                     const int s = lane * C + sl;
                     if (ckey[s] == 0u) continue;
@@ -502,6 +521,7 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
             int best_i = -1;
             auto rescan = [&]() {
                 best_hi = 0; best_lo = 0; best_i = -1;
+#pragma unroll 1
                 for (int i = lane; i < n_slots_c; i += 32) {
                     const uint32_t k = ckey[i];
                     if (k == 0u) continue;
@@ -510,6 +530,7 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
                 }
             };
             rescan();
+#pragma unroll 1
             for (int r = 0; r < n_keep; ++r) {
                 const uint32_t m1 = __reduce_max_sync(DXFULL, best_hi);
                 const uint32_t m2 = __reduce_max_sync(DXFULL, best_hi == m1 ? best_lo : 0u);
@@ -543,6 +564,7 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
             nbeam = n_keep;
         }
         if (status != FCTC_OK)
+#pragma unroll 1
             for (int i = lane; i < B * (NL > 0 ? NL : 1); i += 32) fold[i] = 0;
         __syncwarp();
 
@@ -560,6 +582,7 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
                 } else {
                     off = (long long)o;
                     int node = bv.nd[0];
+#pragma unroll 1
                     for (int k = len - 1; k >= 0; --k) {
                         p.labels[off + k] = uint8_t(S.nlab[node] + 1);
                         node = S.parent[node];
