@@ -24,6 +24,8 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
+#include <vector>
 
 #include <cuda_fp16.h>
 
@@ -908,15 +910,39 @@ static int dx_batch_host_any(fctc_handle* h, const void* post1_any, const void* 
                                    pool_capacity, offsets + first, lens + first, status + first, &used))
             return rc;
     }
-    // pairs whose trie outgrew the default pool: again, one at a time, at the hard bound
+    // pairs whose trie (or ring pool) outgrew the default plan: gathered and decoded again in one pass per group of at
+    // most 256 MiB of posteriors, at the hard bound (one ring per node: cannot overflow)
     const int32_t bound = std::max<int32_t>(1, (n_labels - 1) * beam_size);
-    for (int64_t n = 0; n < n_pairs; ++n) {
-        if (status[n] != FCTC_NODE_POOL_OVERFLOW) continue;
-        if (int rc = dx_host_chunk(h, post1_host + n * n_rows_1 * n_labels * eb, post2_host + n * n_rows_2 * n_labels * eb,
-                                   in_f16, envelope_host ? envelope_host + n * n_rows_1 * 2 : nullptr, 1, n_rows_1, n_rows_2, n_labels, W,
-                                   beam_size, beam_cut_threshold, collapse_repeats, exp_mode, bound, labels, pool_capacity,
-                                   offsets + n, lens + n, status + n, &used))
-            return rc;
+    std::vector<int64_t> again;
+    for (int64_t n = 0; n < n_pairs; ++n)
+        if (status[n] == FCTC_NODE_POOL_OVERFLOW) again.push_back(n);
+    if (!again.empty()) {
+        const int64_t b1 = n_rows_1 * int64_t(n_labels) * eb, b2 = n_rows_2 * int64_t(n_labels) * eb, be = n_rows_1 * 16;
+        const int64_t group = std::max<int64_t>(1, (int64_t(256) << 20) / std::max<int64_t>(b1 + b2, 1));
+        std::vector<unsigned char> g1, g2;
+        std::vector<int64_t> ge, off2;
+        std::vector<int32_t> len2, st2;
+        for (size_t g0 = 0; g0 < again.size(); g0 += size_t(group)) {
+            const int64_t k = std::min<int64_t>(group, int64_t(again.size() - g0));
+            g1.resize(size_t(std::max<int64_t>(k * b1, 16)));
+            g2.resize(size_t(std::max<int64_t>(k * b2, 16)));
+            if (envelope_host) ge.resize(size_t(k * n_rows_1 * 2));
+            for (int64_t i = 0; i < k; ++i) {
+                const int64_t n = again[g0 + size_t(i)];
+                memcpy(g1.data() + i * b1, post1_host + n * b1, size_t(b1));
+                if (b2) memcpy(g2.data() + i * b2, post2_host + n * b2, size_t(b2));
+                if (envelope_host) memcpy(ge.data() + i * n_rows_1 * 2, envelope_host + n * n_rows_1 * 2, size_t(be));
+            }
+            off2.assign(size_t(k), 0); len2.assign(size_t(k), 0); st2.assign(size_t(k), 0);
+            if (int rc = dx_host_chunk(h, g1.data(), g2.data(), in_f16, envelope_host ? ge.data() : nullptr, k, n_rows_1, n_rows_2,
+                                       n_labels, W, beam_size, beam_cut_threshold, collapse_repeats, exp_mode, bound, labels,
+                                       pool_capacity, off2.data(), len2.data(), st2.data(), &used))
+                return rc;
+            for (int64_t i = 0; i < k; ++i) {
+                const int64_t n = again[g0 + size_t(i)];
+                offsets[n] = off2[size_t(i)]; lens[n] = len2[size_t(i)]; status[n] = st2[size_t(i)];
+            }
+        }
     }
     if (pool_used) *pool_used = used;
     return 0;
