@@ -25,6 +25,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <thread>
 #include <vector>
 
 #include <cuda_fp16.h>
@@ -885,11 +886,29 @@ static int dx_batch_host_any(fctc_handle* h, const void* post1_any, const void* 
     // kernel clamps), or all of network 2 without an envelope
     int64_t wmax = n_rows_2;
     if (envelope_host) {
-        wmax = 1;
-        for (int64_t i = 0; i < n_pairs * n_rows_1; ++i) {
-            const uint64_t lo = uint64_t(envelope_host[2 * i]), hi_u = uint64_t(envelope_host[2 * i + 1]);
-            const int64_t hi = hi_u > uint64_t(n_rows_2) ? n_rows_2 : int64_t(hi_u);
-            if (lo < uint64_t(hi) && hi - int64_t(lo) > wmax) wmax = hi - int64_t(lo);
+        // (16 bytes per network-1 row: for a large batch the scan is split over a few host threads — one thread took
+        // as long as the copy-in of the whole chunk)
+        const int64_t total = n_pairs * n_rows_1;
+        auto scan = [&](int64_t i0, int64_t i1) {
+            int64_t w = 1;
+            for (int64_t i = i0; i < i1; ++i) {
+                const uint64_t lo = uint64_t(envelope_host[2 * i]), hi_u = uint64_t(envelope_host[2 * i + 1]);
+                const int64_t hi = hi_u > uint64_t(n_rows_2) ? n_rows_2 : int64_t(hi_u);
+                if (lo < uint64_t(hi) && hi - int64_t(lo) > w) w = hi - int64_t(lo);
+            }
+            return w;
+        };
+        int n_threads = int(std::min<int64_t>(8, std::max<int64_t>(1, total >> 20)));
+        n_threads = std::min<int>(n_threads, std::max(1u, std::thread::hardware_concurrency()));
+        if (n_threads <= 1) {
+            wmax = scan(0, total);
+        } else {
+            std::vector<int64_t> part(n_threads, 1);
+            std::vector<std::thread> pool;
+            for (int k = 0; k < n_threads; ++k)
+                pool.emplace_back([&, k]() { part[k] = scan(total * k / n_threads, total * (k + 1) / n_threads); });
+            for (std::thread& th : pool) th.join();
+            wmax = *std::max_element(part.begin(), part.end());
         }
     }
     const int W = int(wmax + 1);
