@@ -142,6 +142,10 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
         ticket = __shfl_sync(FULL, ticket, 0);
         if (ticket >= (unsigned long long)p.N) break;
         const long long n = (long long)ticket;
+#ifdef FCTC_BEAM_TIMING
+        unsigned long long t_start;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
+#endif
         const float* rd = p.post + n * T * C * S;
         const uint16_t* rdh = reinterpret_cast<const uint16_t*>(p.post) + n * T * C;  // the same rows when HALF
         const bool bf16 = p.in_bf16 != 0;
@@ -541,6 +545,17 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
             p.offsets[n] = off;
             p.lens[n] = len;
             p.status[n] = status;
+#ifdef FCTC_BEAM_TIMING
+            {   // development probe (tools/beam_timing_probe.py): start and duration of the read in microseconds, and the SM,
+                // in place of offsets / lens
+                unsigned long long t_end;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
+                unsigned smid;
+                asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+                p.offsets[n] = (long long)(((t_start / 1000ull) & 0xffffffffull) | ((unsigned long long)smid << 48));
+                p.lens[n] = int((t_end - t_start) / 1000ull);
+            }
+#endif
         }
         __syncwarp();
     }
