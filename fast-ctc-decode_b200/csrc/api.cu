@@ -811,7 +811,20 @@ int beam_host_pass(fctc_handle* h, const void* post_host, int in_f16, int64_t n_
     const int64_t budget = std::max<int64_t>(int64_t((free_b + owner.scratch.bytes) / 4 * 3), int64_t(1) << 28);
     const int64_t need = fctc::beam_scratch_bytes(h->sm_count, chunk, n_rows, n_labels, beam_size, nodes_per_row, budget,
                                                   &nodes_per_slot, &n_slots);
-    if (int rc = ensure(h, owner.scratch, size_t(need))) return rc;
+    // Wide beams with a pool for every warp the SMs can hold: the chunks' kernels are not made to run in turn but
+    // share the pools through a ring of free slot numbers (kernels.h), so that a chunk's first CTAs start as the
+    // chunk before it runs out of reads.  A read takes 0.7x to 1.7x the median time, and a kernel alone on the GPU
+    // spends that spread with most warps idle (one round of beam-32 reads: 112 ms alone, 57-65 ms in a long launch).
+    const int wide_per_sm = fctc::beam_wide_warps_per_sm(beam_size, n_labels, n_rows);
+    static const int overlap_knob = fctc::env_knob("FCTC_BEAM_OVERLAP");  // tuning knob: 1 = never share (kernels in turn)
+    const bool shared_pools = wide_per_sm > 0 && n_slots == h->sm_count * wide_per_sm && chunk < n_reads && overlap_knob != 1;
+    const size_t ring_off = (size_t(need) + 255) & ~size_t(255);
+    if (int rc = ensure(h, owner.scratch, shared_pools ? ring_off + size_t(n_slots) * 4 + 256 : size_t(need))) return rc;
+    unsigned int* ring = reinterpret_cast<unsigned int*>(static_cast<unsigned char*>(owner.scratch.p) + ring_off);
+    if (shared_pools) {
+        FCTC_CUDA(h, fctc::launch_beam_ring_init(ring + 64, ring, n_slots, owner.stream));
+        FCTC_CUDA(h, cudaStreamSynchronize(owner.stream));
+    }
     // every resident warp decodes one read at a time: a chunk that is not a whole number of such rounds
     // pays a full round for its leftover reads
     if (chunk > n_slots && chunk < n_reads) chunk = chunk / n_slots * n_slots;
@@ -825,9 +838,14 @@ int beam_host_pass(fctc_handle* h, const void* post_host, int in_f16, int64_t n_
         p.pool_cap = cnt * slot_entries; p.offsets = static_cast<int64_t*>(s.offsets.p);
         p.lens = static_cast<int32_t*>(s.lens.p); p.status = static_cast<int32_t*>(s.status.p);
         p.cursor = static_cast<unsigned long long*>(s.cursor.p); p.scratch = owner.scratch.p;
-        p.scratch_bytes = int64_t(owner.scratch.bytes); p.ticket = static_cast<unsigned long long*>(owner.scratch.p);
+        p.scratch_bytes = int64_t(need); p.ticket = static_cast<unsigned long long*>(owner.scratch.p);
         Slot& other = (&s == &h->slot[0]) ? h->slot[1] : h->slot[0];
-        if (!first_launch) FCTC_CUDA(h, cudaStreamWaitEvent(s.stream, other.kernel_done, 0));  // the scratch is free again
+        if (shared_pools) {
+            p.ticket = static_cast<unsigned long long*>(s.cursor.p) + 1;  // a counter per chunk: two kernels are in flight
+            p.slot_ring = ring + 64; p.ring_ctr = ring; p.ring_size = n_slots;
+        } else if (!first_launch) {
+            FCTC_CUDA(h, cudaStreamWaitEvent(s.stream, other.kernel_done, 0));  // the scratch is free again
+        }
         first_launch = false;
         FCTC_CUDA(h, fctc::launch_beam(p, h->sm_count, s.stream));
         FCTC_CUDA(h, cudaEventRecord(s.kernel_done, s.stream));

@@ -103,8 +103,17 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
     __syncthreads();
     const int lane = threadIdx.x & 31;
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);  // tells the compiler it is warp-uniform
-    const int slot = blockIdx.x * BM_WARPS + warp;
+    int slot = blockIdx.x * BM_WARPS + warp;
     if (slot >= p.n_slots) return;
+    if (p.slot_ring) {  // launches sharing one scratch (kernels.h): take a free trie pool
+        unsigned v = 0;
+        if (lane == 0) {
+            const unsigned i = atomicAdd(p.ring_ctr, 1u) % unsigned(p.ring_size);
+            while ((v = atomicExch(p.slot_ring + i, 0u)) == 0u) __nanosleep(256);
+            __threadfence();
+        }
+        slot = int(__shfl_sync(0xffffffffu, v, 0)) - 1;
+    }
     unsigned char* ws = smem + (size_t)warp * L.warp_bytes;
     const int B = p.beam_size, C = CT ? CT : p.C, NL = C - 1;
     const long long T = p.T;
@@ -147,9 +156,15 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
 #endif
         const float* rd = p.post + n * T * C * S;
-        const uint16_t* rdh = reinterpret_cast<const uint16_t*>(p.post) + n * T * C;  // the same rows when HALF
+        const uint16_t* rdh = reinterpret_cast<const uint16_t*>(p.post) + n * T * C * S;  // the same rows when HALF
         const bool bf16 = p.in_bf16 != 0;
         auto fetch = [&](long long e) -> float { return HALF ? widen16(__ldg(rdh + e), bf16) : __ldg(rd + e); };
+        // element i of a posterior row: staged rows are float32 in shared memory; the crf search reads its
+        // state-dependent rows where they lie, so 16-bit values are widened here
+        auto at = [&](const float* row, int i) -> float {
+            if (CRF && HALF) return widen16(__ldg(rdh + (row - rd) + i), bf16);
+            return row[i];
+        };
 
         int cur = 0;
         BeamView bv = beam_view(ws, L, 0, B);
@@ -231,7 +246,7 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
                     const float lp = bv.lp[b], gp = bv.gp[b];
                     const int tip = bv.tip[b];
                     const float* pr = CRF ? pr_time + (size_t)bv.st[b] * C : pr_shared;
-                    const float p_blank = pr[0];
+                    const float p_blank = at(pr, 0);
                     bool has_self = false;
                     float s_lp = 0.0f, s_gp = 0.0f;
                     if (p_blank > thr) {  // src/search.rs:191-198
@@ -239,7 +254,7 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
                         has_self = true;
                     }
                     if (collapse && tip >= 0) {  // src/search.rs:205-211
-                        const float pt = pr[tip + 1];
+                        const float pt = at(pr, tip + 1);
                         if (!(pt < thr)) {
                             s_lp = __fmul_rn(lp, pt);
                             has_self = true;
@@ -253,7 +268,7 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
                             if (bv.nd[k] == mypar) r = k;
                         if (r >= 0) {
                             const float* prp = CRF ? pr_time + (size_t)bv.st[r] * C : pr_shared;  // the parent's row
-                            const float pt = prp[tip + 1];
+                            const float pt = at(prp, tip + 1);
                             if (!(pt < thr)) {
                                 const float plp = bv.lp[r], pgp = bv.gp[r];
                                 float c;
@@ -281,7 +296,7 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
                     int n_new = 0;
                     for (int l = 0; l < NL; ++l) {
                         const int s = b * C + 1 + l;
-                        const float pl = pr[l + 1];
+                        const float pl = at(pr, l + 1);
                         uint32_t key = 0;
                         if (!(pl < thr)) {  // src/search.rs:201-203
                             const bool repeat = collapse && l == tip;
@@ -559,6 +574,20 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
         }
         __syncwarp();
     }
+    if (p.slot_ring) {  // hand the trie pool back: its stores are ordered before the slot number shows up in the ring
+        __threadfence();
+        __syncwarp();
+        if (lane == 0) {
+            const unsigned j = atomicAdd(p.ring_ctr + 1, 1u) % unsigned(p.ring_size);
+            while (atomicCAS(p.slot_ring + j, 0u, unsigned(slot) + 1u) != 0u) __nanosleep(256);
+        }
+    }
+}
+
+__global__ void beam_ring_init_kernel(unsigned int* ring, unsigned int* ctr, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) ring[i] = unsigned(i) + 1u;
+    if (i < 2) ctr[i] = 0u;
 }
 
 static bool plan_beam(int B, int C, bool crf, BeamLayout* L) {
@@ -599,6 +628,22 @@ static int default_nodes_per_row(int C, int B) {
     return int(d);
 }
 
+int beam_wide_warps_per_sm(int beam_size, int C, int64_t T) {
+    if (beam_small_eligible(beam_size, C, T)) return 0;
+    int per_sm = 24;
+    BeamLayout L;
+    if (plan_beam(beam_size, C, false, &L)) {
+        const long long cta = (long long)L.warp_bytes * BM_WARPS + 256 + 1024;  // + static table + the per-CTA reserve
+        long long ctas = (227LL * 1024) / cta;
+        if (ctas > 8) ctas = 8;
+        if (ctas < 1) ctas = 1;
+        per_sm = int(ctas) * BM_WARPS;
+    }
+    static const int per_sm_knob = env_knob("FCTC_BEAM_WARPS_PER_SM");  // tuning knob
+    if (per_sm_knob > 0) per_sm = per_sm_knob;
+    return per_sm;
+}
+
 int64_t beam_scratch_bytes(int sm_count, int64_t N, int64_t T, int C, int beam_size, int nodes_per_row,
                            int64_t budget_bytes, int64_t* nodes_per_slot, int* n_slots) {
     if (nodes_per_row <= 0) nodes_per_row = default_nodes_per_row(C, beam_size);
@@ -607,20 +652,8 @@ int64_t beam_scratch_bytes(int sm_count, int64_t N, int64_t T, int C, int beam_s
     // The kernel is latency-bound (sequential per read), so throughput follows the number of resident
     // warps: 24 per SM is what registers and shared memory allow.  One trie pool per resident warp.
     // as many 4-warp CTAs as one SM's shared memory holds (7 at beam 32 with five labels: 28 warps), 32 warps at most
-    int per_sm = 24;
-    {
-        BeamLayout L;
-        if (plan_beam(beam_size, C, false, &L)) {
-            const long long cta = (long long)L.warp_bytes * BM_WARPS + 256 + 1024;  // + static table + the per-CTA reserve
-            long long ctas = (227LL * 1024) / cta;
-            if (ctas > 8) ctas = 8;
-            if (ctas < 1) ctas = 1;
-            per_sm = int(ctas) * BM_WARPS;
-        }
-    }
-    static const int per_sm_knob = env_knob("FCTC_BEAM_WARPS_PER_SM");  // tuning knob
-    if (per_sm_knob > 0) per_sm = per_sm_knob;
-    if (beam_small_eligible(beam_size, C, T)) per_sm = beam_small_warps_per_sm();  // narrow beams: lighter warps
+    int per_sm = beam_wide_warps_per_sm(beam_size, C, T);
+    if (per_sm == 0) per_sm = beam_small_warps_per_sm();  // narrow beams: lighter warps
     const int wpc = beam_warps_per_cta(beam_size, C, T);
     long long slots = (long long)sm_count * per_sm;
     if (slots > N) slots = N;
@@ -655,8 +688,8 @@ cudaError_t launch_beam(const BeamParams& p, int sm_count, cudaStream_t stream) 
     if (!plan_beam(p.beam_size, p.C, p.S > 0, &L)) return cudaErrorInvalidConfiguration;
     const int smem = L.warp_bytes * BM_WARPS;
     const bool crf = p.S > 0;
-    if (crf && p.in_f16) return cudaErrorInvalidValue;  // the crf search reads its state-dependent rows directly: f32 only
-    auto kernel = crf ? (p.C == 5 ? beam_search_kernel<true, 5, false> : beam_search_kernel<true, 0, false>)
+    auto kernel = crf ? (p.in_f16 ? (p.C == 5 ? beam_search_kernel<true, 5, true> : beam_search_kernel<true, 0, true>)
+                                  : (p.C == 5 ? beam_search_kernel<true, 5, false> : beam_search_kernel<true, 0, false>))
                       : p.in_f16 ? (p.C == 5 ? beam_search_kernel<false, 5, true> : beam_search_kernel<false, 0, true>)
                                  : (p.C == 5 ? beam_search_kernel<false, 5, false> : beam_search_kernel<false, 0, false>);
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
@@ -667,6 +700,12 @@ cudaError_t launch_beam(const BeamParams& p, int sm_count, cudaStream_t stream) 
     if (e != cudaSuccess) return e;
     const int grid = p.n_slots / BM_WARPS;
     kernel<<<grid, BM_THREADS, smem, stream>>>(p, L);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_beam_ring_init(unsigned int* slot_ring, unsigned int* ring_ctr, int ring_size, cudaStream_t stream) {
+    if (ring_size <= 0) return cudaErrorInvalidValue;
+    beam_ring_init_kernel<<<(ring_size + 255) / 256, 256, 0, stream>>>(slot_ring, ring_ctr, ring_size);
     return cudaGetLastError();
 }
 

@@ -91,9 +91,15 @@ __global__ void __launch_bounds__(BS_THREADS, BS_MINBLOCKS) beam_small_kernel(co
         if (ticket >= (unsigned long long)p.N) break;
         const long long n = (long long)ticket;
         const float* rd = p.post + n * T * C * S;
-        const uint16_t* rdh = reinterpret_cast<const uint16_t*>(p.post) + n * T * C;  // the same rows when HALF
+        const uint16_t* rdh = reinterpret_cast<const uint16_t*>(p.post) + n * T * C * S;  // the same rows when HALF
         const bool bf16 = p.in_bf16 != 0;
         auto fetch = [&](long long e) -> float { return HALF ? widen16(__ldg(rdh + e), bf16) : __ldg(rd + e); };
+        // element i of a posterior row: staged rows are float32 in shared memory; the crf search reads its
+        // state-dependent rows where they lie, so 16-bit values are widened here
+        auto at = [&](const float* row, long long i) -> float {
+            if (CRF && HALF) return widen16(__ldg(rdh + (row - rd) + i), bf16);
+            return row[i];
+        };
 
         // the hypothesis of my lane group (src/search.rs:170-175: one root hypothesis, gap_prob 1)
         int nd = ROOT, par = -2, dep = 0, tip = -1, skp = ROOT, st = 0;
@@ -153,8 +159,8 @@ __global__ void __launch_bounds__(BS_THREADS, BS_MINBLOCKS) beam_small_kernel(co
                 const long long t = t0 + rr;
                 const bool active = myb < nbeam;
                 const float* pr = CRF ? rd + t * S * C + (size_t)st * C : rows + rr * C;  // my hypothesis' row
-                const float p_mine = active ? pr[sl] : 0.0f;                               // blank for s = 0
-                const float p_tip = (active && sl == 0 && tip >= 0) ? pr[tip + 1] : 0.0f;
+                const float p_mine = active ? at(pr, sl) : 0.0f;                               // blank for s = 0
+                const float p_tip = (active && sl == 0 && tip >= 0) ? at(pr, tip + 1) : 0.0f;
                 // my node's child for my label, asked for now so that the load overlaps the steps below
                 int x_child = -1;
                 if (active && sl > 0)
@@ -186,7 +192,7 @@ __global__ void __launch_bounds__(BS_THREADS, BS_MINBLOCKS) beam_small_kernel(co
                 const int pst = CRF ? __shfl_sync(FULL, st, r_lane) : 0;
                 unsigned fold_bit = 0u;
                 if (found) {
-                    const float pt = CRF ? rd[t * S * C + (size_t)pst * C + tip + 1] : p_tip;  // the parent's row
+                    const float pt = CRF ? at(rd, t * S * C + (long long)pst * C + tip + 1) : p_tip;  // the parent's row
                     if (!(pt < thr)) {
                         float c;
                         if (collapse && ptip == tip) c = __fmul_rn(pgp, pt);  // src/search.rs:220-226
@@ -400,8 +406,8 @@ int beam_small_warps_per_sm() {
 
 cudaError_t launch_beam_small(const BeamParams& p, cudaStream_t stream) {
     const bool crf = p.S > 0;
-    if (crf && p.in_f16) return cudaErrorInvalidValue;  // the crf search reads its state-dependent rows directly: f32 only
-    auto kernel = crf ? (p.C == 5 ? beam_small_kernel<true, 5, false> : beam_small_kernel<true, 0, false>)
+    auto kernel = crf ? (p.in_f16 ? (p.C == 5 ? beam_small_kernel<true, 5, true> : beam_small_kernel<true, 0, true>)
+                                  : (p.C == 5 ? beam_small_kernel<true, 5, false> : beam_small_kernel<true, 0, false>))
                       : p.in_f16 ? (p.C == 5 ? beam_small_kernel<false, 5, true> : beam_small_kernel<false, 0, true>)
                                  : (p.C == 5 ? beam_small_kernel<false, 5, false> : beam_small_kernel<false, 0, false>);
     const int smem = BS_WARP_SMEM * BS_WARPS;

@@ -14,6 +14,7 @@
 #include <cstdio>
 
 #include "device_utils.cuh"
+#include "input.cuh"
 #include "kernels.h"
 #include "phred.cuh"
 
@@ -25,7 +26,8 @@ __constant__ double c_crf_invc[16] = FCTC_LOGF_INVC;
 __constant__ double c_crf_logc[16] = FCTC_LOGF_LOGC;
 
 struct CrfGreedyParams {
-    const float* post;  // [N, T, S, C]
+    const float* post;  // [N, T, S, C]; 16-bit values behind the same pointer when in_kind != 0
+    int in_kind;        // FCTC_IN_F32 / F16 / BF16: 16-bit values are widened exactly to f32 as they are read
     const float* init;  // [N, n_init]
     int64_t N, T;
     int S, C, n_init;
@@ -53,6 +55,18 @@ __device__ __forceinline__ void first_argmax(const float* v, int n, int& arg, fl
     }
 }
 
+// the same over 16-bit values (binary16 or bfloat16), each widened exactly before it is compared
+__device__ __forceinline__ void first_argmax16(const uint16_t* v, int n, bool bf16, int& arg, float& best, bool& nan) {
+    best = widen16(v[0], bf16);
+    arg = 0;
+    nan = nan || (best != best);
+    for (int i = 1; i < n; ++i) {
+        const float x = widen16(v[i], bf16);
+        nan = nan || (x != x);
+        if (x > best) { best = x; arg = i; }
+    }
+}
+
 template <typename QT>
 __global__ void __launch_bounds__(128) crf_greedy_kernel(const CrfGreedyParams p) {
     __shared__ double s_invc[16], s_logc[16];
@@ -65,6 +79,8 @@ __global__ void __launch_bounds__(128) crf_greedy_kernel(const CrfGreedyParams p
     if (n >= p.N) return;
     const int S = p.S, C = p.C, n_base = C - 1;
     const float* rd = p.post + n * p.T * S * C;
+    const uint16_t* rdh = reinterpret_cast<const uint16_t*>(p.post) + n * p.T * S * C;
+    const bool wide = p.in_kind == 0, bf16 = p.in_kind == 2;
     uint8_t* out_lab = p.labels + n * p.slot_stride;
     QT* out_qual = reinterpret_cast<QT*>(p.quals) + n * p.slot_stride;
     int* out_path = p.path + n * p.slot_stride;
@@ -77,7 +93,8 @@ __global__ void __launch_bounds__(128) crf_greedy_kernel(const CrfGreedyParams p
         if (state < 0 || state >= S) { panic = true; break; }  // slice index out of range
         int label;
         float prob;
-        first_argmax(rd + (t * S + state) * C, C, label, prob, panic);  // :407, :412
+        if (wide) first_argmax(rd + (t * S + state) * C, C, label, prob, panic);  // :407, :412
+        else first_argmax16(rdh + (t * S + state) * C, C, bf16, label, prob, panic);
         if (panic) break;
         if (label > 0) {
             out_path[count] = int(t);
@@ -126,6 +143,14 @@ bool crf_quality_fits_u8(float qscale, float qbias) {
     return std::fabs(40.0 * double(qscale)) + std::fabs(double(qbias)) + 34.0 < 255.0;
 }
 
+// state-conditioned posteriors come as float32, binary16 or bfloat16; logits are not defined for them here
+int crf_input_kind(fctc_handle* h, int kind) {
+    if (!h) return FCTC_E_ARGUMENT;
+    if (kind != FCTC_IN_F32 && kind != FCTC_IN_F16 && kind != FCTC_IN_BF16)
+        return fctc::handle_fail(h, FCTC_E_ARGUMENT, "crf input_kind must be FCTC_IN_F32, FCTC_IN_F16 or FCTC_IN_BF16");
+    return 0;
+}
+
 #define CRF_CUDA(call)                                                                         \
     do {                                                                                       \
         cudaError_t e__ = (call);                                                              \
@@ -134,11 +159,13 @@ bool crf_quality_fits_u8(float qscale, float qbias) {
 
 }  // namespace
 
-extern "C" int fctc_crf_greedy_batch_device(fctc_handle* h, const float* post_dev, const float* init_dev, int64_t n_reads,
-                                            int64_t n_rows, int32_t n_state, int32_t n_labels, int32_t n_init,
-                                            int32_t qstring, float qscale, float qbias, uint8_t* labels_dev,
-                                            void* quals_dev, int32_t qual_bytes, int32_t* path_dev, int64_t pool_capacity,
-                                            int64_t* offsets_dev, int32_t* lens_dev, int32_t* status_dev, void* stream) {
+extern "C" int fctc_crf_greedy_batch_device_in(fctc_handle* h, const void* post_dev, int32_t input_kind, const float* init_dev,
+                                               int64_t n_reads, int64_t n_rows, int32_t n_state, int32_t n_labels,
+                                               int32_t n_init, int32_t qstring, float qscale, float qbias,
+                                               uint8_t* labels_dev, void* quals_dev, int32_t qual_bytes, int32_t* path_dev,
+                                               int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev,
+                                               int32_t* status_dev, void* stream) {
+    if (int rc = crf_input_kind(h, input_kind)) return rc;
     if (int rc = crf_check(h, n_reads, n_rows, n_state, n_labels, n_init)) return rc;
     if (!post_dev || !init_dev || !labels_dev || !path_dev || !offsets_dev || !lens_dev || !status_dev)
         return fctc::handle_fail(h, FCTC_E_ARGUMENT, "null device pointer");
@@ -150,7 +177,8 @@ extern "C" int fctc_crf_greedy_batch_device(fctc_handle* h, const float* post_de
     if (pool_capacity < n_reads * stride) return fctc::handle_fail(h, FCTC_E_CAPACITY, "result pool too small: n_reads*round_up(n_rows,32) entries needed");
     CRF_CUDA(cudaSetDevice(fctc::handle_device(h)));
     fctc::CrfGreedyParams p{};
-    p.post = post_dev; p.init = init_dev; p.N = n_reads; p.T = n_rows; p.S = n_state; p.C = n_labels; p.n_init = n_init;
+    p.post = static_cast<const float*>(post_dev); p.in_kind = input_kind; p.init = init_dev; p.N = n_reads; p.T = n_rows;
+    p.S = n_state; p.C = n_labels; p.n_init = n_init;
     p.qstring = qstring; p.qscale = qscale; p.qbias = qbias; p.labels = labels_dev; p.quals = quals_dev;
     p.qual_bytes = qual_bytes; p.path = path_dev; p.slot_stride = stride; p.offsets = offsets_dev; p.lens = lens_dev;
     p.status = status_dev;
@@ -158,13 +186,24 @@ extern "C" int fctc_crf_greedy_batch_device(fctc_handle* h, const float* post_de
     return 0;
 }
 
-extern "C" int fctc_crf_beam_search_batch_device(fctc_handle* h, const float* post_dev, const float* init_dev,
-                                                 int64_t n_reads, int64_t n_rows, int32_t n_state, int32_t n_labels,
-                                                 int32_t n_init, int32_t beam_size, float beam_cut_threshold,
-                                                 uint8_t* labels_dev, int32_t* path_dev, int64_t pool_capacity,
-                                                 int64_t* offsets_dev, int32_t* lens_dev, int32_t* status_dev,
-                                                 unsigned long long* pool_used_dev, void* scratch_dev,
-                                                 int64_t scratch_bytes, int32_t nodes_per_row, void* stream) {
+extern "C" int fctc_crf_greedy_batch_device(fctc_handle* h, const float* post_dev, const float* init_dev, int64_t n_reads,
+                                            int64_t n_rows, int32_t n_state, int32_t n_labels, int32_t n_init,
+                                            int32_t qstring, float qscale, float qbias, uint8_t* labels_dev,
+                                            void* quals_dev, int32_t qual_bytes, int32_t* path_dev, int64_t pool_capacity,
+                                            int64_t* offsets_dev, int32_t* lens_dev, int32_t* status_dev, void* stream) {
+    return fctc_crf_greedy_batch_device_in(h, post_dev, FCTC_IN_F32, init_dev, n_reads, n_rows, n_state, n_labels, n_init, qstring,
+                                           qscale, qbias, labels_dev, quals_dev, qual_bytes, path_dev, pool_capacity, offsets_dev,
+                                           lens_dev, status_dev, stream);
+}
+
+extern "C" int fctc_crf_beam_search_batch_device_in(fctc_handle* h, const void* post_dev, int32_t input_kind,
+                                                    const float* init_dev, int64_t n_reads, int64_t n_rows, int32_t n_state,
+                                                    int32_t n_labels, int32_t n_init, int32_t beam_size,
+                                                    float beam_cut_threshold, uint8_t* labels_dev, int32_t* path_dev,
+                                                    int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev,
+                                                    int32_t* status_dev, unsigned long long* pool_used_dev, void* scratch_dev,
+                                                    int64_t scratch_bytes, int32_t nodes_per_row, void* stream) {
+    if (int rc = crf_input_kind(h, input_kind)) return rc;
     if (int rc = crf_check(h, n_reads, n_rows, n_state, n_labels, n_init)) return rc;
     // the reference's wrapper validates only the alphabet (src/lib.rs:263-270); beam_size 0 would
     // empty the beam at once (RanOutOfBeam), a negative value cannot be passed as usize
@@ -179,13 +218,27 @@ extern "C" int fctc_crf_beam_search_batch_device(fctc_handle* h, const float* po
     const int64_t need = fctc::beam_scratch_bytes(fctc::handle_sm_count(h), n_reads, n_rows, n_labels, beam_size, nodes_per_row,
                                                   scratch_bytes, &p.nodes_per_slot, &p.n_slots);
     if (scratch_bytes < need) return fctc::handle_fail(h, FCTC_E_CAPACITY, "beam scratch too small (see fctc_beam_scratch_bytes)");
-    p.post = post_dev; p.N = n_reads; p.T = n_rows; p.C = n_labels; p.beam_size = beam_size; p.threshold = beam_cut_threshold;
+    p.post = static_cast<const float*>(post_dev); p.in_f16 = input_kind != FCTC_IN_F32; p.in_bf16 = input_kind == FCTC_IN_BF16;
+    p.N = n_reads; p.T = n_rows; p.C = n_labels; p.beam_size = beam_size; p.threshold = beam_cut_threshold;
     p.collapse = 0; p.labels = labels_dev; p.path = path_dev; p.pool_cap = pool_capacity; p.offsets = offsets_dev;
     p.lens = lens_dev; p.status = status_dev; p.cursor = pool_used_dev; p.scratch = scratch_dev; p.scratch_bytes = scratch_bytes;
     p.ticket = static_cast<unsigned long long*>(scratch_dev);
     p.S = n_state; p.init = init_dev; p.n_init = n_init;
     CRF_CUDA(fctc::launch_beam(p, fctc::handle_sm_count(h), static_cast<cudaStream_t>(stream)));
     return 0;
+}
+
+extern "C" int fctc_crf_beam_search_batch_device(fctc_handle* h, const float* post_dev, const float* init_dev,
+                                                 int64_t n_reads, int64_t n_rows, int32_t n_state, int32_t n_labels,
+                                                 int32_t n_init, int32_t beam_size, float beam_cut_threshold,
+                                                 uint8_t* labels_dev, int32_t* path_dev, int64_t pool_capacity,
+                                                 int64_t* offsets_dev, int32_t* lens_dev, int32_t* status_dev,
+                                                 unsigned long long* pool_used_dev, void* scratch_dev,
+                                                 int64_t scratch_bytes, int32_t nodes_per_row, void* stream) {
+    return fctc_crf_beam_search_batch_device_in(h, post_dev, FCTC_IN_F32, init_dev, n_reads, n_rows, n_state, n_labels, n_init,
+                                                beam_size, beam_cut_threshold, labels_dev, path_dev, pool_capacity, offsets_dev,
+                                                lens_dev, status_dev, pool_used_dev, scratch_dev, scratch_bytes, nodes_per_row,
+                                                stream);
 }
 
 // ---- single-read host entry points: the shape of the pyo3 functions src/lib.rs:214-286 ---------------

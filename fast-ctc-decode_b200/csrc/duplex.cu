@@ -135,13 +135,16 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
         const long long n = (long long)ticket;
         const float* rd1 = p.post1 + n * (long long)T1 * C * NS;
         const float* rd2 = p.post2 + n * (long long)T2 * C * NS;
-        // binary16 posteriors (plain search only): the same rows behind half pointers, widened on load
-        const __half* rh1 = reinterpret_cast<const __half*>(p.post1) + n * (long long)T1 * C;
-        const __half* rh2 = reinterpret_cast<const __half*>(p.post2) + n * (long long)T2 * C;
-        const bool half_in = !CRF && p.in_f16 != 0;
+        // binary16 posteriors: the same rows behind half pointers, widened on load
+        const __half* rh1 = reinterpret_cast<const __half*>(p.post1) + n * (long long)T1 * C * NS;
+        const __half* rh2 = reinterpret_cast<const __half*>(p.post2) + n * (long long)T2 * C * NS;
+        const bool half_in = p.in_f16 != 0;
         // network-2 value of row i, state s, column c in log space
         auto lp2 = [&](int i, int s_, int c) -> float {
-            if (CRF) return glibc_logf(rd2[((size_t)i * NS + s_) * C + c], s_invc, s_logc);
+            if (CRF) {
+                const size_t e = ((size_t)i * NS + s_) * C + c;
+                return glibc_logf(half_in ? __half2float(rh2[e]) : rd2[e], s_invc, s_logc);
+            }
             return S.logp2[(size_t)i * C + c];
         };
         const long long* env = p.env ? p.env + n * (long long)T1 * 2 : nullptr;
@@ -230,7 +233,10 @@ __global__ void __launch_bounds__(DX_THREADS, DX_MINBLOCKS) duplex_search_kernel
                     lp1[c] = glibc_logf(half_in ? __half2float(rh1[(size_t)t * C + c]) : rd1[(size_t)t * C + c], s_invc, s_logc);
             // network-1 value of this row for a hypothesis in state s_, column c
             auto row1 = [&](int s_, int c) -> float {
-                if (CRF) return glibc_logf(rd1[((size_t)t * NS + s_) * C + c], s_invc, s_logc);
+                if (CRF) {
+                    const size_t e = ((size_t)t * NS + s_) * C + c;
+                    return glibc_logf(half_in ? __half2float(rh1[e]) : rd1[e], s_invc, s_logc);
+                }
                 return lp1[c];
             };
 
@@ -736,6 +742,15 @@ extern "C" int64_t fctc_duplex_scratch_bytes(const fctc_handle* h, int64_t n_pai
                                       nodes_per_row, int64_t(96) << 30, nullptr, nullptr, 0, nullptr);
 }
 
+extern "C" int64_t fctc_crf_duplex_scratch_bytes(const fctc_handle* h, int64_t n_pairs, int64_t n_rows_1, int64_t n_rows_2,
+                                                 int32_t n_labels, int32_t beam_size, int32_t max_window,
+                                                 int32_t nodes_per_row) {
+    if (!h || n_labels <= 0 || beam_size <= 0 || n_rows_1 <= 0 || n_rows_2 < 0) return 0;
+    const int W = int((max_window > 0 && max_window < n_rows_2 ? max_window : n_rows_2) + 1);
+    return fctc::duplex_scratch_bytes(fctc::handle_sm_count(h), n_pairs, int(n_rows_1), int(n_rows_2), n_labels, beam_size, W,
+                                      nodes_per_row, int64_t(96) << 30, nullptr, nullptr, 1, nullptr);
+}
+
 static int dx_batch_device_any(fctc_handle* h, const void* post1_dev, const void* post2_dev, int in_f16,
                                int64_t n_pairs, int64_t n_rows_1, int64_t n_rows_2,
                                int32_t n_labels, const int64_t* envelope_dev, int32_t max_window,
@@ -1034,13 +1049,16 @@ extern "C" int fctc_beam_search_duplex(fctc_handle* h, const float* post1_host, 
 // ---- crf variant: replaces duplex::crf_beam_search (src/duplex.rs:652-834) as called from
 //      src/lib.rs:563-574.  The reference holds no test vector for it (parity unpinned): the check
 //      here is against this repository's CPU restatement. ---------------------------------------------
-extern "C" int fctc_crf_beam_search_duplex_batch_device(
-    fctc_handle* h, const float* post1_dev, const float* init1_dev, int32_t n_init1, const float* post2_dev,
-    const float* init2_dev, int32_t n_init2, int64_t n_pairs, int64_t n_rows_1, int64_t n_rows_2, int32_t n_state,
-    int32_t n_labels, const int64_t* envelope_dev, int32_t max_window, int32_t beam_size, float beam_cut_threshold,
-    int32_t exp_mode, uint8_t* labels_dev, int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev,
-    int32_t* status_dev, unsigned long long* pool_used_dev, void* scratch_dev, int64_t scratch_bytes,
+extern "C" int fctc_crf_beam_search_duplex_batch_device_in(
+    fctc_handle* h, const void* post1_dev, const float* init1_dev, int32_t n_init1, const void* post2_dev,
+    const float* init2_dev, int32_t n_init2, int32_t input_kind, int64_t n_pairs, int64_t n_rows_1, int64_t n_rows_2,
+    int32_t n_state, int32_t n_labels, const int64_t* envelope_dev, int32_t max_window, int32_t beam_size,
+    float beam_cut_threshold, int32_t exp_mode, uint8_t* labels_dev, int64_t pool_capacity, int64_t* offsets_dev,
+    int32_t* lens_dev, int32_t* status_dev, unsigned long long* pool_used_dev, void* scratch_dev, int64_t scratch_bytes,
     int32_t nodes_per_row, void* stream) {
+    if (!h) return FCTC_E_ARGUMENT;
+    if (input_kind != FCTC_IN_F32 && input_kind != FCTC_IN_F16)
+        return fctc::handle_fail(h, FCTC_E_ARGUMENT, "the duplex searches take FCTC_IN_F32 or FCTC_IN_F16 posteriors");
     if (int rc = dx_check(h, n_pairs, n_rows_1, n_rows_2, n_labels, beam_size, beam_cut_threshold)) return rc;
     if (n_state <= 0 || n_init1 <= 0 || n_init2 <= 0) return fctc::handle_fail(h, FCTC_E_ARGUMENT, "n_state and the init_state vectors must be non-empty");
     if (n_rows_2 * int64_t(n_labels) * n_state >= (int64_t(1) << 40)) return fctc::handle_fail(h, FCTC_E_UNSUPPORTED, "network output too large");
@@ -1056,8 +1074,9 @@ extern "C" int fctc_crf_beam_search_duplex_batch_device(
     const int64_t need = fctc::duplex_scratch_bytes(fctc::handle_sm_count(h), n_pairs, int(n_rows_1), int(n_rows_2), n_labels,
                                                     beam_size, p.W, nodes_per_row, scratch_bytes, &p.nodes_per_slot, &p.n_slots, 1,
                                                     &p.n_rings);
-    if (need > scratch_bytes) return fctc::handle_fail(h, FCTC_E_CAPACITY, "duplex scratch too small (see fctc_duplex_scratch_bytes)");
-    p.post1 = static_cast<const float*>(post1_dev); p.post2 = static_cast<const float*>(post2_dev); p.in_f16 = 0;
+    if (need > scratch_bytes) return fctc::handle_fail(h, FCTC_E_CAPACITY, "duplex scratch too small (see fctc_crf_duplex_scratch_bytes)");
+    p.post1 = static_cast<const float*>(post1_dev); p.post2 = static_cast<const float*>(post2_dev);
+    p.in_f16 = input_kind == FCTC_IN_F16;
     p.env = reinterpret_cast<const long long*>(envelope_dev);
     p.N = n_pairs; p.T1 = int(n_rows_1); p.T2 = int(n_rows_2); p.C = n_labels; p.beam_size = beam_size;
     p.threshold = beam_cut_threshold; p.collapse = 0; p.exp_mode = exp_mode;
@@ -1067,6 +1086,20 @@ extern "C" int fctc_crf_beam_search_duplex_batch_device(
     e = fctc::launch_duplex(p, static_cast<cudaStream_t>(stream));
     if (e != cudaSuccess) return fctc::handle_fail(h, FCTC_E_CUDA, cudaGetErrorString(e));
     return 0;
+}
+
+extern "C" int fctc_crf_beam_search_duplex_batch_device(
+    fctc_handle* h, const float* post1_dev, const float* init1_dev, int32_t n_init1, const float* post2_dev,
+    const float* init2_dev, int32_t n_init2, int64_t n_pairs, int64_t n_rows_1, int64_t n_rows_2, int32_t n_state,
+    int32_t n_labels, const int64_t* envelope_dev, int32_t max_window, int32_t beam_size, float beam_cut_threshold,
+    int32_t exp_mode, uint8_t* labels_dev, int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev,
+    int32_t* status_dev, unsigned long long* pool_used_dev, void* scratch_dev, int64_t scratch_bytes,
+    int32_t nodes_per_row, void* stream) {
+    return fctc_crf_beam_search_duplex_batch_device_in(h, post1_dev, init1_dev, n_init1, post2_dev, init2_dev, n_init2, FCTC_IN_F32,
+                                                       n_pairs, n_rows_1, n_rows_2, n_state, n_labels, envelope_dev, max_window,
+                                                       beam_size, beam_cut_threshold, exp_mode, labels_dev, pool_capacity,
+                                                       offsets_dev, lens_dev, status_dev, pool_used_dev, scratch_dev,
+                                                       scratch_bytes, nodes_per_row, stream);
 }
 
 // One pair from host memory; arrays C-contiguous: post [T, S, C], init [n_init], envelope usize [T1, 2] or NULL.

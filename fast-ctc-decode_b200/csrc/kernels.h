@@ -92,6 +92,12 @@ struct BeamParams {
     int64_t nodes_per_slot;  // node capacity of one slot
     int n_slots;             // slots available in scratch
     unsigned long long* ticket;  // read counter for dynamic scheduling (inside scratch)
+    // Launches that share one scratch and run at the same time (the host pipeline's consecutive chunks, wide beams):
+    // a warp takes its trie pool from a ring of free slot numbers and puts it back when it has no read left, so the
+    // next launch's CTAs fill the SMs as this launch's last reads end.  Null: slot = position in the grid.
+    unsigned int* slot_ring;     // [ring_size] slot number + 1, 0 = taken
+    unsigned int* ring_ctr;      // [0] takes so far, [1] returns so far
+    int ring_size;
     // crf variant (search::crf_beam_search): S > 0 selects it; post is [N, T, S, C]
     int S;
     const float* init;  // [N, n_init] initial state scores
@@ -102,6 +108,10 @@ struct BeamParams {
 int64_t beam_scratch_bytes(int sm_count, int64_t N, int64_t T, int C, int beam_size, int nodes_per_row,
                            int64_t budget_bytes, int64_t* nodes_per_slot, int* n_slots);
 cudaError_t launch_beam(const BeamParams& p, int sm_count, cudaStream_t stream);
+// fills a slot ring with every slot number and clears its two counters (ring_ctr points at two words)
+cudaError_t launch_beam_ring_init(unsigned int* slot_ring, unsigned int* ring_ctr, int ring_size, cudaStream_t stream);
+// the wide kernel's resident warps per SM for this shape (0 when the narrow-beam kernel takes it)
+int beam_wide_warps_per_sm(int beam_size, int C, int64_t T);
 bool beam_shape_supported(int beam_size, int C);
 // bytes of one warp's trie pool for `cap` nodes, for the kernel that (beam_size, C, T) selects
 int64_t beam_pool_bytes(int64_t cap, int beam_size, int C, int64_t T);

@@ -92,6 +92,7 @@ _SIGNATURES = {
     "fctc_multi_last_error": (C.c_char_p, []),
     "fctc_multi_release": (None, []),
     "fctc_duplex_scratch_bytes": (_i64, [_vp, _i64, _i64, _i64, _i32, _i32, _i32, _i32]),
+    "fctc_crf_duplex_scratch_bytes": (_i64, [_vp, _i64, _i64, _i64, _i32, _i32, _i32, _i32]),
     "fctc_beam_search_duplex_batch_device": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i64, _i32, _vp, _i32, _i32, _f32,
                                                        _i32, _i32, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _i64, _i32,
                                                        _vp]),
@@ -108,6 +109,13 @@ _SIGNATURES = {
                                                _i32, _vp, _i64, _vp, _vp, _vp, _vp]),
     "fctc_crf_beam_search_batch_device": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i32, _i32, _i32, _i32, _f32, _vp, _vp,
                                                     _i64, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _vp]),
+    "fctc_crf_greedy_batch_device_in": (C.c_int, [_vp, _vp, _i32, _vp, _i64, _i64, _i32, _i32, _i32, _i32, _f32, _f32, _vp,
+                                                  _vp, _i32, _vp, _i64, _vp, _vp, _vp, _vp]),
+    "fctc_crf_beam_search_batch_device_in": (C.c_int, [_vp, _vp, _i32, _vp, _i64, _i64, _i32, _i32, _i32, _i32, _f32, _vp,
+                                                       _vp, _i64, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _vp]),
+    "fctc_crf_beam_search_duplex_batch_device_in": (C.c_int, [_vp, _vp, _vp, _i32, _vp, _vp, _i32, _i32, _i64, _i64, _i64,
+                                                              _i32, _i32, _vp, _i32, _i32, _f32, _i32, _vp, _i64, _vp, _vp,
+                                                              _vp, _vp, _vp, _i64, _i32, _vp]),
     "fctc_crf_greedy_search": (C.c_int, [_vp, _vp, _i64, _i32, _i32, _vp, _i32, _i32, _f32, _f32, _vp, _vp, _vp, _i64,
                                          _vp]),
     "fctc_crf_beam_search": (C.c_int, [_vp, _vp, _i64, _i32, _i32, _vp, _i32, _i32, _f32, _vp, _vp, _i64, _vp]),
@@ -279,6 +287,13 @@ class Decoder:
     def duplex_scratch_bytes(self, n_pairs, n_rows_1, n_rows_2, n_labels, beam_size, max_window=0, nodes_per_row=0):
         return int(self._L.fctc_duplex_scratch_bytes(self._h, n_pairs, n_rows_1, n_rows_2, n_labels, beam_size,
                                                      max_window, nodes_per_row))
+
+    def crf_duplex_scratch_bytes(self, n_pairs, n_rows_1, n_rows_2, n_labels, beam_size, max_window=0, nodes_per_row=0):
+        return int(self._L.fctc_crf_duplex_scratch_bytes(self._h, n_pairs, n_rows_1, n_rows_2, n_labels, beam_size,
+                                                         max_window, nodes_per_row))
+
+    def last_error(self):
+        return (self._L.fctc_last_error(self._h) or b"").decode()
 
     def beam_search_duplex_batch_device(self, post1_ptr, post2_ptr, n_pairs, n_rows_1, n_rows_2, n_labels, envelope_ptr,
                                         max_window, beam_size, beam_cut_threshold, collapse_repeats, exp_mode,

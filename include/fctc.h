@@ -360,6 +360,21 @@ int fctc_crf_beam_search_batch_device(fctc_handle* h, const float* post_dev, con
                                       int32_t* path_dev, int64_t pool_capacity, int64_t* offsets_dev,
                                       int32_t* lens_dev, int32_t* status_dev, unsigned long long* pool_used_dev,
                                       void* scratch_dev, int64_t scratch_bytes, int32_t nodes_per_row, void* stream);
+/* The same two searches over 16-bit posteriors as the network's last layer leaves them: input_kind is FCTC_IN_F32,
+ * FCTC_IN_F16 or FCTC_IN_BF16 (no logits kinds here), every value is widened exactly to float32 where it is read
+ * (the searches read one state's row per step, in place), so the results equal those of the float32 call on the
+ * widened array.  init_dev stays float32 (n_init values per read). */
+int fctc_crf_greedy_batch_device_in(fctc_handle* h, const void* post_dev, int32_t input_kind, const float* init_dev,
+                                    int64_t n_reads, int64_t n_rows, int32_t n_state, int32_t n_labels, int32_t n_init,
+                                    int32_t qstring, float qscale, float qbias, uint8_t* labels_dev, void* quals_dev,
+                                    int32_t qual_bytes, int32_t* path_dev, int64_t pool_capacity, int64_t* offsets_dev,
+                                    int32_t* lens_dev, int32_t* status_dev, void* stream);
+int fctc_crf_beam_search_batch_device_in(fctc_handle* h, const void* post_dev, int32_t input_kind, const float* init_dev,
+                                         int64_t n_reads, int64_t n_rows, int32_t n_state, int32_t n_labels,
+                                         int32_t n_init, int32_t beam_size, float beam_cut_threshold, uint8_t* labels_dev,
+                                         int32_t* path_dev, int64_t pool_capacity, int64_t* offsets_dev,
+                                         int32_t* lens_dev, int32_t* status_dev, unsigned long long* pool_used_dev,
+                                         void* scratch_dev, int64_t scratch_bytes, int32_t nodes_per_row, void* stream);
 int fctc_crf_greedy_search(fctc_handle* h, const float* post_host, int64_t n_rows, int32_t n_state, int32_t n_labels,
                            const float* init_host, int32_t n_init, int32_t qstring, float qscale, float qbias,
                            uint8_t* labels, uint32_t* quals, int64_t* path, int64_t capacity, int64_t* out_len);
@@ -367,6 +382,9 @@ int fctc_crf_beam_search(fctc_handle* h, const float* post_host, int64_t n_rows,
                          const float* init_host, int32_t n_init, int32_t beam_size, float beam_cut_threshold,
                          uint8_t* labels, int64_t* path, int64_t capacity, int64_t* out_len);
 
+/* Scratch for the crf duplex device call (one ring per trie node: larger than fctc_duplex_scratch_bytes' plan). */
+int64_t fctc_crf_duplex_scratch_bytes(const fctc_handle* h, int64_t n_pairs, int64_t n_rows_1, int64_t n_rows_2,
+                                      int32_t n_labels, int32_t beam_size, int32_t max_window, int32_t nodes_per_row);
 int fctc_crf_beam_search_duplex_batch_device(fctc_handle* h, const float* post1_dev, const float* init1_dev,
                                              int32_t n_init1, const float* post2_dev, const float* init2_dev,
                                              int32_t n_init2, int64_t n_pairs, int64_t n_rows_1, int64_t n_rows_2,
@@ -376,6 +394,16 @@ int fctc_crf_beam_search_duplex_batch_device(fctc_handle* h, const float* post1_
                                              int64_t* offsets_dev, int32_t* lens_dev, int32_t* status_dev,
                                              unsigned long long* pool_used_dev, void* scratch_dev,
                                              int64_t scratch_bytes, int32_t nodes_per_row, void* stream);
+/* input_kind FCTC_IN_F32 or FCTC_IN_F16 (both networks alike), as fctc_beam_search_duplex_batch_device_f16. */
+int fctc_crf_beam_search_duplex_batch_device_in(fctc_handle* h, const void* post1_dev, const float* init1_dev,
+                                                int32_t n_init1, const void* post2_dev, const float* init2_dev,
+                                                int32_t n_init2, int32_t input_kind, int64_t n_pairs, int64_t n_rows_1,
+                                                int64_t n_rows_2, int32_t n_state, int32_t n_labels,
+                                                const int64_t* envelope_dev, int32_t max_window, int32_t beam_size,
+                                                float beam_cut_threshold, int32_t exp_mode, uint8_t* labels_dev,
+                                                int64_t pool_capacity, int64_t* offsets_dev, int32_t* lens_dev,
+                                                int32_t* status_dev, unsigned long long* pool_used_dev, void* scratch_dev,
+                                                int64_t scratch_bytes, int32_t nodes_per_row, void* stream);
 int fctc_crf_beam_search_duplex(fctc_handle* h, const float* post1_host, int64_t n_rows_1, const float* init1_host,
                                 int32_t n_init1, const float* post2_host, int64_t n_rows_2, const float* init2_host,
                                 int32_t n_init2, int32_t n_state, int32_t n_labels, const uint64_t* envelope,

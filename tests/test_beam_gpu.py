@@ -146,6 +146,24 @@ def test_node_pool_overflow_is_retried(dec, oracle):
     check_batch(oracle, post, res, 32, 0.0, False)
 
 
+def test_wide_beam_chunks_share_the_trie_pools(dec, oracle):
+    """More reads than one chunk of the host pipeline at beam 32: the chunks' kernels are in flight together and take
+    their trie pools from the ring of free slot numbers (csrc/kernels.h, BeamParams::slot_ring).  Every read must
+    equal the oracle, and the result pool must hold the reads without overlap."""
+    rng = np.random.default_rng(4242)
+    N, T, Cn, beam = 60_000, 64, 5, 32
+    post = peaked_posteriors(rng, (N, T, Cn))
+    res = dec.beam_search_batch(post, beam, 0.0, True)
+    assert (res["status"] == 0).all()
+    order = np.argsort(res["offsets"], kind="stable")
+    off, ln = res["offsets"][order], res["lens"][order].astype(np.int64)
+    assert (off[1:] >= off[:-1] + (ln[:-1] + 31) // 32 * 32).all()
+    check_batch(oracle, post, res, beam, 0.0, True)
+    # and the same call again on the same handle: the ring is set up anew for every call
+    res2 = dec.beam_search_batch(post[:55_000], beam, 0.0, True)
+    check_batch(oracle, post, res2, beam, 0.0, True, reads=range(0, 55_000, 11))
+
+
 def test_device_batch_synthetic(dec, oracle):
     """Device-resident API on generator output; sample of reads checked against the oracle."""
     import torch

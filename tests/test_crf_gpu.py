@@ -143,3 +143,126 @@ def test_crf_duplex_matches_oracle(dec, oracle):
         assert st == ost == 0 and labels.tolist() == ol.tolist()  # glibc's expf / log1pf on the device: identical
         seq = fcd.crf_beam_search_duplex(p1, i1, p2, i2, "NACGT"[:C], envelope=env, beam_size=beam)
         assert isinstance(seq, str) and abs(len(seq) - len(ol)) <= max(2, len(ol) // 10)
+
+
+def _encode16(x, kind):
+    """The device array for an input kind and the float32 values it stands for."""
+    import fctc_b200
+    if kind == fctc_b200.IN_F32:
+        return x, x
+    if kind == fctc_b200.IN_F16:
+        h = x.astype(np.float16)
+        return h.view(np.uint16), h.astype(np.float32)
+    b = fctc_b200.to_bf16_bits(x)
+    return b, fctc_b200.from_bf16_bits(b)
+
+
+@pytest.mark.parametrize("kind", [0, 1, 2], ids=["f32", "f16", "bf16"])
+def test_crf_searches_over_16_bit_posteriors(dec, oracle, kind):
+    """fctc_crf_greedy_batch_device_in / fctc_crf_beam_search_batch_device_in: binary16 and bfloat16 posteriors are
+    widened exactly where the searches read them, so labels, paths and quality characters equal the oracle's on the
+    widened float32 array (narrow, wide and beyond-32 beams)."""
+    import torch
+    rng = np.random.default_rng(77 + kind)
+    N, T, S, C = 24, 150, 16, 5
+    post = np.stack([crf_posteriors(rng, T, S, C, 1.0 if n % 2 else 0.0) for n in range(N)])
+    init = rng.random((N, S), dtype=np.float32)
+    arr, vals = _encode16(post, kind)
+    dev = torch.device("cuda:0")
+    dpost, dinit = torch.from_numpy(np.ascontiguousarray(arr).view(np.int16 if kind else np.float32)).to(dev), torch.from_numpy(init).to(dev)
+    stride = (T + 31) // 32 * 32
+    labels = torch.empty(N * stride, dtype=torch.uint8, device=dev)
+    quals = torch.empty(N * stride, dtype=torch.uint8, device=dev)
+    path = torch.empty(N * stride, dtype=torch.int32, device=dev)
+    offsets = torch.empty(N, dtype=torch.int64, device=dev)
+    lens = torch.empty(N, dtype=torch.int32, device=dev)
+    status = torch.empty(N, dtype=torch.int32, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream or None
+    rc = dec._L.fctc_crf_greedy_batch_device_in(dec._h, dpost.data_ptr(), kind, dinit.data_ptr(), N, T, S, C, S, 1, 0.9, 1.0,
+                                                labels.data_ptr(), quals.data_ptr(), 1, path.data_ptr(), N * stride,
+                                                offsets.data_ptr(), lens.data_ptr(), status.data_ptr(), stream)
+    assert rc == 0, dec.last_error()
+    torch.cuda.synchronize()
+    lab, q, pth, ln = labels.cpu().numpy(), quals.cpu().numpy(), path.cpu().numpy(), lens.cpu().numpy()
+    assert (status.cpu().numpy() == 0).all()
+    for n in range(N):
+        ost, ol, oq, op = oracle.crf_greedy(vals[n], init[n], True, 0.9, 1.0)
+        o = n * stride
+        assert ln[n] == len(ol) and np.array_equal(lab[o:o + ln[n]], ol) and np.array_equal(q[o:o + ln[n]], oq)
+        assert np.array_equal(pth[o:o + ln[n]], op)
+
+    used = torch.zeros(32, dtype=torch.int64, device=dev)
+    for beam, thr in ((5, 0.0), (5, 0.02), (32, 0.0), (40, 0.0)):
+        nbytes = dec.beam_scratch_bytes(N, T, C, beam, (C - 1) * beam)
+        scratch = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        rc = dec._L.fctc_crf_beam_search_batch_device_in(dec._h, dpost.data_ptr(), kind, dinit.data_ptr(), N, T, S, C, S, beam,
+                                                         thr, labels.data_ptr(), path.data_ptr(), N * stride,
+                                                         offsets.data_ptr(), lens.data_ptr(), status.data_ptr(),
+                                                         used.data_ptr(), scratch.data_ptr(), nbytes, (C - 1) * beam, stream)
+        assert rc == 0, dec.last_error()
+        torch.cuda.synchronize()
+        lab, pth, ln, off, st = (labels.cpu().numpy(), path.cpu().numpy(), lens.cpu().numpy(), offsets.cpu().numpy(),
+                                 status.cpu().numpy())
+        for n in range(N):
+            ost, ol, op = oracle.crf_beam_search(vals[n], init[n], beam, thr)
+            assert st[n] == ost, (beam, thr, n)
+            if ost == 0:
+                o = off[n]
+                assert lab[o:o + ln[n]].tolist() == list(ol) and pth[o:o + ln[n]].tolist() == list(op), (beam, thr, n)
+    # logits are not defined for state-conditioned posteriors
+    rc = dec._L.fctc_crf_greedy_batch_device_in(dec._h, dpost.data_ptr(), 0x10, dinit.data_ptr(), N, T, S, C, S, 0, 1.0, 0.0,
+                                                labels.data_ptr(), None, 1, path.data_ptr(), N * stride,
+                                                offsets.data_ptr(), lens.data_ptr(), status.data_ptr(), stream)
+    assert rc < 0 and "input_kind" in dec.last_error()
+
+
+def test_crf_duplex_over_binary16_posteriors(dec, oracle):
+    """fctc_crf_beam_search_duplex_batch_device_in with FCTC_IN_F16: equal to the oracle on the widened arrays
+    (exact-exp and max-plus modes)."""
+    import torch
+    rng = np.random.default_rng(91)
+    N, T1, T2, S, C, beam, w = 6, 70, 64, 16, 5, 5, 8
+    hid = np.where(rng.random((N, T1)) < 0.6, 0, rng.integers(1, C, (N, T1)))
+
+    def render(T):
+        idx = np.minimum((np.arange(T) * T1) // T, T1 - 1)
+        x = (0.1 * rng.random((N, T, S, C), dtype=np.float32)).astype(np.float32)
+        for n in range(N):
+            x[n, np.arange(T), :, hid[n, idx]] += 1.0
+        x /= x.sum(axis=3, keepdims=True, dtype=np.float32)
+        return x.astype(np.float16)
+    h1, h2 = render(T1), render(T2)
+    v1, v2 = h1.astype(np.float32), h2.astype(np.float32)
+    i1, i2 = rng.random((N, S), dtype=np.float32), rng.random((N, S), dtype=np.float32)
+    c = (np.arange(T1) * T2) // T1
+    env1 = np.stack([np.maximum(0, c - w), np.minimum(T2, c + w + 1)], axis=1).astype(np.int64)
+    env = np.ascontiguousarray(np.broadcast_to(env1, (N, T1, 2)))
+    dev = torch.device("cuda:0")
+    d1, d2 = torch.from_numpy(h1.view(np.int16)).to(dev), torch.from_numpy(h2.view(np.int16)).to(dev)
+    di1, di2, denv = torch.from_numpy(i1).to(dev), torch.from_numpy(i2).to(dev), torch.from_numpy(env).to(dev)
+    stride = max((T1 + 31) // 32 * 32, 32)
+    labels = torch.empty(N * stride, dtype=torch.uint8, device=dev)
+    offsets = torch.empty(N, dtype=torch.int64, device=dev)
+    lens = torch.empty(N, dtype=torch.int32, device=dev)
+    status = torch.empty(N, dtype=torch.int32, device=dev)
+    used = torch.zeros(32, dtype=torch.int64, device=dev)
+    npr = (C - 1) * beam
+    nbytes = dec.crf_duplex_scratch_bytes(N, T1, T2, C, beam, 2 * w + 1, npr)
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    for mode in (0, 1):
+        rc = dec._L.fctc_crf_beam_search_duplex_batch_device_in(
+            dec._h, d1.data_ptr(), di1.data_ptr(), S, d2.data_ptr(), di2.data_ptr(), S, 1, N, T1, T2, S, C, denv.data_ptr(),
+            2 * w + 1, beam, 0.0, mode, labels.data_ptr(), N * stride, offsets.data_ptr(), lens.data_ptr(),
+            status.data_ptr(), used.data_ptr(), scratch.data_ptr(), nbytes, npr,
+            torch.cuda.current_stream().cuda_stream or None)
+        assert rc == 0, dec.last_error()
+        torch.cuda.synchronize()
+        lab, ln, off, st = labels.cpu().numpy(), lens.cpu().numpy(), offsets.cpu().numpy(), status.cpu().numpy()
+        for n in range(N):
+            ost, ol = oracle.crf_beam_search_duplex(v1[n], i1[n], v2[n], i2[n], env1.astype(np.uint64), beam, 0.0, exp_mode=mode)
+            assert st[n] == ost == 0 and lab[off[n]:off[n] + ln[n]].tolist() == ol.tolist(), (mode, n)
+    rc = dec._L.fctc_crf_beam_search_duplex_batch_device_in(
+        dec._h, d1.data_ptr(), di1.data_ptr(), S, d2.data_ptr(), di2.data_ptr(), S, 2, N, T1, T2, S, C, denv.data_ptr(),
+        2 * w + 1, beam, 0.0, 0, labels.data_ptr(), N * stride, offsets.data_ptr(), lens.data_ptr(), status.data_ptr(),
+        used.data_ptr(), scratch.data_ptr(), nbytes, npr, None)
+    assert rc < 0
