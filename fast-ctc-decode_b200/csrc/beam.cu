@@ -95,6 +95,34 @@ static __device__ __noinline__ void softmax_staged_rows(float* rows, int n_rows,
     for (int r = lane; r < n_rows; r += 32) softmax_row(rows + r * C, C, mode, xt);
 }
 
+// Launches sharing one scratch (kernels.h): the warp takes a free trie pool from the ring (slot number + 1) and puts it
+// back when it has no read left.  Every lane takes every turn of the waiting loop: a loop that only lane 0 runs leaves
+// the warp diverged in the compiler's eyes for the rest of the kernel, and the per-warp state moves from uniform to
+// per-thread registers (48 -> 80 registers, 6 resident CTAs instead of 8).
+static __device__ __noinline__ unsigned beam_take_slot(unsigned* ctr, unsigned* ring, unsigned n) {
+    const bool first = (threadIdx.x & 31) == 0;
+    unsigned i = 0;
+    if (first) i = atomicAdd(ctr, 1u) % n;
+    unsigned v;
+    do {
+        unsigned x = 0;
+        if (first) x = atomicExch(ring + i, 0u);
+        v = __shfl_sync(0xffffffffu, x, 0);
+        if (v == 0u) __nanosleep(256);
+    } while (v == 0u);
+    __threadfence();
+    return v;
+}
+
+static __device__ __noinline__ void beam_return_slot(unsigned* ctr, unsigned* ring, unsigned n, int slot) {
+    __threadfence();  // the pool's stores are ordered before the slot number shows up in the ring
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) {
+        const unsigned j = atomicAdd(ctr + 1, 1u) % n;
+        while (atomicCAS(ring + j, 0u, unsigned(slot) + 1u) != 0u) __nanosleep(256);
+    }
+}
+
 template <bool CRF, int CT, bool HALF>
 __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParams p, const BeamLayout L) {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -105,15 +133,7 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);  // tells the compiler it is warp-uniform
     int slot = blockIdx.x * BM_WARPS + warp;
     if (slot >= p.n_slots) return;
-    if (p.slot_ring) {  // launches sharing one scratch (kernels.h): take a free trie pool
-        unsigned v = 0;
-        if (lane == 0) {
-            const unsigned i = atomicAdd(p.ring_ctr, 1u) % unsigned(p.ring_size);
-            while ((v = atomicExch(p.slot_ring + i, 0u)) == 0u) __nanosleep(256);
-            __threadfence();
-        }
-        slot = int(__shfl_sync(0xffffffffu, v, 0)) - 1;
-    }
+    if (p.slot_ring) slot = int(beam_take_slot(p.ring_ctr, p.slot_ring, unsigned(p.ring_size))) - 1;
     unsigned char* ws = smem + (size_t)warp * L.warp_bytes;
     const int B = p.beam_size, C = CT ? CT : p.C, NL = C - 1;
     const long long T = p.T;
@@ -561,27 +581,21 @@ __global__ void __launch_bounds__(BM_THREADS) beam_search_kernel(const BeamParam
             p.lens[n] = len;
             p.status[n] = status;
 #ifdef FCTC_BEAM_TIMING
-            {   // development probe (tools/beam_timing_probe.py): start and duration of the read in microseconds, and the SM,
-                // in place of offsets / lens
+            {   // development probe (tools/beam_timing_probe.py), in place of the read's offset: start in microseconds
+                // (bits 0-31), duration in units of 8 microseconds (bits 32-47), SM (bits 48-63)
                 unsigned long long t_end;
                 asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
                 unsigned smid;
                 asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
-                p.offsets[n] = (long long)(((t_start / 1000ull) & 0xffffffffull) | ((unsigned long long)smid << 48));
-                p.lens[n] = int((t_end - t_start) / 1000ull);
+                unsigned long long dur = (t_end - t_start) / 8000ull;
+                if (dur > 0xffffull) dur = 0xffffull;
+                p.offsets[n] = (long long)(((t_start / 1000ull) & 0xffffffffull) | (dur << 32) | ((unsigned long long)smid << 48));
             }
 #endif
         }
         __syncwarp();
     }
-    if (p.slot_ring) {  // hand the trie pool back: its stores are ordered before the slot number shows up in the ring
-        __threadfence();
-        __syncwarp();
-        if (lane == 0) {
-            const unsigned j = atomicAdd(p.ring_ctr + 1, 1u) % unsigned(p.ring_size);
-            while (atomicCAS(p.slot_ring + j, 0u, unsigned(slot) + 1u) != 0u) __nanosleep(256);
-        }
-    }
+    if (p.slot_ring) beam_return_slot(p.ring_ctr, p.slot_ring, unsigned(p.ring_size), slot);
 }
 
 __global__ void beam_ring_init_kernel(unsigned int* ring, unsigned int* ctr, int n) {

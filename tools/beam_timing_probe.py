@@ -25,11 +25,25 @@ for rep in range(2):
                                  lens.data_ptr(), status.data_ptr(), used.data_ptr(), scratch.data_ptr(), nb, 0, st)
     e1.record(); torch.cuda.synchronize()
 ms = e0.elapsed_time(e1)
-o = offsets.cpu().numpy().astype(np.uint64); d = lens.cpu().numpy().astype(np.int64)
+o = offsets.cpu().numpy().astype(np.uint64); ln = lens.cpu().numpy().astype(np.int64)
 start = (o & np.uint64(0xffffffff)).astype(np.int64); sm = (o >> np.uint64(48)).astype(np.int64)
+d = ((o >> np.uint64(32)) & np.uint64(0xffff)).astype(np.int64) * 8
 start -= start.min()
 print(f"N={N} T={T} kernel {ms:.1f} ms; read duration us: min {d.min()} p10 {np.percentile(d,10):.0f} median {np.median(d):.0f} p90 {np.percentile(d,90):.0f} max {d.max()}")
 print("start us: p0,p50,p90,p99,max", start.min(), np.median(start), np.percentile(start,90), np.percentile(start,99), start.max())
 late = start > 1000
 print("reads starting later than 1 ms:", int(late.sum()), "on SMs:", len(np.unique(sm[late])), "SMs used:", len(np.unique(sm)))
 print("reads per SM min/max", np.bincount(sm).min(), np.bincount(sm).max())
+print("corr(duration, emitted labels) %.3f; labels min/median/max %d %d %d" % (np.corrcoef(d, ln)[0, 1], ln.min(), np.median(ln), ln.max()))
+per_sm = np.array([d[sm == k].mean() for k in np.unique(sm)])
+within = np.array([d[sm == k].std() for k in np.unique(sm)])
+print("per-SM mean duration us: min %.0f median %.0f max %.0f; std of a read's duration inside one SM: median %.0f" %
+      (per_sm.min(), np.median(per_sm), per_sm.max(), np.median(within)))
+edges = np.percentile(start, [0, 20, 40, 60, 80, 100])
+for a, b in zip(edges[:-1], edges[1:]):
+    m = (start >= a) & (start <= b)
+    print("  reads starting in [%.0f, %.0f] us: median duration %.0f us, p90 %.0f" % (a, b, np.median(d[m]), np.percentile(d[m], 90)))
+first = start < 1000
+if first.any():
+    k = np.argsort(d[first])
+    print("first-round reads: fastest 5 durations", d[first][k[:5]], "on SMs", sm[first][k[:5]], "; slowest 5", d[first][k[-5:]], "on SMs", sm[first][k[-5:]])
