@@ -1105,7 +1105,7 @@ int fctc_test_poison_shared_memory(fctc_handle* h, int32_t byte) {
 
 int fctc_test_libm_device(fctc_handle* h, const float* x_dev, const float* y_dev, float* out_dev, int64_t n, int32_t which,
                           void* stream) {
-    if (!h || !x_dev || !out_dev || which < 0 || which > 4 || (which == 4 && !y_dev)) return FCTC_E_ARGUMENT;
+    if (!h || !x_dev || !out_dev || which < 0 || which > 6 || (which >= 4 && !y_dev)) return FCTC_E_ARGUMENT;
     FCTC_CUDA(h, cudaSetDevice(h->device));
     FCTC_CUDA(h, fctc::launch_libm_probe(x_dev, y_dev, out_dev, n, which, static_cast<cudaStream_t>(stream)));
     return 0;

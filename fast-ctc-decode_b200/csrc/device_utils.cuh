@@ -89,11 +89,16 @@ __device__ __forceinline__ uint32_t order_key(float v) {
     return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
 }
 
+// The shuffle's own predicate (true where the source lane exists) guards the add: two instructions per step
+// instead of shuffle + compare + select + add.
 __device__ __forceinline__ int warp_inclusive_scan(int v, int lane) {
+    (void)lane;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
-        int n = __shfl_up_sync(0xffffffffu, v, d);
-        if (lane >= d) v += n;
+        asm volatile("{\n\t.reg .pred p;\n\t.reg .s32 t;\n\t"
+                     "shfl.sync.up.b32 t|p, %0, %1, 0, 0xffffffff;\n\t"
+                     "@p add.s32 %0, %0, t;\n\t}"
+                     : "+r"(v) : "r"(d));
     }
     return v;
 }

@@ -118,7 +118,13 @@ __global__ void __launch_bounds__(256) libm_probe_kernel(const float* x, const f
         else if (which == 1) r = glibc_log1pf_unit(v);
         else if (which == 2) r = glibc_logf(v, invc, logc);
         else if (which == 3) r = glibc_log10f(v, invc, logc);
-        else r = lg_add(v, y[i], 0, xt);
+        else if (which == 5) {  // fast minus exact quality value for the miss probability v; y = {qscale, qbias}
+            const QualityParams qp = make_quality_params(y[0], y[1]);
+            r = phred_fast_q(v, qp) - phred_exact_q(v, y[0], y[1], invc, logc);
+        } else if (which == 6) {  // the eps the fast path allows at that value
+            const QualityParams qp = make_quality_params(y[0], y[1]);
+            r = phred_fast_eps(phred_fast_q(v, qp), qp);
+        } else r = lg_add(v, y[i], 0, xt);
         out[i] = r;
     }
 }

@@ -58,46 +58,17 @@ __constant__ double c_logf_invc[16] = FCTC_LOGF_INVC;
 __constant__ double c_logf_logc[16] = FCTC_LOGF_LOGC;
 __constant__ uint64_t c_vit_exp2f[32] = FCTC_EXP2F_TAB;  // glibc expf's table, for the exact softmax of logits (input.cuh)
 
-// ---------------------------------------------------------------------------------------------
-// Quality character.  Fast path: q from MUFU.LG2; it differs from the reference's float
-// evaluation (glibc log10f, three rounded f32 ops) by at most
-//     D <= 6e-6*|qscale| + 4e-7*(|q - qbias| + |q|)
-// (2 ulp of lg2 at |lg2 p| <= 128, times 3.0103, plus the roundings on both sides).  If q is
-// farther than eps >> D from every k + 0.5 boundary, both round to the same integer and the
-// fast result is exact; otherwise (about 0.2 % of labels) the binary64 path decides.
-// ---------------------------------------------------------------------------------------------
-struct QualityParams {  // per-launch constants of the fast path
-    float qscale, qbias;
-    float k1;    // -10*log10(2) * qscale
-    float eps0;  // 1e-3*|qscale| + 2e-5*|qbias| + 1e-6
-};
-__device__ __forceinline__ QualityParams make_quality_params(float qscale, float qbias) {
-    QualityParams q;
-    q.qscale = qscale;
-    q.qbias = qbias;
-    q.k1 = -3.0102999566f * qscale;
-    q.eps0 = 1e-3f * fabsf(qscale) + 2e-5f * fabsf(qbias) + 1e-6f;
-    return q;
-}
-
-__device__ __forceinline__ bool phred_fast(float mean, const QualityParams& qp, uint32_t* code) {
-    const float miss = __fadd_rn(1.0f, -mean);
-    const float pm = (miss < 1e-4f) ? 1e-4f : miss;  // >= 1e-4 (or NaN): never denormal
-    float l2;
-    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(l2) : "f"(pm));
-    const float q = fmaf(l2, qp.k1, qp.qbias);
-    const float eps = fmaf(fabsf(q), 2e-5f, qp.eps0);  // >= the bound D above, with a wide margin
-    const float fr = q - floorf(q);
-    *code = __float2uint_rn(q) + 33u;  // cvt.rni.u32.f32 clamps to [0, 2^32-1] and maps NaN to 0
-    return fabsf(fr - 0.5f) > eps;     // false for NaN / inf / huge |q|: the exact path decides
-}
-
 template <typename QT>
 __device__ __forceinline__ QT quality_char(float sum, int n, const QualityParams& qp, const double* invc,
                                            const double* logc, bool& bad_char) {
-    const float mean = __fdiv_rn(sum, float(n));  // IEEE division (src/search.rs:350); x / 1 == x exactly
+    // mean = sum / n, an IEEE division (src/search.rs:350).  For a sum of moderate size (2^-60 <= sum < 2^60; n < 2^30)
+    // the straight-line core of the division is exact (phred.cuh), so the common case has no range check of its own:
+    // one test sends everything else — odd sums and quality values too close to a rounding boundary — to the exact path.
+    const float nf = float(n);
+    const bool moderate = (__float_as_uint(sum) - 0x21800000u) < 0x3c000000u;
     uint32_t code;
-    if (!phred_fast(mean, qp, &code)) code = phred_code(mean, qp.qscale, qp.qbias, invc, logc);
+    if (!(phred_fast(fdiv_moderate(sum, nf), qp, &code) && moderate))
+        code = phred_code(__fdiv_rn(sum, nf), qp.qscale, qp.qbias, invc, logc);
     if (sizeof(QT) == 4 && !is_unicode_scalar(code)) bad_char = true;
     return QT(code);
 }
@@ -383,7 +354,9 @@ __global__ void __launch_bounds__(VW_THREADS, QSTRING ? VW_MINBLOCKS_Q : VW_MINB
                 bool reach[RPL];
 #pragma unroll
                 for (int r = 0; r < RPL; ++r) {
-                    S[r] = __fadd_rn(0.0f, pr[r]);  // label_prob_total starts at 0.0 (src/search.rs:339,354)
+                    // label_prob_total starts at 0.0 (src/search.rs:339,354); 0.0 + p differs from p only in the sign of
+                    // a zero, which the quality value, a function of 1 - mean, does not see
+                    S[r] = pr[r];
                     nr[r] = 1;
                     bool alive = COLLAPSE;
 #pragma unroll

@@ -499,7 +499,10 @@ int fctc_test_poison_shared_memory(fctc_handle* h, int32_t byte);
 
 /* Test hook (replaces nothing): runs the DEVICE builds of the libm restatements over an array — which = 0 expf (x <= 0),
  * 1 log1pf (0 <= x <= 1), 2 logf, 3 log10f, 4 LogSpace '+' of (x[i], y[i]) in exact-exp mode — so that tests compare the
- * arithmetic the kernels execute with the host's libm directly.  y_dev may be NULL unless which == 4. */
+ * arithmetic the kernels execute with the host's libm directly; 5: the quality value of the Viterbi kernel's fast path
+ * (hardware lg2) minus the reference's (glibc log10f and three rounded operations) for the miss probability x[i], with
+ * y = {qscale, qbias}; 6: the distance from a rounding boundary below which the fast path defers to the exact one at
+ * that value.  y_dev may be NULL unless which >= 4. */
 int fctc_test_libm_device(fctc_handle* h, const float* x_dev, const float* y_dev, float* out_dev, int64_t n, int32_t which,
                           void* stream);
 

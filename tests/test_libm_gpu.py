@@ -89,3 +89,25 @@ def test_logspace_add_on_device(dec, oracle):
     e = host(oracle, "oracle_expf_n", d)
     l = host(oracle, "oracle_log1pf_n", e)
     same_bits(got[:n], (big + l).astype(np.float32))
+
+
+@pytest.mark.parametrize("qscale,qbias", [(1.0, 0.0), (0.7, 2.0), (2.5, -3.0), (1.0, 33.0), (0.1, 0.0), (40.0, 100.0), (-1.0, 50.0),
+                                          (0.013, -0.5), (3.3, 1e3)])
+def test_fast_quality_value_stays_inside_its_margin(dec, qscale, qbias):
+    """The Viterbi kernel takes the quality character from a hardware lg2 whenever the value lies farther than eps
+    from a rounding boundary (csrc/phred.cuh, phred_fast).  Here the distance between that value and the reference's
+    (glibc log10f, three rounded float32 operations) is measured on the device for EVERY float32 miss probability from
+    1e-4 to 1 and a stride through (1, 2^40]: it must stay below a quarter of eps."""
+    import torch
+    lo = int(np.float32(1e-4).view(np.uint32))
+    bits = np.concatenate([np.arange(lo, 0x3F800001, dtype=np.uint32), np.arange(0x3F800000, 0x53800000, 4099, dtype=np.uint32)])
+    x = bits.view(np.float32).copy()
+    y = np.array([qscale, qbias], np.float32)
+    dx, dy = torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda()
+    diff, eps = torch.empty_like(dx), torch.empty_like(dx)
+    st = torch.cuda.current_stream().cuda_stream
+    dec.libm_device(dx.data_ptr(), dy.data_ptr(), diff.data_ptr(), x.size, 5, st)
+    dec.libm_device(dx.data_ptr(), dy.data_ptr(), eps.data_ptr(), x.size, 6, st)
+    torch.cuda.synchronize()
+    ratio = float((diff.abs() / eps).max())
+    assert x.size > 100_000_000 and ratio < 0.25, ratio
