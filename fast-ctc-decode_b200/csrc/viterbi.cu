@@ -58,17 +58,24 @@ __constant__ double c_logf_invc[16] = FCTC_LOGF_INVC;
 __constant__ double c_logf_logc[16] = FCTC_LOGF_LOGC;
 __constant__ uint64_t c_vit_exp2f[32] = FCTC_EXP2F_TAB;  // glibc expf's table, for the exact softmax of logits (input.cuh)
 
+// The two halves of quality_char: the straight-line shortcut (false = its result must not be used) and the exact path.
+__device__ __forceinline__ bool quality_fast(float sum, int n, const QualityParams& qp, uint32_t* code) {
+    const bool moderate = (__float_as_uint(sum) - 0x21800000u) < 0x3c000000u;
+    return phred_fast(fdiv_moderate(sum, float(n)), qp, code) && moderate;
+}
+__device__ __forceinline__ uint32_t quality_exact(float sum, int n, const QualityParams& qp, const double* invc,
+                                                  const double* logc) {
+    return phred_code(__fdiv_rn(sum, float(n)), qp.qscale, qp.qbias, invc, logc);
+}
+
 template <typename QT>
 __device__ __forceinline__ QT quality_char(float sum, int n, const QualityParams& qp, const double* invc,
                                            const double* logc, bool& bad_char) {
     // mean = sum / n, an IEEE division (src/search.rs:350).  For a sum of moderate size (2^-60 <= sum < 2^60; n < 2^30)
     // the straight-line core of the division is exact (phred.cuh), so the common case has no range check of its own:
     // one test sends everything else — odd sums and quality values too close to a rounding boundary — to the exact path.
-    const float nf = float(n);
-    const bool moderate = (__float_as_uint(sum) - 0x21800000u) < 0x3c000000u;
     uint32_t code;
-    if (!(phred_fast(fdiv_moderate(sum, nf), qp, &code) && moderate))
-        code = phred_code(__fdiv_rn(sum, nf), qp.qscale, qp.qbias, invc, logc);
+    if (!quality_fast(sum, n, qp, &code)) code = quality_exact(sum, n, qp, invc, logc);
     if (sizeof(QT) == 4 && !is_unicode_scalar(code)) bad_char = true;
     return QT(code);
 }
