@@ -56,12 +56,12 @@ WORKLOADS = {
     "beam32": dict(reads=65_536, T=10_000, C=5, kind="beam", beam=32, thr=0.0, collapse=1, cpu_sample=128,
                    e2e_reads=32768, label="beam_search 65,536 reads x T=10,000 x C=5, beam_size=32, beam_cut_threshold=0.0"),
     "duplex": dict(reads=16_384, T=4000, T2=4000, C=5, kind="duplex", beam=5, thr=0.0, collapse=1, band=32, exp_mode=0,
-                   cpu_sample=64, e2e_reads=8192,  # one even round of the pairs in flight
+                   cpu_sample=64, e2e_reads=16384,  # the whole configuration: two chunks, the second copied in under the first's kernel
                    label="duplex 2D envelope beam search: 16,384 pairs x T1=T2=4000 x C=5, beam_size=5, band +-32, exact exp "
                          "(exp_mode 0: glibc's expf/log1pf evaluated on the device, results bit-identical to the CPU reference)"),
     # the same search with CUDA's own expf/log1pf (exp_mode 2, the opt-in fast mode; round 1's duplex figure was measured this way)
     "duplex_cuda_exp": dict(reads=16_384, T=4000, T2=4000, C=5, kind="duplex", beam=5, thr=0.0, collapse=1, band=32, exp_mode=2,
-                            cpu_sample=64, e2e_reads=8192,
+                            cpu_sample=64, e2e_reads=16384,
                             label="duplex 2D envelope beam search: 16,384 pairs x T1=T2=4000 x C=5, beam_size=5, band +-32, "
                                   "exp_mode 2 (CUDA expf/log1pf: last-bit differences from a glibc host)"),
 }

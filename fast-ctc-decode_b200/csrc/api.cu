@@ -716,6 +716,7 @@ void* handle_pinned_buffer(fctc_handle* h, int index, size_t bytes) {
     return h->extra_pin[index];
 }
 cudaStream_t handle_stream(fctc_handle* h) { return h->stream; }
+cudaStream_t handle_aux_stream(fctc_handle* h) { return h->slot[1].stream; }
 }  // namespace fctc
 
 int64_t fctc_beam_scratch_bytes(const fctc_handle* h, int64_t n_reads, int64_t n_rows, int32_t n_labels,

@@ -823,43 +823,63 @@ extern "C" int fctc_beam_search_duplex_batch_device_f16(fctc_handle* h, const vo
 
 namespace {
 
-// One synchronous pass over pairs [first, first+cnt) of host arrays.  Results are appended to the
-// host pool at *used.
-int dx_host_chunk(fctc_handle* h, const void* post1, const void* post2, int in_f16, const int64_t* env, int64_t cnt, int64_t T1,
-                  int64_t T2, int32_t C, int W, int32_t beam, float thr, int32_t collapse, int32_t exp_mode,
-                  int32_t nodes_per_row, uint8_t* labels, int64_t pool_cap, int64_t* offsets, int32_t* lens,
-                  int32_t* status, int64_t* used) {
-    cudaStream_t st = fctc::handle_stream(h);
-    const int64_t stride = (T1 + 31) & ~int64_t(31);
+#define DX_CUDA(call)                                                                          \
+    do {                                                                                       \
+        cudaError_t e__ = (call);                                                              \
+        if (e__ != cudaSuccess) return fctc::handle_fail(h, FCTC_E_CUDA, cudaGetErrorString(e__)); \
+    } while (0)
+
+// A chunk of pairs goes through three steps, so that the next chunk's inputs can be copied in while this chunk's
+// kernel runs: stage (inputs to one of two device sets, on the stream given), launch (kernel and the small result
+// arrays, on the handle's stream, after the staging event), finish (wait, labels to the host pool at *used).
+struct DxInputs {
+    float* d1 = nullptr;
+    float* d2 = nullptr;
+    long long* de = nullptr;
+};
+struct DxChunk {
+    int64_t cnt = 0, stride = 0;
+    uint8_t* dl = nullptr;
+    unsigned long long* hcur = nullptr;
+};
+
+int dx_stage(fctc_handle* h, int set, cudaStream_t cs, const void* post1, const void* post2, int in_f16, const int64_t* env,
+             int64_t cnt, int64_t T1, int64_t T2, int32_t C, DxInputs* in) {
     const size_t eb = in_f16 ? 2 : 4;
     const size_t b1 = size_t(cnt) * T1 * C * eb, b2 = size_t(cnt) * T2 * C * eb, be = size_t(cnt) * T1 * 16;
-    float* d1 = static_cast<float*>(fctc::handle_device_buffer(h, 0, b1));
-    float* d2 = static_cast<float*>(fctc::handle_device_buffer(h, 1, std::max<size_t>(b2, 16)));
-    long long* de = env ? static_cast<long long*>(fctc::handle_device_buffer(h, 2, be)) : nullptr;
+    const int base = set ? 13 : 0;  // persistent buffers 0-2 and 13-15 of the handle
+    in->d1 = static_cast<float*>(fctc::handle_device_buffer(h, base, std::max<size_t>(b1, 16)));
+    in->d2 = static_cast<float*>(fctc::handle_device_buffer(h, base + 1, std::max<size_t>(b2, 16)));
+    in->de = env ? static_cast<long long*>(fctc::handle_device_buffer(h, base + 2, be)) : nullptr;
+    if (!in->d1 || !in->d2 || (env && !in->de)) return FCTC_E_NOMEM;
+    if (b1) DX_CUDA(cudaMemcpyAsync(in->d1, post1, b1, cudaMemcpyHostToDevice, cs));
+    if (b2) DX_CUDA(cudaMemcpyAsync(in->d2, post2, b2, cudaMemcpyHostToDevice, cs));
+    if (env) DX_CUDA(cudaMemcpyAsync(in->de, env, be, cudaMemcpyHostToDevice, cs));
+    return 0;
+}
+
+int dx_launch(fctc_handle* h, const DxInputs& in, cudaEvent_t staged, int in_f16, int64_t cnt, int64_t T1, int64_t T2, int32_t C,
+              int W, int32_t beam, float thr, int32_t collapse, int32_t exp_mode, int32_t nodes_per_row, int64_t* offsets,
+              int32_t* lens, int32_t* status, DxChunk* ck) {
+    cudaStream_t st = fctc::handle_stream(h);
+    const int64_t stride = (T1 + 31) & ~int64_t(31);
     uint8_t* dl = static_cast<uint8_t*>(fctc::handle_device_buffer(h, 3, size_t(cnt * stride)));
     int64_t* doff = static_cast<int64_t*>(fctc::handle_device_buffer(h, 4, size_t(cnt) * 8));
     int32_t* dlen = static_cast<int32_t*>(fctc::handle_device_buffer(h, 5, size_t(cnt) * 4));
     int32_t* dst = static_cast<int32_t*>(fctc::handle_device_buffer(h, 6, size_t(cnt) * 4));
     unsigned long long* dcur = static_cast<unsigned long long*>(fctc::handle_device_buffer(h, 7, 256));
     unsigned long long* hcur = static_cast<unsigned long long*>(fctc::handle_pinned_buffer(h, 0, 64));
-    if (!d1 || !d2 || (env && !de) || !dl || !doff || !dlen || !dst || !dcur || !hcur) return FCTC_E_NOMEM;
+    if (!dl || !doff || !dlen || !dst || !dcur || !hcur) return FCTC_E_NOMEM;
     fctc::DuplexParams p{};
     p.W = W;
     const int64_t need = fctc::duplex_scratch_bytes(fctc::handle_sm_count(h), cnt, int(T1), int(T2), C, beam, W, nodes_per_row,
                                                     dx_free_budget(h), &p.nodes_per_slot, &p.n_slots, 0, &p.n_rings);
     void* scratch = fctc::handle_device_buffer(h, 8, size_t(need));
     if (!scratch) return FCTC_E_NOMEM;
-#define DX_CUDA(call)                                                                          \
-    do {                                                                                       \
-        cudaError_t e__ = (call);                                                              \
-        if (e__ != cudaSuccess) return fctc::handle_fail(h, FCTC_E_CUDA, cudaGetErrorString(e__)); \
-    } while (0)
-    DX_CUDA(cudaMemcpyAsync(d1, post1, b1, cudaMemcpyHostToDevice, st));
-    if (b2) DX_CUDA(cudaMemcpyAsync(d2, post2, b2, cudaMemcpyHostToDevice, st));
-    if (env) DX_CUDA(cudaMemcpyAsync(de, env, be, cudaMemcpyHostToDevice, st));
+    if (staged) DX_CUDA(cudaStreamWaitEvent(st, staged, 0));
     DX_CUDA(cudaMemsetAsync(dcur, 0, 8, st));
-    p.post1 = d1; p.post2 = d2; p.in_f16 = in_f16; p.env = de; p.N = cnt; p.T1 = int(T1); p.T2 = int(T2); p.C = C; p.beam_size = beam;
-    p.threshold = thr; p.collapse = collapse; p.exp_mode = exp_mode; p.labels = dl; p.pool_cap = cnt * stride;
+    p.post1 = in.d1; p.post2 = in.d2; p.in_f16 = in_f16; p.env = in.de; p.N = cnt; p.T1 = int(T1); p.T2 = int(T2); p.C = C;
+    p.beam_size = beam; p.threshold = thr; p.collapse = collapse; p.exp_mode = exp_mode; p.labels = dl; p.pool_cap = cnt * stride;
     p.offsets = doff; p.lens = dlen; p.status = dst; p.cursor = dcur; p.scratch = scratch;
     p.ticket = static_cast<unsigned long long*>(scratch);
     DX_CUDA(fctc::launch_duplex(p, st));
@@ -867,15 +887,34 @@ int dx_host_chunk(fctc_handle* h, const void* post1, const void* post2, int in_f
     DX_CUDA(cudaMemcpyAsync(offsets, doff, size_t(cnt) * 8, cudaMemcpyDeviceToHost, st));
     DX_CUDA(cudaMemcpyAsync(lens, dlen, size_t(cnt) * 4, cudaMemcpyDeviceToHost, st));
     DX_CUDA(cudaMemcpyAsync(status, dst, size_t(cnt) * 4, cudaMemcpyDeviceToHost, st));
+    ck->cnt = cnt; ck->stride = stride; ck->dl = dl; ck->hcur = hcur;
+    return 0;
+}
+
+int dx_finish(fctc_handle* h, const DxChunk& ck, uint8_t* labels, int64_t pool_cap, int64_t* offsets, int64_t* used) {
+    cudaStream_t st = fctc::handle_stream(h);
     DX_CUDA(cudaStreamSynchronize(st));
-    const int64_t got = int64_t(*hcur);
+    const int64_t got = int64_t(*ck.hcur);
     if (*used + got > pool_cap) return fctc::handle_fail(h, FCTC_E_CAPACITY, "result pool too small (n_pairs*round_up(n_rows_1,32) always suffices)");
-    if (got) DX_CUDA(cudaMemcpyAsync(labels + *used, dl, size_t(got), cudaMemcpyDeviceToHost, st));
+    if (got) DX_CUDA(cudaMemcpyAsync(labels + *used, ck.dl, size_t(got), cudaMemcpyDeviceToHost, st));
     DX_CUDA(cudaStreamSynchronize(st));
-#undef DX_CUDA
-    for (int64_t i = 0; i < cnt; ++i) offsets[i] += *used;
+    for (int64_t i = 0; i < ck.cnt; ++i) offsets[i] += *used;
     *used += got;
     return 0;
+}
+
+// One synchronous pass over `cnt` pairs of host arrays.  Results are appended to the host pool at *used.
+int dx_host_chunk(fctc_handle* h, const void* post1, const void* post2, int in_f16, const int64_t* env, int64_t cnt, int64_t T1,
+                  int64_t T2, int32_t C, int W, int32_t beam, float thr, int32_t collapse, int32_t exp_mode,
+                  int32_t nodes_per_row, uint8_t* labels, int64_t pool_cap, int64_t* offsets, int32_t* lens,
+                  int32_t* status, int64_t* used) {
+    DxInputs in;
+    DxChunk ck;
+    if (int rc = dx_stage(h, 0, fctc::handle_stream(h), post1, post2, in_f16, env, cnt, T1, T2, C, &in)) return rc;
+    if (int rc = dx_launch(h, in, nullptr, in_f16, cnt, T1, T2, C, W, beam, thr, collapse, exp_mode, nodes_per_row, offsets, lens,
+                           status, &ck))
+        return rc;
+    return dx_finish(h, ck, labels, pool_cap, offsets, used);
 }
 
 }  // namespace
@@ -934,15 +973,52 @@ static int dx_batch_host_any(fctc_handle* h, const void* post1_any, const void* 
                               (fctc::duplex_packed_shape(beam_size, n_labels, 0) ? fctc::duplex_packed_slots_per_sm(exp_mode) : 24);
     int64_t chunk = std::max<int64_t>((int64_t(2) << 30) / std::max<int64_t>(pair_bytes, 1), 1);
     if (chunk > in_flight) chunk = chunk / in_flight * in_flight;
+    static const int chunk_knob = fctc::env_knob("FCTC_DUPLEX_CHUNK_PAIRS");  // tuning / test knob
+    if (chunk_knob > 0) chunk = chunk_knob;
     chunk = std::max<int64_t>(1, std::min<int64_t>(chunk, n_pairs));
     int64_t used = 0;
-    for (int64_t first = 0; first < n_pairs; first += chunk) {
-        const int64_t cnt = std::min(chunk, n_pairs - first);
-        if (int rc = dx_host_chunk(h, post1_host + first * n_rows_1 * n_labels * eb, post2_host + first * n_rows_2 * n_labels * eb,
-                                   in_f16, envelope_host ? envelope_host + first * n_rows_1 * 2 : nullptr, cnt, n_rows_1, n_rows_2,
-                                   n_labels, W, beam_size, beam_cut_threshold, collapse_repeats, exp_mode, 0, labels,
-                                   pool_capacity, offsets + first, lens + first, status + first, &used))
-            return rc;
+    {
+        // chunk k+1 is copied into the other input set on a second stream while chunk k's kernel runs; the kernel is
+        // queued before that copy so that a caller with pageable memory (whose copy blocks the host) loses nothing
+        cudaStream_t cs = fctc::handle_aux_stream(h);
+        cudaEvent_t staged[2] = {nullptr, nullptr};
+        for (cudaEvent_t& e : staged)
+            if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess)
+                return fctc::handle_fail(h, FCTC_E_CUDA, "cudaEventCreate failed");
+        auto stage = [&](int64_t first, int set, DxInputs* in) -> int {
+            const int64_t cnt = std::min(chunk, n_pairs - first);
+            if (int rc = dx_stage(h, set, cs, post1_host + first * n_rows_1 * n_labels * eb,
+                                  post2_host + first * n_rows_2 * n_labels * eb, in_f16,
+                                  envelope_host ? envelope_host + first * n_rows_1 * 2 : nullptr, cnt, n_rows_1, n_rows_2,
+                                  n_labels, in))
+                return rc;
+            if (cudaEventRecord(staged[set], cs) != cudaSuccess) return fctc::handle_fail(h, FCTC_E_CUDA, "cudaEventRecord failed");
+            return 0;
+        };
+        DxInputs in[2];
+        if (chunk < n_pairs) {  // both input sets exist before the scratch takes its share of what is free
+            const size_t b1 = size_t(chunk) * n_rows_1 * n_labels * eb, b2 = size_t(chunk) * n_rows_2 * n_labels * eb;
+            for (int base : {0, 13})
+                if (!fctc::handle_device_buffer(h, base, std::max<size_t>(b1, 16)) ||
+                    !fctc::handle_device_buffer(h, base + 1, std::max<size_t>(b2, 16)) ||
+                    (envelope_host && !fctc::handle_device_buffer(h, base + 2, size_t(chunk) * n_rows_1 * 16))) {
+                    for (cudaEvent_t e : staged) cudaEventDestroy(e);
+                    return FCTC_E_NOMEM;
+                }
+        }
+        int rc = stage(0, 0, &in[0]);
+        int set = 0;
+        for (int64_t first = 0; rc == 0 && first < n_pairs; first += chunk, set ^= 1) {
+            const int64_t cnt = std::min(chunk, n_pairs - first);
+            DxChunk ck;
+            rc = dx_launch(h, in[set], staged[set], in_f16, cnt, n_rows_1, n_rows_2, n_labels, W, beam_size, beam_cut_threshold,
+                           collapse_repeats, exp_mode, 0, offsets + first, lens + first, status + first, &ck);
+            if (rc == 0 && first + chunk < n_pairs) rc = stage(first + chunk, set ^ 1, &in[set ^ 1]);
+            if (rc == 0) rc = dx_finish(h, ck, labels, pool_capacity, offsets + first, &used);
+        }
+        cudaStreamSynchronize(cs);
+        for (cudaEvent_t e : staged) cudaEventDestroy(e);
+        if (rc) return rc;
     }
     // pairs whose trie (or ring pool) outgrew the default plan: gathered and decoded again in one pass per group of at
     // most 256 MiB of posteriors, at the hard bound (one ring per node: cannot overflow)

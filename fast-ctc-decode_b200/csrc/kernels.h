@@ -18,6 +18,7 @@ void* handle_device_buffer(fctc_handle* h, int index, size_t bytes);  // NULL on
 size_t handle_device_buffer_bytes(const fctc_handle* h, int index);   // current size of a persistent buffer
 void* handle_pinned_buffer(fctc_handle* h, int index, size_t bytes);
 cudaStream_t handle_stream(fctc_handle* h);
+cudaStream_t handle_aux_stream(fctc_handle* h);  // a second stream of the handle, for copies that run under a kernel
 
 // Integer tuning knob from the environment (development aid), 0 when unset or not positive.  Each call site keeps
 // the value in a function-local static, so the environment is read once per process, not once per launch.

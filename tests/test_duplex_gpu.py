@@ -172,6 +172,51 @@ def test_ring_pool_reuse_and_overflow_retry():
         assert (4 in out["device_status"]) == expect_refusals, f"rings={rings}: device statuses {out['device_status']}"
 
 
+CHUNK_SCRIPT = r"""
+import json, numpy as np
+import fctc_b200, oracle
+from helpers import duplex_pairs, band_envelope
+oracle.build()
+dec = fctc_b200.Decoder(0)
+rng = np.random.default_rng(99)
+N, T = 37, 120
+p1, p2 = duplex_pairs(rng, N, T, T + 7)
+env = band_envelope(N, T, T + 7, 12)
+ok = {}
+for mode in (0, 1):
+    for f16 in (False, True):
+        a1, a2 = (p1.astype(np.float16), p2.astype(np.float16)) if f16 else (p1, p2)
+        res = dec.beam_search_duplex_batch(a1, a2, env, 5, 0.0, True, exp_mode=mode)
+        ol, olen, ost = oracle.beam_search_duplex_batch(a1.astype(np.float32), a2.astype(np.float32), env.astype(np.uint64), 5, 0.0,
+                                                        True, exp_mode=mode)
+        same = res["status"].tolist() == ost.tolist()
+        for n in range(N):
+            o, ln = int(res["offsets"][n]), int(res["lens"][n])
+            same = same and res["labels"][o:o + ln].tolist() == ol[n, :olen[n]].tolist()
+        ok[f"{mode}_{int(f16)}"] = bool(same)
+print(json.dumps(ok))
+"""
+
+
+def test_host_batch_in_several_chunks():
+    """The host entry point copies chunk k+1 into a second set of input buffers while chunk k's kernel runs.  With
+    FCTC_DUPLEX_CHUNK_PAIRS=8 (read once per process, hence the subprocess) 37 pairs go through five chunks, the
+    last a short one; float32 and binary16, exact-exp and max-plus: all equal to the oracle."""
+    import json
+    import os
+    import subprocess
+    import sys
+    here = os.path.dirname(os.path.abspath(__file__))
+    root = os.path.dirname(here)
+    envv = dict(os.environ)
+    envv["PYTHONPATH"] = os.pathsep.join([root, os.path.join(root, "fast-ctc-decode_b200"), here])
+    envv["FCTC_DUPLEX_CHUNK_PAIRS"] = "8"
+    r = subprocess.run([sys.executable, "-c", CHUNK_SCRIPT], env=envv, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stderr[-2000:]
+    out = json.loads(r.stdout.strip().splitlines()[-1])
+    assert out and all(out.values()), out
+
+
 @pytest.mark.parametrize("case", CASES[:5], ids=lambda c: "N{}_T{}x{}_C{}_b{}_thr{}_c{}_w{}".format(*c))
 def test_cuda_exp_mode_tolerance(dec, oracle, case):
     """exp_mode 2 (CUDA's expf / log1pf): last-bit differences may flip a near-tie in a few pairs."""
