@@ -938,6 +938,7 @@ static int dx_batch_host_any(fctc_handle* h, const void* post1_any, const void* 
     if (n_pairs == 0) return 0;
     // ring size of the per-node vectors: the widest window the envelope asks for (clamped as the
     // kernel clamps), or all of network 2 without an envelope
+    auto widest_window = [&]() -> int64_t {
     int64_t wmax = n_rows_2;
     if (envelope_host) {
         // (16 bytes per network-1 row: for a large batch the scan is split over a few host threads — one thread took
@@ -965,7 +966,9 @@ static int dx_batch_host_any(fctc_handle* h, const void* post1_any, const void* 
             wmax = *std::max_element(part.begin(), part.end());
         }
     }
-    const int W = int(wmax + 1);
+    return wmax;
+    };
+    int W = 0;  // found on the host while the first chunk is being copied in
     const int64_t pair_bytes = (n_rows_1 + n_rows_2) * int64_t(n_labels) * eb;
     // a chunk is a whole number of rounds of the pairs in flight (a partial round costs a full one), as many as 2 GiB
     // of posteriors hold, at least one
@@ -976,6 +979,11 @@ static int dx_batch_host_any(fctc_handle* h, const void* post1_any, const void* 
     static const int chunk_knob = fctc::env_knob("FCTC_DUPLEX_CHUNK_PAIRS");  // tuning / test knob
     if (chunk_knob > 0) chunk = chunk_knob;
     chunk = std::max<int64_t>(1, std::min<int64_t>(chunk, n_pairs));
+    if (chunk < n_pairs) {  // chunks of equal size: the same kernel time in total, and a shorter first copy to wait for
+        const int64_t n_chunks = (n_pairs + chunk - 1) / chunk;
+        const int64_t even = ((n_pairs + n_chunks - 1) / n_chunks + 3) & ~int64_t(3);
+        chunk = std::min(chunk, even);
+    }
     int64_t used = 0;
     {
         // chunk k+1 is copied into the other input set on a second stream while chunk k's kernel runs; the kernel is
@@ -1007,6 +1015,7 @@ static int dx_batch_host_any(fctc_handle* h, const void* post1_any, const void* 
                 }
         }
         int rc = stage(0, 0, &in[0]);
+        W = int(widest_window() + 1);
         int set = 0;
         for (int64_t first = 0; rc == 0 && first < n_pairs; first += chunk, set ^= 1) {
             const int64_t cnt = std::min(chunk, n_pairs - first);
