@@ -722,10 +722,20 @@ cudaStream_t handle_aux_stream(fctc_handle* h) { return h->slot[1].stream; }
 int64_t fctc_beam_scratch_bytes(const fctc_handle* h, int64_t n_reads, int64_t n_rows, int32_t n_labels,
                                 int32_t beam_size, int32_t nodes_per_row) {
     if (!h || n_labels <= 0 || beam_size <= 0) return 0;
-    // recommended size: one trie pool per resident warp, capped at 96 GiB (a smaller buffer is accepted
-    // by the device entry points: they run as many pools as fit, at least 4)
-    return fctc::beam_scratch_bytes(h->sm_count, n_reads, n_rows, n_labels, beam_size, nodes_per_row, int64_t(96) << 30,
-                                    nullptr, nullptr);
+    // recommended size: one trie pool per resident warp, capped at 96 GiB or 70 % of the device's memory, whichever is
+    // more (a smaller buffer is accepted by the device entry points: they run as many pools as fit, at least 4).
+    // At beam 32 and 10,000 rows a pool is 24 MB and the 4,736 resident warps of a B200 want 106 GiB: under a flat
+    // 96 GiB cap 4,292 of them ran and the rest of a launch's first round waited for a pool.
+    int64_t cap = int64_t(96) << 30;
+    size_t free_b = 0, total_b = 0;
+    int dev = -1;
+    if (cudaGetDevice(&dev) == cudaSuccess) {
+        if (dev != h->device) cudaSetDevice(h->device);
+        if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) cap = std::max<int64_t>(cap, int64_t(total_b / 10 * 7));
+        else cudaGetLastError();
+        if (dev != h->device) cudaSetDevice(dev);
+    }
+    return fctc::beam_scratch_bytes(h->sm_count, n_reads, n_rows, n_labels, beam_size, nodes_per_row, cap, nullptr, nullptr);
 }
 
 namespace {

@@ -200,7 +200,7 @@ int fctc_viterbi_search(fctc_handle* h, const float* post_host, int64_t n_rows, 
  * The device API needs trie scratch at scratch_dev (256-byte aligned): one pool of nodes_per_row
  * proposals per posterior row for every read in flight (hard bound (n_labels-1)*beam_size; 0
  * selects a default that the host entry points grow on FCTC_NODE_POOL_OVERFLOW).
- * fctc_beam_scratch_bytes() is the recommended size (a pool per resident warp, capped at 96 GiB);
+ * fctc_beam_scratch_bytes() is the recommended size (a pool per resident warp, capped at 96 GiB or 70 % of the device's memory, whichever is more);
  * a smaller buffer is accepted — the launch then keeps fewer reads in flight (at least 4 pools
  * must fit, else FCTC_E_CAPACITY).
  * ------------------------------------------------------------------------------------------ */
