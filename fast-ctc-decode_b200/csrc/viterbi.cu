@@ -96,6 +96,7 @@ struct WarpLayout {  // shared memory plan of the streaming kernel (bytes)
     int off_open;    // {sum, length} of the run left open at the end of the previous tile
     int warp_bytes;
     int cta_fixed;   // log tables at the start of the CTA's shared memory
+    int max_ctas;    // resident CTAs per SM the plan wants at most (0: as many as fit)
 };
 
 // Explicit shared-space accesses on 32-bit addresses (keeps address arithmetic 32-bit and lets
@@ -321,20 +322,23 @@ __global__ void __launch_bounds__(VW_THREADS, QSTRING ? VW_MINBLOCKS_Q : VW_MINB
             // emission flags (src/search.rs:347) and output positions
             int prev0 = __shfl_up_sync(FULLMASK, lab[RPL - 1], 1);
             if (lane == 0) prev0 = last_label;
+            // The emissions before this lane's first, from one ballot per row position: the four votes are independent,
+            // where a shuffle scan is five dependent steps (16 % of the kernel's stall samples sat on it).
             bool em[RPL];
-            int cnt = 0;
+            int li0 = 0;         // tile-local index of this lane's first emission
+            int tile_total = 0;  // warp-uniform
             {
                 int prev = prev0;
+                const unsigned below = (1u << lane) - 1u;
 #pragma unroll
                 for (int r = 0; r < RPL; ++r) {
                     em[r] = lab[r] != 0 && (!COLLAPSE || lab[r] != prev);
                     prev = lab[r];
-                    cnt += em[r] ? 1 : 0;
+                    const unsigned votes = __ballot_sync(FULLMASK, em[r]);
+                    li0 += __popc(votes & below);
+                    tile_total += __popc(votes);
                 }
             }
-            const int incl = warp_inclusive_scan(cnt, lane);
-            const int tile_total = __shfl_sync(FULLMASK, incl, 31);
-            const int li0 = incl - cnt;  // tile-local index of this lane's first emission
 
             // labels and emission rows go straight to the read's slot
             {
@@ -351,45 +355,43 @@ __global__ void __launch_bounds__(VW_THREADS, QSTRING ? VW_MINBLOCKS_Q : VW_MINB
             const int new_last = COLLAPSE ? __shfl_sync(FULLMASK, lab[RPL - 1], 31) : -1;
 
             if (QSTRING) {
-                // Run sums, always in row order (src/search.rs:362-365).  S[r] = sum of the run that
-                // starts at this lane's row r over the lane's own rows; a run that reaches the lane's
-                // last row is finished by the NEXT lane (which adds its leading rows that continue it,
-                // possibly none) and lands in the queue slot of its emission: slot s (1-based) holds the
-                // tile's s-th emission, slot 0 the run left open by the previous tile.
-                float S[RPL];
-                int nr[RPL];
-                bool reach[RPL];
+                // Run sums, always in row order (src/search.rs:362-365), as ONE chain over the lane's rows that starts
+                // anew wherever the label changes: acc[k] / len[k] = sum and length, up to row k, of the run that holds
+                // row k, counted from the run's first row in this lane.  A run that ends inside the lane and began
+                // here (at an emission) is complete: it goes to the queue slot of that emission — slot s (1-based)
+                // holds the tile's s-th emission, slot 0 the run left open by the previous tile.  The run that holds
+                // the lane's last row is finished by the NEXT lane (which adds its leading rows that continue it,
+                // possibly none); a run that came in from the previous lane is finished further down.
+                // (label_prob_total starts at 0.0, src/search.rs:339,354; 0.0 + p differs from p only in the sign of a
+                // zero, which the quality value, a function of 1 - mean, does not see.)
+                bool cont[RPL];  // row k carries on row k-1's run (k >= 1)
+                float acc[RPL];
+                int len[RPL];
+                acc[0] = pr[0];
+                len[0] = 1;
+                bool all_cont = COLLAPSE;
 #pragma unroll
-                for (int r = 0; r < RPL; ++r) {
-                    // label_prob_total starts at 0.0 (src/search.rs:339,354); 0.0 + p differs from p only in the sign of
-                    // a zero, which the quality value, a function of 1 - mean, does not see
-                    S[r] = pr[r];
-                    nr[r] = 1;
-                    bool alive = COLLAPSE;
-#pragma unroll
-                    for (int k = r + 1; k < RPL; ++k) {
-                        alive = alive && (lab[k] == lab[k - 1]);
-                        if (alive) { S[r] = __fadd_rn(S[r], pr[k]); nr[r] = k - r + 1; }
-                    }
-                    reach[r] = alive;  // without collapse every non-blank row is a finished run of its own
+                for (int k = 1; k < RPL; ++k) {
+                    cont[k] = COLLAPSE && lab[k] == lab[k - 1];
+                    acc[k] = cont[k] ? __fadd_rn(acc[k - 1], pr[k]) : pr[k];
+                    len[k] = cont[k] ? len[k - 1] + 1 : 1;
+                    all_cont = all_cont && cont[k];
                 }
                 {
-                    uint32_t slot = q_base + 8 * (li0 + 1);
+                    int e = li0;  // tile-local number of the last emission at or before row k
 #pragma unroll
-                    for (int r = 0; r < RPL; ++r) {
-                        if (em[r] && !reach[r]) sts_run(slot, S[r], nr[r]);
-                        if (em[r]) slot += 8;
+                    for (int k = 0; k < RPL; ++k) {
+                        e += em[k] ? 1 : 0;
+                        const bool ends = (k + 1 < RPL) ? !cont[k + 1] : !COLLAPSE;  // without collapse every row is a run
+                        if (ends && lab[k] != 0 && e != li0) sts_run(q_base + 8 * e, acc[k], len[k]);
                     }
                 }
                 bool open_out = false;
                 if (COLLAPSE) {
                     const bool c0 = lab[0] == prev0;
-                    float tS = S[RPL - 1];  // the run holding the lane's last row, from its first row in this lane
-                    int tn = 1;
-#pragma unroll
-                    for (int r = RPL - 2; r >= 0; --r)
-                        if (reach[r]) { tS = S[r]; tn = nr[r]; }
-                    const bool whole = c0 && reach[0];  // every row continues the run carried in
+                    float tS = acc[RPL - 1];  // the run holding the lane's last row, from its first row in this lane
+                    int tn = len[RPL - 1];
+                    const bool whole = c0 && all_cont;  // every row continues the run carried in
                     if (whole && prev0 != 0) tn = -1;   // its tail is unknown until the carry arrives
                     // The run left open by the previous tile.  The cell is only meaningful when one is open
                     // (open_in): otherwise shared memory may hold anything there — including the bit pattern
@@ -418,7 +420,7 @@ __global__ void __launch_bounds__(VW_THREADS, QSTRING ? VW_MINBLOCKS_Q : VW_MINB
 #pragma unroll
                         for (int r = 0; r + 1 < RPL; ++r) {
                             if (alive) { hs = __fadd_rn(hs, pr[r]); ++hn; }
-                            alive = alive && (lab[r + 1] == lab[r]);
+                            alive = alive && cont[r + 1];
                         }
                         sts_run(q_base + 8 * li0, hs, hn);
                     }
@@ -645,8 +647,18 @@ static bool plan_stream(const ViterbiParams& p, WarpLayout* L) {
     const long long rows = p.T < TILE ? p.T : TILE;
     const long long stage = ((rows * p.C * (p.in_f16 ? 2 : 4) + 15) & ~15LL) + 32;
     if (stage > 16 * 1024) return false;
-    // enough bytes in flight per warp to cover HBM latency at the variant's resident warps per SM
+    // Ring depth and resident CTAs.  Every warp is one stream of 2.5 KB requests into HBM, and beyond ~2,400-3,000
+    // concurrent streams the memory system loses efficiency faster than the extra warps gain (1M reads x 4000 x 5 f32,
+    // ms per launch as CTAs per SM x stages; with / without quality strings): 3x3 17.8 / 14.2, 4x2 16.6 / 14.2,
+    // 4x3 16.7 / 14.4, 5x3 16.6 / 16.1, 6x3 17.4 / 20.6 (round 1's choice with quality strings), 4x4 18.2 / 14.7 (round
+    // 1's choice without), 8x2 17.4 / 20.5, 2x4 22.7 / 13.85.  So the quality variant, which needs its warps for the
+    // arithmetic, runs 5 CTAs of 3 stages and the other 3 CTAs of 3 stages; other alphabets keep what shared memory allows.
     int ns = int(((p.qstring ? 8 : 11) * 1024) / stage);
+    L->max_ctas = 0;
+    if (!p.in_f16 && p.C <= 8) {
+        ns = 3;
+        L->max_ctas = p.qstring ? 5 : 3;
+    }
     if (p.in_f16) ns = p.qstring ? 6 : 10;  // half-size tiles: deeper rings (measured: 3 stages 1.43 ms, 10 stages 0.58 ms)
     static const int stages_knob = env_knob("FCTC_VIT_STAGES");  // tuning knob
     if (stages_knob > 0) ns = stages_knob;
@@ -672,6 +684,9 @@ static cudaError_t launch_stream(const ViterbiParams& p, const WarpLayout& L, in
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, VW_THREADS, smem);
     if (e != cudaSuccess) return e;
     if (per_sm < 1) per_sm = 1;
+    static const int ctas_knob = env_knob("FCTC_VIT_CTAS");  // tuning knob: resident CTAs per SM, up to what fits
+    const int want = ctas_knob > 0 ? ctas_knob : L.max_ctas;
+    if (want > 0 && want < per_sm) per_sm = want;
     long long grid = (long long)sm_count * per_sm;
     const long long need = (p.N + VW_WARPS - 1) / VW_WARPS;
     if (grid > need) grid = need;
