@@ -659,7 +659,11 @@ static bool plan_stream(const ViterbiParams& p, WarpLayout* L) {
         ns = 3;
         L->max_ctas = p.qstring ? 5 : 3;
     }
-    if (p.in_f16) ns = p.qstring ? 6 : 10;  // half-size tiles: deeper rings (measured: 3 stages 1.43 ms, 10 stages 0.58 ms)
+    if (p.in_f16) {  // half-size tiles: deeper rings.  With quality strings the kernel is bound by its arithmetic (6 CTAs x 6
+        // stages 15.0 ms, 4 x 6 16.3, 3 x 6 18.4); without, by the streams again (3 x 6 8.31 ms, 4 x 4 8.36, 4 x 10 8.65, 8 x 4 19.5)
+        ns = p.qstring ? 6 : (p.C <= 8 ? 6 : 10);
+        if (!p.qstring && p.C <= 8) L->max_ctas = 3;
+    }
     static const int stages_knob = env_knob("FCTC_VIT_STAGES");  // tuning knob
     if (stages_knob > 0) ns = stages_knob;
     if (ns > VW_MAX_STAGES) ns = VW_MAX_STAGES;
