@@ -19,8 +19,8 @@ PLANS = {
     "18beam_search_kernelILb0ELi5ELb1E": (128, 8),   # the same, 16-bit posteriors
     "18beam_search_kernelILb1ELi5ELb0E": (128, 8),   # crf
     "17beam_small_kernelILb0ELi5ELb0E": (128, 8),    # narrow beam: 32 warps per SM
-    "21viterbi_stream_kernelIhLi4ELb1ELb1ELb1ELb0ELb0E": (128, 6),  # headline: qstring, collapse, five labels, f32
-    "21viterbi_stream_kernelIhLi4ELb1ELb0ELb1ELb0ELb0E": (128, 4),  # without quality strings: 4 CTAs, deeper rings
+    "21viterbi_stream_kernelIhLi4ELb1ELb1ELb1ELb0ELb0E": (128, 5),  # headline: qstring, collapse, five labels, f32 (5 CTAs by plan)
+    "21viterbi_stream_kernelIhLi4ELb1ELb0ELb1ELb0ELb0E": (128, 3),  # without quality strings: 3 CTAs by plan
     "20duplex_packed_kernelILi0E": (32, 16),         # exact exp: 16 single-warp CTAs
     "20duplex_packed_kernelILi1E": (32, 24),
     "20duplex_packed_kernelILi2E": (32, 24),
