@@ -655,14 +655,15 @@ static bool plan_stream(const ViterbiParams& p, WarpLayout* L) {
     // arithmetic, runs 5 CTAs of 3 stages and the other 3 CTAs of 3 stages; other alphabets keep what shared memory allows.
     int ns = int(((p.qstring ? 8 : 11) * 1024) / stage);
     L->max_ctas = 0;
-    if (!p.in_f16 && p.C == 5) {  // (four labels, whose rows go through the interleaved path, still gain up to 7-8 CTAs)
+    if (!p.in_f16 && p.C == 5 && p.softmax == 0) {  // (four labels, whose rows go through the interleaved path, still gain up to
+        // 7-8 CTAs; logits, with the softmax in the kernel, keep every warp they can get)
         ns = 3;
         L->max_ctas = p.qstring ? 5 : 3;
     }
     if (p.in_f16) {  // half-size tiles: deeper rings.  With quality strings the kernel is bound by its arithmetic (6 CTAs x 6
         // stages 15.0 ms, 4 x 6 16.3, 3 x 6 18.4); without, by the streams again (3 x 6 8.31 ms, 4 x 4 8.36, 4 x 10 8.65, 8 x 4 19.5)
         ns = p.qstring ? 6 : (p.C == 5 ? 6 : 10);
-        if (!p.qstring && p.C == 5) L->max_ctas = 3;
+        if (!p.qstring && p.C == 5 && p.softmax == 0) L->max_ctas = 3;
     }
     static const int stages_knob = env_knob("FCTC_VIT_STAGES");  // tuning knob
     if (stages_knob > 0) ns = stages_knob;
